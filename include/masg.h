@@ -1,0 +1,142 @@
+/*
+ * masg.h — C ABI of libmasg.so: the B200 (sm_100a) batched synthesis path for
+ * sarulab-speech/Mid-Attribute-Speaker-Generation.
+ *
+ * The reference has no FFI/plugin interface of its own (it is pure Python/PyTorch);
+ * the drop-in boundary is the Python call surface of two nn.Modules and three distribution helpers
+ * (SURVEY.md §8(b)).  Each entry point below names the reference callable it stands behind
+ * (file:line under the reference tree).  The Python shims in
+ * mid-attribute-speaker-generation_b200/{fastspeech2,hifigan,distributions}.py keep the reference
+ * signatures and forward here through ctypes; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - plain C symbols, no exceptions cross the boundary; every call returns 0 on success, non-zero
+ *     on error, and masg_last_error(ctx) returns a message (the shim raises RuntimeError).
+ *   - all pointers are DEVICE pointers on the context's device unless the name starts with h_.
+ *   - all work is enqueued on the cudaStream_t passed as `void* stream` (0 = legacy default
+ *     stream); no hidden device-wide synchronisation.  The only host syncs are the documented ones
+ *     (phase A publishes T_max; the *_host entry points copy results back).
+ *   - inputs/outputs are caller-owned; the library owns its repacked weights and a workspace arena.
+ *   - a context is not thread-safe; contexts are independent.  One context per (device, stream).
+ *   - no CPU fallback and no alternate backends: an unsupported configuration is an error.
+ */
+#ifndef MASG_H_
+#define MASG_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct masg_ctx masg_ctx;
+
+enum { MASG_PREC_BF16 = 0,   /* bf16 operands on tcgen05 tensor cores, fp32 accumulate (mel max-abs <= 1e-2) */
+       MASG_PREC_FP32 = 1 }; /* fp32 CUDA-core path (mel max-abs <= 1e-4); the strict-parity mode       */
+
+/* library / build identification (no reference counterpart) */
+const char* masg_version(void);
+
+/* utils/model.py:11-34 get_model → one context per device.  precision: MASG_PREC_*. */
+int  masg_ctx_create(int device, int precision, masg_ctx** out);
+void masg_ctx_destroy(masg_ctx* ctx);
+const char* masg_last_error(masg_ctx* ctx);   /* ctx may be NULL: returns the last ctx-less error */
+
+/* nn.Module.load_state_dict (utils/model.py:21 for FastSpeech2, :66 for hifigan.Generator):
+ * register one caller-owned fp32 (or int64 for num_batches_tracked: ignored) device tensor under its
+ * reference state_dict key.  `model` is "fs2" or "hifigan".  HiFi-GAN accepts
+ * either weight-normed keys (weight_g/weight_v) or folded ones (weight).  Tensors are read at commit. */
+int masg_load_tensor(masg_ctx* ctx, const char* model, const char* key, const float* dev_ptr,
+                     int ndim, const int64_t* shape);
+/* Repack the registered tensors into kernel layouts (QKV concat, conv weights to [k][Cin][Cout],
+ * BatchNorm folded (transformer/Layers.py:129-137), weight-norm folded = Generator.remove_weight_norm,
+ * hifigan/models.py:167-174).  Re-callable after another load_state_dict. */
+int masg_fs2_commit(masg_ctx* ctx, void* stream);
+int masg_hifigan_commit(masg_ctx* ctx, void* stream);
+
+/* FastSpeech2.forward / synthesize_from_speaker_emb, first half (model/fastspeech2.py:187-241):
+ * get_mask_from_lengths → Encoder → + speaker embedding → duration/pitch/energy predictors →
+ * bucketize+embedding → duration rounding → mel lengths.  Performs ONE stream synchronisation to
+ * publish max(mel_lens) to *h_tmax (host).
+ *   texts, accents : int64 [B, L]   (accents_is_1d != 0: accents is [L], broadcast over the batch,
+ *                                    synthesize.py:234)
+ *   src_lens       : int64 [B];  spk_emb: fp32 [B,256]
+ *   p_ctl, e_ctl, d_ctl: controls; e_ctl is accepted and IGNORED, energy is scaled by p_ctl exactly
+ *                        as model/modules.py:123-125 does.
+ *   d_target       : nullable fp32 [B, L]: teacher-forced durations (modules.py:128-130)
+ *   out: pitch, energy, log_d, d_rounded fp32 [B, L]; mel_lens int64 [B]; src_mask uint8 [B, L]
+ *        (1 = pad). */
+int masg_fs2_phase_a(masg_ctx* ctx, void* stream, const int64_t* texts, const int64_t* accents,
+                     int accents_is_1d, const int64_t* src_lens, int B, int L, const float* spk_emb,
+                     float p_ctl, float e_ctl, float d_ctl, const float* d_target,
+                     float* pitch, float* energy, float* log_d, float* d_rounded, int64_t* mel_lens,
+                     uint8_t* src_mask, int64_t* h_tmax);
+
+/* Second half (model/fastspeech2.py:232-244): LengthRegulator (model/modules.py:167-194) → Decoder →
+ * mel_linear → PostNet + residual.  Uses the state left by the preceding phase A on the same ctx.
+ *   out: mel, postnet_mel fp32 [B, T, 80]; mel_mask uint8 [B, T] (1 = pad); T = *h_tmax of phase A,
+ *        or the caller's max_mel_len. */
+int masg_fs2_phase_b(masg_ctx* ctx, void* stream, int T, float* mel, float* postnet_mel, uint8_t* mel_mask);
+
+/* LengthRegulator.forward alone (model/modules.py:167-194 + utils/tools.py:363-381) and the duration
+ * rule of VarianceAdaptor.forward (modules.py:132-135) — the bit-exact integer kernels, exposed for
+ * parity tests.  masg_duration_round: d = clamp(rint(exp(log_d) - 1) * d_ctl, 0).  masg_length_regulate:
+ * x fp32 [B, L, C], d fp32 [B, L] → out fp32 [B, T, C] zero-padded, mel_lens int64 [B], mask uint8 [B,T]. */
+int masg_duration_round(masg_ctx* ctx, void* stream, const float* log_d, float d_ctl, int64_t n, float* d_rounded);
+int masg_mel_lengths(masg_ctx* ctx, void* stream, const float* d, int B, int L, int64_t* mel_lens);
+int masg_length_regulate(masg_ctx* ctx, void* stream, const float* x, const float* d, int B, int L, int C,
+                         int T, float* out, int64_t* mel_lens, uint8_t* mel_mask);
+/* VarianceAdaptor.get_pitch_embedding tail (modules.py:85-88): x[row] += table[bucketize(v[row], bins)] */
+int masg_bucketize_embed_add(masg_ctx* ctx, void* stream, const float* v, const float* bins, int n_bins_m1,
+                             const float* table, int64_t rows, int C, float* x, int64_t* idx_out /*nullable*/);
+
+/* hifigan.Generator.forward (hifigan/models.py:149-165): mel fp32 [B, 80, T] → wav fp32 [B, 1, 256 T].
+ * wav_i16 (nullable): int16 [B, 256 T] = C-cast of wav*32768 as utils/model.py:82-85 (wrap, not saturate).
+ * mel_is_channels_last != 0: mel is [B, T, 80] (postnet output layout; skips the transpose that
+ * utils/tools.py:266 performs). */
+int masg_hifigan_forward(masg_ctx* ctx, void* stream, const float* mel, int mel_is_channels_last, int B, int T,
+                         float* wav, int16_t* wav_i16);
+
+/* SpeakerMetaEncoder.forward (model/fastspeech2.py:332-341): meta fp32 [N,4] → pi [N,3], mu/sigma [N,3,256]. */
+int masg_gmm_params(masg_ctx* ctx, void* stream, const float* meta, int N, float* pi, float* mu, float* sigma);
+/* MixtureSameFamily.sample() (model/fastspeech2.py:176-180, distributions.py .sample()): per row n draw
+ * k ~ Categorical(pi[n or 0]) and x = mu[.,k] + scale[.,k]·eps.  Philox counter RNG (seed, offset).
+ * pi [Np,K], mu/scale [Np,K,D] with Np = N or 1 (broadcast).  k_inject (int32 [N]) / eps_inject (fp32
+ * [N,D]) nullable: inject the draws for exact tests.  k_out nullable. */
+int masg_gmm_sample(masg_ctx* ctx, void* stream, const float* pi, const float* mu, const float* scale,
+                    int N, int Np, int K, int D, uint64_t seed, uint64_t offset,
+                    const int32_t* k_inject, const float* eps_inject, float* out, int32_t* k_out);
+/* InterpolateGMM.__init__/interpolate_rate (model/distributions.py:12-62): device closed forms for the
+ * K×K cost (as written, Appendix B-9), component means and McCann scales; the K×K exact EMD
+ * (ot.emd, :22) runs on the host inside this call (one small D2H of the cost matrix).
+ * a/b: pi [K], mu/sigma [K,D].  out: weights [K*K] (gamma.flatten()), comp_mu/comp_scale [K*K, D]
+ * in the reference's (j,i) order; h_cost (nullable host double [K*K]). */
+int masg_gmm_interpolate(masg_ctx* ctx, void* stream, const float* pi_a, const float* mu_a, const float* sig_a,
+                         const float* pi_b, const float* mu_b, const float* sig_b, int K, int D, float t,
+                         int recompute_plan, float* weights, float* comp_mu, float* comp_scale, double* h_cost);
+/* BarycenterGMM maths (model/distributions.py:136-192): A attribute GMMs (pi [A,K], mu/sigma [A,K,D]),
+ * rate [A] → all K^A barycentres (mean [K^A,D], std [K^A,D]) and per-barycentre weights [K^A]
+ * (zero for unused ones); the shim keeps the reference's first-use component order. */
+int masg_gmm_barycenter(masg_ctx* ctx, void* stream, const float* pi, const float* mu, const float* sigma,
+                        const float* h_rate, int A, int K, int D, float* bary_mean, float* bary_std,
+                        float* bary_weight, int32_t* assign /* [A*K] nearest barycentre index */);
+
+/* End-to-end with HOST buffers (examples_gen.py:114-140 synthesize() + utils/model.py:74-92
+ * vocoder_infer): H2D of ids/lens/speaker embeddings, FastSpeech2, HiFi-GAN, int16 conversion and D2H
+ * of the waveforms, all inside the call.  h_wav_i16 must hold B * 256 * t_cap samples; rows are
+ * written with stride 256 * t_cap (t_cap >= resulting T_max, else error).  h_mel_lens int64 [B]. */
+int masg_synthesize_host(masg_ctx* ctx, void* stream, const int64_t* h_texts, const int64_t* h_accents,
+                         const int64_t* h_src_lens, int B, int L, const float* h_spk_emb,
+                         float p_ctl, float e_ctl, float d_ctl, int t_cap,
+                         int16_t* h_wav_i16, int64_t* h_mel_lens, int64_t* h_tmax);
+
+/* Counters for the benchmark harness: number of kernels this context launched since the last reset. */
+int64_t masg_launch_count(masg_ctx* ctx, int reset);
+/* Intermediate tap for parity tests: copies a named internal fp32 buffer of the last forward
+ * ("encoder_out" [B,L,256], "lr_out" [B,T,256], "decoder_out" [B,T,256]) into dst (device, fp32). */
+int masg_debug_tap(masg_ctx* ctx, void* stream, const char* name, float* dst, int64_t n_elems);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MASG_H_ */

@@ -1,0 +1,314 @@
+// extern "C" boundary of libmasg.so (include/masg.h).  No exceptions cross it: every entry point
+// catches MasgError and returns non-zero with the message retrievable through masg_last_error().
+#include "common.cuh"
+#include "tc.cuh"
+#include <cstring>
+#include <cmath>
+#include <algorithm>
+
+static thread_local std::string g_err;
+
+#define API_BEGIN(ctx)                                                                   \
+    if (!(ctx)) { g_err = "null masg_ctx"; return 1; }                                     \
+    try {                                                                                  \
+        int _dev = -1; cudaGetDevice(&_dev);                                               \
+        if (_dev != (ctx)->device) CUDA_OK(cudaSetDevice((ctx)->device));
+#define API_END(ctx)                                                                     \
+        return 0;                                                                          \
+    } catch (const MasgError& e) { (ctx)->err = e.msg; g_err = e.msg; return 1; }          \
+      catch (const std::exception& e) { (ctx)->err = e.what(); g_err = e.what(); return 2; }
+
+extern "C" {
+
+const char* masg_version(void) { return "masg-b200 0.1 (sm_100a)"; }
+
+int masg_ctx_create(int device, int precision, masg_ctx** out) {
+    try {
+        MASG_CHECK(out != nullptr, "null out pointer");
+        MASG_CHECK(precision == MASG_PREC_BF16 || precision == MASG_PREC_FP32, "unknown precision %d", precision);
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        MASG_CHECK(e == cudaSuccess && n > 0, "no CUDA device available (%s): this library has no CPU fallback", cudaGetErrorString(e));
+        MASG_CHECK(device >= 0 && device < n, "device %d out of range (%d devices)", device, n);
+        cudaDeviceProp prop;
+        CUDA_OK(cudaGetDeviceProperties(&prop, device));
+        MASG_CHECK(prop.major == 10, "device %d is sm_%d%d; libmasg is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        CUDA_OK(cudaSetDevice(device));
+        masg_ctx* c = new masg_ctx();
+        c->device = device; c->precision = precision;
+        CUDA_OK(cudaMallocHost(&c->h_pinned, 64 * sizeof(int64_t)));
+        *out = c;
+        return 0;
+    } catch (const MasgError& e) { g_err = e.msg; return 1; }
+}
+
+static void free_owned(masg_ctx* c) {
+    for (void* p : c->owned) cudaFree(p);
+    c->owned.clear();
+    c->pos_long = nullptr; c->pos_long_n = 0;
+}
+
+void masg_ctx_destroy(masg_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_owned(c);
+    c->arena.release(); c->arena_b.release();
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->io_buf) cudaFree(c->io_buf);
+    delete c;
+}
+
+const char* masg_last_error(masg_ctx* c) { return c ? c->err.c_str() : g_err.c_str(); }
+
+int masg_load_tensor(masg_ctx* c, const char* model, const char* key, const float* dev_ptr, int ndim, const int64_t* shape) {
+    API_BEGIN(c)
+    MASG_CHECK(model && key && dev_ptr, "null argument");
+    cudaPointerAttributes at;
+    CUDA_OK(cudaPointerGetAttributes(&at, dev_ptr));
+    MASG_CHECK(at.type == cudaMemoryTypeDevice && at.device == c->device, "tensor '%s' is not on cuda:%d (CPU tensors are an error: no fallback)", key, c->device);
+    TensorRef t; t.ptr = dev_ptr; t.shape.assign(shape, shape + ndim);
+    if (!strcmp(model, "fs2")) { c->fs2_t[key] = t; c->fs2_ready = false; }
+    else if (!strcmp(model, "hifigan")) { c->hg_t[key] = t; c->hg_ready = false; }
+    else MASG_CHECK(false, "unknown model '%s' (expected 'fs2' or 'hifigan')", model);
+    API_END(c)
+}
+
+int masg_fs2_commit(masg_ctx* c, void* stream) {
+    API_BEGIN(c)
+    fs2_commit(c, (cudaStream_t)stream);
+    API_END(c)
+}
+int masg_hifigan_commit(masg_ctx* c, void* stream) {
+    API_BEGIN(c)
+    hifigan_commit(c, (cudaStream_t)stream);
+    API_END(c)
+}
+
+int masg_fs2_phase_a(masg_ctx* c, void* stream, const int64_t* texts, const int64_t* accents, int accents_is_1d,
+                     const int64_t* src_lens, int B, int L, const float* spk_emb, float p_ctl, float e_ctl, float d_ctl,
+                     const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded, int64_t* mel_lens,
+                     uint8_t* src_mask, int64_t* h_tmax) {
+    API_BEGIN(c)
+    MASG_CHECK(texts && src_lens && spk_emb && pitch && energy && log_d, "null argument");
+    fs2_phase_a(c, (cudaStream_t)stream, texts, accents, accents_is_1d, src_lens, B, L, spk_emb, p_ctl, e_ctl, d_ctl, d_target,
+                pitch, energy, log_d, d_rounded, mel_lens, src_mask, h_tmax);
+    API_END(c)
+}
+int masg_fs2_phase_b(masg_ctx* c, void* stream, int T, float* mel, float* postnet_mel, uint8_t* mel_mask) {
+    API_BEGIN(c)
+    MASG_CHECK(mel && postnet_mel, "null argument");
+    fs2_phase_b(c, (cudaStream_t)stream, T, mel, postnet_mel, mel_mask);
+    API_END(c)
+}
+
+int masg_duration_round(masg_ctx* c, void* stream, const float* log_d, float d_ctl, int64_t n, float* d_rounded) {
+    API_BEGIN(c)
+    if (n > 0) launch_duration(c, (cudaStream_t)stream, log_d, d_ctl, n, d_rounded);
+    API_END(c)
+}
+int masg_mel_lengths(masg_ctx* c, void* stream, const float* d, int B, int L, int64_t* mel_lens) {
+    API_BEGIN(c)
+    if (B > 0) launch_mel_lens(c, (cudaStream_t)stream, d, B, L, mel_lens, nullptr);
+    API_END(c)
+}
+int masg_length_regulate(masg_ctx* c, void* stream, const float* x, const float* d, int B, int L, int C, int T, float* out,
+                         int64_t* mel_lens, uint8_t* mel_mask) {
+    API_BEGIN(c)
+    MASG_CHECK(C % 4 == 0, "C=%d must be a multiple of 4", C);
+    launch_length_regulate(c, (cudaStream_t)stream, x, d, B, L, C, T, nullptr, out, mel_lens, mel_mask);
+    API_END(c)
+}
+int masg_bucketize_embed_add(masg_ctx* c, void* stream, const float* v, const float* bins, int n_bins_m1, const float* table,
+                             int64_t rows, int C, float* x, int64_t* idx_out) {
+    API_BEGIN(c)
+    MASG_CHECK(C % 4 == 0, "C=%d must be a multiple of 4", C);
+    if (rows > 0) launch_bucket_add(c, (cudaStream_t)stream, v, bins, n_bins_m1, table, rows, C, x, idx_out);
+    API_END(c)
+}
+
+int masg_hifigan_forward(masg_ctx* c, void* stream, const float* mel, int mel_is_channels_last, int B, int T, float* wav,
+                         int16_t* wav_i16) {
+    API_BEGIN(c)
+    MASG_CHECK(mel && (wav || wav_i16), "null argument");
+    hifigan_forward(c, (cudaStream_t)stream, mel, mel_is_channels_last, B, T, wav, wav_i16);
+    API_END(c)
+}
+
+int masg_gmm_params(masg_ctx* c, void* stream, const float* meta, int N, float* pi, float* mu, float* sigma) {
+    API_BEGIN(c)
+    MASG_CHECK(c->fs2_ready, "FastSpeech2 weights not committed");
+    if (N > 0) launch_gmm_params(c, (cudaStream_t)stream, meta, N, pi, mu, sigma);
+    API_END(c)
+}
+int masg_gmm_sample(masg_ctx* c, void* stream, const float* pi, const float* mu, const float* scale, int N, int Np, int K, int D,
+                    uint64_t seed, uint64_t offset, const int32_t* k_inject, const float* eps_inject, float* out, int32_t* k_out) {
+    API_BEGIN(c)
+    MASG_CHECK(Np == 1 || Np == N, "Np=%d must be 1 or N=%d", Np, N);
+    if (N > 0) launch_gmm_sample(c, (cudaStream_t)stream, pi, mu, scale, N, Np, K, D, seed, offset, k_inject, eps_inject, out, k_out);
+    API_END(c)
+}
+
+// Exact earth-mover plan for an n x m problem (n, m <= 4): enumerate the basic solutions of the
+// transportation polytope (supports of n+m-1 cells), keep the cheapest feasible one; ties keep the
+// lexicographically first support.  Stands in for POT ot.emd (model/distributions.py:22).
+static void emd_small(const double* a, const double* b_in, const double* M, int n, int m, double* G) {
+    double b[8], sa = 0, sb = 0;
+    for (int i = 0; i < n; ++i) sa += a[i];
+    for (int j = 0; j < m; ++j) sb += b_in[j];
+    for (int j = 0; j < m; ++j) b[j] = b_in[j] * (sa / sb);
+    int nc = n * m, ns = n + m - 1;
+    std::vector<int> idx(ns);
+    for (int i = 0; i < ns; ++i) idx[i] = i;
+    double best = INFINITY; std::vector<int> bsup; std::vector<double> bx;
+    while (true) {
+        // solve rows: n row-sum constraints + first m-1 column constraints
+        double A[8][9];
+        for (int r = 0; r < ns; ++r) {
+            for (int t = 0; t < ns; ++t) {
+                int ci = idx[t] / m, cj = idx[t] % m;
+                A[r][t] = r < n ? (ci == r ? 1.0 : 0.0) : (cj == r - n ? 1.0 : 0.0);
+            }
+            A[r][ns] = r < n ? a[r] : b[r - n];
+        }
+        bool sing = false;
+        for (int col = 0; col < ns && !sing; ++col) {
+            int piv = col; double mx = fabs(A[col][col]);
+            for (int r = col + 1; r < ns; ++r) if (fabs(A[r][col]) > mx) { mx = fabs(A[r][col]); piv = r; }
+            if (mx < 1e-12) { sing = true; break; }
+            if (piv != col) for (int t = 0; t <= ns; ++t) std::swap(A[piv][t], A[col][t]);
+            for (int r = 0; r < ns; ++r) if (r != col) {
+                double f = A[r][col] / A[col][col];
+                if (f != 0.0) for (int t = col; t <= ns; ++t) A[r][t] -= f * A[col][t];
+            }
+        }
+        if (!sing) {
+            double x[8]; bool ok = true; double lastcol = 0;
+            for (int t = 0; t < ns; ++t) { x[t] = A[t][ns] / A[t][t]; if (x[t] < -1e-12) ok = false; }
+            for (int t = 0; t < ns && ok; ++t) if (idx[t] % m == m - 1) lastcol += x[t];
+            if (ok && fabs(lastcol - b[m - 1]) > 1e-9) ok = false;
+            if (ok) {
+                double cost = 0;
+                for (int t = 0; t < ns; ++t) cost += x[t] * M[idx[t]];
+                if (cost < best - 1e-15) { best = cost; bsup = idx; bx.assign(x, x + ns); }
+            }
+        }
+        int t = ns - 1;
+        while (t >= 0 && idx[t] == nc - ns + t) --t;
+        if (t < 0) break;
+        ++idx[t];
+        for (int r = t + 1; r < ns; ++r) idx[r] = idx[r - 1] + 1;
+    }
+    for (int i = 0; i < nc; ++i) G[i] = 0.0;
+    for (size_t t = 0; t < bsup.size(); ++t) G[bsup[t]] = bx[t] > 0 ? bx[t] : 0.0;
+}
+
+int masg_gmm_interpolate(masg_ctx* c, void* stream, const float* pi_a, const float* mu_a, const float* sig_a, const float* pi_b,
+                         const float* mu_b, const float* sig_b, int K, int D, float t, int recompute_plan, float* weights,
+                         float* comp_mu, float* comp_scale, double* h_cost) {
+    API_BEGIN(c)
+    cudaStream_t s = (cudaStream_t)stream;
+    MASG_CHECK(K >= 1 && K <= 4, "K=%d unsupported (exact EMD enumerates supports for K <= 4)", K);
+    launch_gmm_interp_comps(c, s, mu_a, sig_a, mu_b, sig_b, K, D, t, comp_mu, comp_scale);
+    if (recompute_plan) {
+        c->arena_b.reset();
+        double* cost = c->arena_b.get<double>(K * K);
+        launch_gmm_interp_cost(c, s, mu_a, sig_a, mu_b, sig_b, K, D, cost);
+        double hc[16], G[16], ha[4], hb[4]; float fa[4], fb[4], fw[16];
+        CUDA_OK(cudaMemcpyAsync(hc, cost, K * K * sizeof(double), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(fa, pi_a, K * sizeof(float), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(fb, pi_b, K * sizeof(float), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        for (int i = 0; i < K; ++i) { ha[i] = fa[i]; hb[i] = fb[i]; }
+        emd_small(ha, hb, hc, K, K, G);
+        for (int i = 0; i < K * K; ++i) fw[i] = (float)G[i];
+        CUDA_OK(cudaMemcpyAsync(weights, fw, K * K * sizeof(float), cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaStreamSynchronize(s));          // fw is a stack buffer
+        if (h_cost) memcpy(h_cost, hc, K * K * sizeof(double));
+    }
+    API_END(c)
+}
+
+int masg_gmm_barycenter(masg_ctx* c, void* stream, const float* pi, const float* mu, const float* sigma, const float* h_rate,
+                        int A, int K, int D, float* bary_mean, float* bary_std, float* bary_weight, int32_t* assign) {
+    API_BEGIN(c)
+    cudaStream_t s = (cudaStream_t)stream;
+    MASG_CHECK(A >= 1 && A <= 8 && K >= 1, "A=%d K=%d unsupported", A, K);
+    int nb = 1; for (int a = 0; a < A; ++a) nb *= K;
+    c->arena_b.reset();
+    float* rate = c->arena_b.get<float>(A);
+    CUDA_OK(cudaMemcpyAsync(rate, h_rate, A * sizeof(float), cudaMemcpyHostToDevice, s));
+    launch_gmm_bary(c, s, mu, sigma, rate, A, K, D, bary_mean, bary_std);
+    launch_gmm_bary_assign(c, s, mu, sigma, bary_mean, bary_std, A, K, D, nb, assign);
+    std::vector<int32_t> ha(A * K); std::vector<float> hp(A * K), hw(nb, 0.f);
+    CUDA_OK(cudaMemcpyAsync(ha.data(), assign, A * K * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(hp.data(), pi, A * K * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    for (int i = 0; i < A; ++i) for (int j = 0; j < K; ++j) hw[ha[i * K + j]] += h_rate[i] * hp[i * K + j];
+    CUDA_OK(cudaMemcpyAsync(bary_weight, hw.data(), nb * sizeof(float), cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    API_END(c)
+}
+
+int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
+                         int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int t_cap,
+                         int16_t* h_wav_i16, int64_t* h_mel_lens, int64_t* h_tmax) {
+    API_BEGIN(c)
+    cudaStream_t s = (cudaStream_t)stream;
+    MASG_CHECK(h_texts && h_accents && h_src_lens && h_spk_emb && h_wav_i16, "null argument");
+    // the I/O staging area is a growth-only buffer of its own (arena/arena_b are reset by the phases)
+    size_t rows = (size_t)B * L;
+    size_t need_in = rows * 8 * 2 + B * 8 * 2 + (size_t)B * 256 * 4 + rows * 4 * 4 + 4096;
+    size_t need = need_in + ((size_t)B * t_cap * 80 * 4) * 2 + (size_t)B * t_cap * 256 * 2 + 4096;
+    if (c->io_cap < need) {
+        if (c->io_buf) { CUDA_OK(cudaStreamSynchronize(s)); cudaFree(c->io_buf); c->io_buf = nullptr; }
+        CUDA_OK(cudaMalloc(&c->io_buf, need)); c->io_cap = need;
+    }
+    char* p = (char*)c->io_buf;
+    auto take = [&](size_t bytes) { void* r = p; p += (bytes + 255) & ~size_t(255); return r; };
+    int64_t* texts = (int64_t*)take(rows * 8); int64_t* acc = (int64_t*)take(rows * 8);
+    int64_t* lens = (int64_t*)take(B * 8); int64_t* mel_lens = (int64_t*)take(B * 8);
+    float* spk = (float*)take((size_t)B * 256 * 4);
+    float* pitch = (float*)take(rows * 4); float* energy = (float*)take(rows * 4); float* logd = (float*)take(rows * 4);
+    float* drnd = (float*)take(rows * 4);
+    CUDA_OK(cudaMemcpyAsync(texts, h_texts, rows * 8, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(acc, h_accents, rows * 8, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(lens, h_src_lens, B * 8, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(spk, h_spk_emb, (size_t)B * 256 * 4, cudaMemcpyHostToDevice, s));
+    int64_t tmax = 0;
+    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, pitch, energy, logd, drnd, mel_lens, nullptr, &tmax);
+    MASG_CHECK(tmax > 0, "no frames to synthesise (all durations are zero)");
+    MASG_CHECK(tmax <= t_cap, "T_max=%lld exceeds t_cap=%d", (long long)tmax, t_cap);
+    int T = (int)tmax;
+    float* mel = (float*)take((size_t)B * T * 80 * 4); float* post = (float*)take((size_t)B * T * 80 * 4);
+    int16_t* w16 = (int16_t*)take((size_t)B * T * 256 * 2);
+    fs2_phase_b(c, s, T, mel, post, nullptr);
+    hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
+    CUDA_OK(cudaMemcpy2DAsync(h_wav_i16, (size_t)t_cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
+    if (h_mel_lens) CUDA_OK(cudaMemcpyAsync(h_mel_lens, mel_lens, B * 8, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    if (h_tmax) *h_tmax = tmax;
+    API_END(c)
+}
+
+int64_t masg_launch_count(masg_ctx* c, int reset) {
+    if (!c) return -1;
+    int64_t n = c->launches;
+    if (reset) c->launches = 0;
+    return n;
+}
+
+int masg_debug_tap(masg_ctx* c, void* stream, const char* name, float* dst, int64_t n_elems) {
+    API_BEGIN(c)
+    const float* src = nullptr; int64_t n = 0;
+    if (!strcmp(name, "encoder_out")) { src = c->tap_enc; n = (int64_t)c->B * c->L * 256; }
+    else if (!strcmp(name, "va_out")) { src = c->va_out; n = (int64_t)c->B * c->L * 256; }
+    else if (!strcmp(name, "lr_out")) { src = c->tap_lr; n = (int64_t)c->B * c->tap_T * 256; }
+    else if (!strcmp(name, "decoder_out")) { src = c->tap_dec; n = (int64_t)c->B * c->tap_T * 256; }
+    MASG_CHECK(src != nullptr, "unknown or unavailable tap '%s'", name);
+    MASG_CHECK(n_elems == n, "tap '%s' has %lld elements, caller asked for %lld", name, (long long)n, (long long)n_elems);
+    CUDA_OK(cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    API_END(c)
+}
+
+}  // extern "C"

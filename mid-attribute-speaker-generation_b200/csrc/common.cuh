@@ -1,0 +1,169 @@
+// Shared declarations for libmasg.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <map>
+#include <unordered_map>
+
+#include "../../include/masg.h"
+
+#define MASG_D 256          // encoder/decoder hidden
+#define MASG_NMEL 80
+#define MASG_DFF 1024
+
+typedef __nv_bfloat16 bf16;
+
+struct MasgError { std::string msg; };
+
+#define MASG_CHECK(cond, ...)                                                              \
+    do { if (!(cond)) { char _b[512]; snprintf(_b, sizeof(_b), __VA_ARGS__);                \
+         throw MasgError{std::string(_b) + " [" #cond "] at " __FILE__ ":" + std::to_string(__LINE__)}; } } while (0)
+#define CUDA_OK(call)                                                                      \
+    do { cudaError_t _e = (call); if (_e != cudaSuccess) {                                  \
+         throw MasgError{std::string("CUDA error: ") + cudaGetErrorString(_e) + " in " #call " at " __FILE__ ":" + std::to_string(__LINE__)}; } } while (0)
+
+// ---- device arena: grown on demand, never freed mid-stream (stream-ordered reuse by one ctx) ----
+struct Arena {
+    char* base = nullptr; size_t cap = 0, off = 0;
+    std::vector<char*> retired;
+    void reset() { off = 0; }
+    size_t mark() const { return off; }
+    void restore(size_t m) { off = m; }
+    void* alloc(size_t bytes);
+    template <typename T> T* get(size_t n) { return (T*)alloc(n * sizeof(T)); }
+    void release();
+};
+
+struct TensorRef { const float* ptr; std::vector<int64_t> shape; int64_t numel() const { int64_t n = 1; for (auto s : shape) n *= s; return n; } };
+
+// ---- generic row-GEMM / conv description shared by the fp32 SIMT kernel and the tcgen05 kernel ----
+// out[b, q*orow + ooff + n] = act( sum_{j<taps, c<Cin} X[b, q + off0 + j*tstep, c] * W[(j*Cin + c), n] + bias[n % bias_mod] )
+//                             (+ R1[...] + R2[...]) * out_scale
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2, ACT_LRELU = 3 };
+
+struct ConvDesc {
+    int Cin = 0, N = 0, taps = 1, off0 = 0, tstep = 1;
+    int bias_mod = 0;                 // 0 → N
+    long orow = 0, ooff = 0;          // output row stride / offset in elements (0 → N / 0)
+    const float* w32 = nullptr;       // [taps*Cin][N] fp32 (SIMT path)
+    const float* bias = nullptr;      // [bias_mod]
+    // tcgen05 path: bf16 weights, K-major [Npad][taps*Cin_pad]
+    const bf16* w16 = nullptr; int Cin_pad = 0, Npad = 0;
+    void* tmap_w = nullptr;           // CUtensorMap* (host copy, 128B)
+};
+
+struct ConvWeights {                  // owned storage for a ConvDesc
+    float* w32 = nullptr; float* bias = nullptr; bf16* w16 = nullptr;
+};
+
+struct FFTLayer {
+    ConvDesc qkv, fc, w1, w2;
+    const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+};
+struct Predictor {
+    ConvDesc c1, c2;
+    const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *lin_w; float lin_b;
+};
+
+struct masg_ctx {
+    int device = 0, precision = 0;
+    std::string err;
+    int64_t launches = 0;
+    Arena arena;                      // per-forward workspace
+    std::vector<void*> owned;         // repacked weights
+    std::map<std::string, TensorRef> fs2_t, hg_t;
+    bool fs2_ready = false, hg_ready = false;
+    // ---- FastSpeech2 ----
+    int n_enc = 0, n_dec = 0, max_seq_len = 1000;
+    const float *word_emb = nullptr, *accent_emb = nullptr, *enc_pos = nullptr, *dec_pos = nullptr;
+    float* pos_long = nullptr; int pos_long_n = 0;           // rebuilt table for len > max_seq_len
+    std::vector<FFTLayer> enc, dec;
+    Predictor pred[3];                                       // duration, pitch, energy
+    const float *pitch_bins = nullptr, *energy_bins = nullptr, *pitch_emb = nullptr, *energy_emb = nullptr;
+    ConvDesc mel_linear, postnet[5];
+    const float *gmm_pi_w, *gmm_pi_b, *gmm_sig_w, *gmm_sig_b, *gmm_mu_w, *gmm_mu_b;
+    // phase A → phase B state
+    int B = 0, L = 0; float* va_out = nullptr; float* d_rounded_dev = nullptr; int64_t* mel_lens_dev = nullptr;
+    const int64_t* src_lens_dev = nullptr;
+    float* tap_enc = nullptr; float* tap_lr = nullptr; float* tap_dec = nullptr; int tap_T = 0;
+    Arena arena_b;                    // phase-B / vocoder workspace (arena holds phase-A state)
+    int64_t* h_pinned = nullptr;      // pinned host scratch (T_max etc.)
+    void* io_buf = nullptr; size_t io_cap = 0;   // device staging of masg_synthesize_host
+    // ---- HiFi-GAN ----
+    ConvDesc hg_pre, hg_ups[4], hg_c1[12][3], hg_c2[12][3];
+    const float* hg_post_w = nullptr; float hg_post_b = 0.f;   // [7][32] fp32
+    int hg_up_rate[4] = {8, 8, 2, 2}, hg_up_k[4] = {16, 16, 4, 4}, hg_ch[5] = {512, 256, 128, 64, 32};
+    int hg_rk[3] = {3, 7, 11}, hg_rd[3] = {1, 3, 5};
+};
+
+// ------------------------------------------------------------------------------------------------
+// kernel launchers (each increments ctx->launches)
+// ------------------------------------------------------------------------------------------------
+struct ConvIO {
+    const float* X = nullptr; long x_bs = 0; int x_ld = 0; int Tin = 0;     // input rows [B][Tin][x_ld]
+    float* Y = nullptr; long y_bs = 0; long y_limit = 0;                    // output, valid elements per batch
+    int B = 1, Q = 0;                                                        // rows computed per batch
+    int in_act = ACT_NONE; float in_slope = 0.f;
+    int out_act = ACT_NONE; float out_slope = 0.f;
+    const float* R1 = nullptr; const float* R2 = nullptr; float out_scale = 1.f;
+};
+void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
+
+void launch_embed(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
+                  const float* wemb, const float* aemb, const float* pos, int B, int L, float* out);
+void launch_add_rowvec(masg_ctx* c, cudaStream_t s, float* x, const float* v, int B, int L, int C);   // x[b,l,:] += v[b,:]
+void launch_add_pos(masg_ctx* c, cudaStream_t s, float* x, const float* pos, int B, int T, int C);
+// y = LN(x (+res)) * g + b ; rows with t >= lens[b] are zeroed when lens != null
+void launch_layernorm(masg_ctx* c, cudaStream_t s, const float* x, const float* res, const float* g, const float* b,
+                      const int64_t* lens, int B, int T, float* y);
+// out[b,t] = (t < lens[b]) ? dot(x[b,t,:], w) + bias : 0
+void launch_rowdot_mask(masg_ctx* c, cudaStream_t s, const float* x, const float* w, float bias, const int64_t* lens,
+                        int B, int T, float scale, float* out);
+void launch_mask(masg_ctx* c, cudaStream_t s, const int64_t* lens, int B, int T, uint8_t* mask);
+void launch_bucket_add(masg_ctx* c, cudaStream_t s, const float* v, const float* bins, int nb, const float* table,
+                       int64_t rows, int C, float* x, int64_t* idx_out);
+void launch_duration(masg_ctx* c, cudaStream_t s, const float* log_d, float d_ctl, int64_t n, float* d);
+void launch_mel_lens(masg_ctx* c, cudaStream_t s, const float* d, int B, int L, int64_t* mel_lens, int64_t* tmax_out);
+void launch_length_regulate(masg_ctx* c, cudaStream_t s, const float* x, const float* d, int B, int L, int C, int T,
+                            const float* pos /*nullable, added to valid+pad rows*/, float* out, int64_t* mel_lens,
+                            uint8_t* mask);
+void launch_attention_f32(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out);
+void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int B, int C, int T, float* out_btc);
+void launch_conv_post(masg_ctx* c, cudaStream_t s, const float* x, const float* w, float bias, int B, long S,
+                      float in_slope, float* wav, int16_t* wav16);
+void launch_pos_table(masg_ctx* c, cudaStream_t s, int n, float* out);
+void launch_add2(masg_ctx* c, cudaStream_t s, const float* a, const float* b, float* out, int64_t n);
+void launch_gmm_params(masg_ctx* c, cudaStream_t s, const float* meta, int N, float* pi, float* mu, float* sigma);
+void launch_gmm_sample(masg_ctx* c, cudaStream_t s, const float* pi, const float* mu, const float* scale, int N, int Np,
+                       int K, int D, uint64_t seed, uint64_t offset, const int32_t* kin, const float* ein, float* out,
+                       int32_t* kout);
+void launch_gmm_interp_cost(masg_ctx* c, cudaStream_t s, const float* mu_a, const float* sig_a, const float* mu_b,
+                            const float* sig_b, int K, int D, double* cost);
+void launch_gmm_interp_comps(masg_ctx* c, cudaStream_t s, const float* mu_a, const float* sig_a, const float* mu_b,
+                             const float* sig_b, int K, int D, float t, float* comp_mu, float* comp_scale);
+void launch_gmm_bary(masg_ctx* c, cudaStream_t s, const float* mu, const float* sigma, const float* rate, int A, int K,
+                     int D, float* bmean, float* bstd);
+void launch_gmm_bary_assign(masg_ctx* c, cudaStream_t s, const float* mu, const float* sigma, const float* bmean,
+                            const float* bstd, int A, int K, int D, int nb, int32_t* assign);
+
+// repack helpers (device side)
+void launch_repack_conv_w(masg_ctx* c, cudaStream_t s, const float* w /*[Cout][Cin][k]*/, int Cout, int Cin, int k,
+                          const float* scale /*nullable per-Cout*/, float* out /*[k*Cin][ldn] at col0*/, int ldn, int col0);
+void launch_repack_convT_w(masg_ctx* c, cudaStream_t s, const float* w /*[Cin][Cout][k]*/, int Cin, int Cout, int k, int u,
+                           float* out /*[2*Cin][u*Cout]*/);
+void launch_weight_norm_fold(masg_ctx* c, cudaStream_t s, const float* v, const float* g, int n0, int inner, float* w);
+void launch_bn_fold(masg_ctx* c, cudaStream_t s, const float* gamma, const float* beta, const float* mean, const float* var,
+                    const float* conv_bias, int C, float* scale, float* bias);
+
+// fs2.cu / hifigan.cu / gmm.cu
+void fs2_commit(masg_ctx* c, cudaStream_t s);
+void hifigan_commit(masg_ctx* c, cudaStream_t s);
+void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
+                 const int64_t* src_lens, int B, int L, const float* spk, float p_ctl, float e_ctl, float d_ctl,
+                 const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded,
+                 int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax);
+void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, uint8_t* mel_mask);
+void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16);

@@ -1,0 +1,276 @@
+// FastSpeech2 inference orchestration (model/fastspeech2.py:187-303): weight repacking at commit and
+// the two-phase forward.  Host code only; every tensor op is a kernel from kernels_mem.cu /
+// conv_simt.cu (fp32 mode) or conv_tc.cu / attn_tc.cu (bf16 tcgen05 mode).
+#include "common.cuh"
+#include "tc.cuh"
+#include <cmath>
+
+void* Arena::alloc(size_t bytes) {
+    bytes = (bytes + 255) & ~size_t(255);
+    if (off + bytes > cap) {
+        // grow: new block sized for everything allocated so far plus this request; old block is retired
+        // (kept alive until release(): kernels already enqueued on the stream may still use it).
+        size_t ncap = cap ? cap : (size_t)64 << 20;
+        while (ncap < off + bytes) ncap *= 2;
+        char* nb = nullptr;
+        CUDA_OK(cudaMalloc(&nb, ncap));
+        // Pointers handed out earlier keep pointing into the retired block, which stays allocated (and keeps
+        // its contents) until release(); only new requests come from the new block.
+        if (base) retired.push_back(base);
+        base = nb; cap = ncap;
+    }
+    void* p = base + off;
+    off += bytes;
+    return p;
+}
+void Arena::release() {
+    for (char* r : retired) cudaFree(r);
+    retired.clear();
+    if (base) cudaFree(base);
+    base = nullptr; cap = off = 0;
+}
+
+static const TensorRef& T_(std::map<std::string, TensorRef>& m, const std::string& key, std::initializer_list<int64_t> shape) {
+    auto it = m.find(key);
+    MASG_CHECK(it != m.end(), "missing state_dict tensor '%s'", key.c_str());
+    const TensorRef& t = it->second;
+    std::vector<int64_t> want(shape);
+    bool ok = want.size() == t.shape.size();
+    for (size_t i = 0; ok && i < want.size(); ++i) ok = want[i] < 0 || want[i] == t.shape[i];
+    MASG_CHECK(ok, "tensor '%s' has an unsupported shape (unsupported configuration; no fallback)", key.c_str());
+    return t;
+}
+
+template <typename T> static T* dev_alloc(masg_ctx* c, size_t n) {
+    T* p = nullptr;
+    CUDA_OK(cudaMalloc(&p, n * sizeof(T)));
+    c->owned.push_back(p);
+    return p;
+}
+
+// Build a ConvDesc from a Conv1d/Linear weight [Cout][Cin][k] (+ optional per-Cout scale and replacement bias)
+ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
+                   const float* scale, const float* bias_override) {
+    ConvDesc d;
+    d.Cin = Cin; d.N = Cout; d.taps = k; d.off0 = -pad; d.tstep = dil; d.bias_mod = Cout; d.orow = Cout; d.ooff = 0;
+    float* w32 = dev_alloc<float>(c, (size_t)k * Cin * Cout);
+    launch_repack_conv_w(c, s, w, Cout, Cin, k, scale, w32, Cout, 0);
+    d.w32 = w32;
+    d.bias = bias_override ? bias_override : bias;
+    if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+    return d;
+}
+
+void fs2_commit(masg_ctx* c, cudaStream_t s) {
+    auto& m = c->fs2_t;
+    c->fs2_ready = false;
+    c->enc.clear(); c->dec.clear();
+    c->word_emb = T_(m, "encoder.src_word_emb.weight", {-1, 256}).ptr;
+    c->accent_emb = T_(m, "encoder.src_accent_emb.weight", {-1, 256}).ptr;
+    const TensorRef& pe = T_(m, "encoder.position_enc", {1, -1, 256});
+    c->enc_pos = pe.ptr; c->max_seq_len = (int)pe.shape[1] - 1;
+    c->dec_pos = T_(m, "decoder.position_enc", {1, pe.shape[1], 256}).ptr;
+    for (int part = 0; part < 2; ++part) {
+        const char* pn = part ? "decoder" : "encoder";
+        auto& vec = part ? c->dec : c->enc;
+        for (int n = 0;; ++n) {
+            std::string p = std::string(pn) + ".layer_stack." + std::to_string(n) + ".";
+            if (!m.count(p + "slf_attn.fc.weight")) break;
+            FFTLayer L;
+            // QKV: three Linear(256,256) concatenated along N (transformer/SubLayers.py:39-41)
+            {
+                ConvDesc d; d.Cin = 256; d.N = 768; d.taps = 1; d.off0 = 0; d.tstep = 1; d.bias_mod = 768; d.orow = 768;
+                float* w32 = dev_alloc<float>(c, 256 * 768); float* b = dev_alloc<float>(c, 768);
+                const char* nm[3] = {"w_qs", "w_ks", "w_vs"};
+                for (int i = 0; i < 3; ++i) {
+                    launch_repack_conv_w(c, s, T_(m, p + "slf_attn." + nm[i] + ".weight", {256, 256}).ptr, 256, 256, 1, nullptr, w32, 768, 256 * i);
+                    CUDA_OK(cudaMemcpyAsync(b + 256 * i, T_(m, p + "slf_attn." + nm[i] + ".bias", {256}).ptr, 256 * 4, cudaMemcpyDeviceToDevice, s));
+                }
+                d.w32 = w32; d.bias = b;
+                if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+                L.qkv = d;
+            }
+            L.fc = make_conv(c, s, T_(m, p + "slf_attn.fc.weight", {256, 256}).ptr, T_(m, p + "slf_attn.fc.bias", {256}).ptr, 256, 256, 1, 0, 1, nullptr, nullptr);
+            L.ln1_g = T_(m, p + "slf_attn.layer_norm.weight", {256}).ptr; L.ln1_b = T_(m, p + "slf_attn.layer_norm.bias", {256}).ptr;
+            const TensorRef& w1 = T_(m, p + "pos_ffn.w_1.weight", {1024, 256, -1});
+            int k1 = (int)w1.shape[2];
+            L.w1 = make_conv(c, s, w1.ptr, T_(m, p + "pos_ffn.w_1.bias", {1024}).ptr, 1024, 256, k1, (k1 - 1) / 2, 1, nullptr, nullptr);
+            const TensorRef& w2 = T_(m, p + "pos_ffn.w_2.weight", {256, 1024, -1});
+            int k2 = (int)w2.shape[2];
+            L.w2 = make_conv(c, s, w2.ptr, T_(m, p + "pos_ffn.w_2.bias", {256}).ptr, 256, 1024, k2, (k2 - 1) / 2, 1, nullptr, nullptr);
+            L.ln2_g = T_(m, p + "pos_ffn.layer_norm.weight", {256}).ptr; L.ln2_b = T_(m, p + "pos_ffn.layer_norm.bias", {256}).ptr;
+            vec.push_back(L);
+        }
+    }
+    MASG_CHECK(!c->enc.empty() && !c->dec.empty(), "no encoder/decoder layers registered");
+    const char* pnames[3] = {"duration", "pitch", "energy"};
+    std::vector<float> lin_b(3);
+    for (int i = 0; i < 3; ++i) {
+        std::string p = std::string("variance_adaptor.") + pnames[i] + "_predictor.";
+        Predictor& P = c->pred[i];
+        const TensorRef& w1 = T_(m, p + "conv_layer.conv1d_1.conv.weight", {256, 256, 3});
+        P.c1 = make_conv(c, s, w1.ptr, T_(m, p + "conv_layer.conv1d_1.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr);
+        P.c2 = make_conv(c, s, T_(m, p + "conv_layer.conv1d_2.conv.weight", {256, 256, 3}).ptr,
+                         T_(m, p + "conv_layer.conv1d_2.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr);   // padding=1 (modules.py:229-231)
+        P.ln1_g = T_(m, p + "conv_layer.layer_norm_1.weight", {256}).ptr; P.ln1_b = T_(m, p + "conv_layer.layer_norm_1.bias", {256}).ptr;
+        P.ln2_g = T_(m, p + "conv_layer.layer_norm_2.weight", {256}).ptr; P.ln2_b = T_(m, p + "conv_layer.layer_norm_2.bias", {256}).ptr;
+        P.lin_w = T_(m, p + "linear_layer.weight", {1, 256}).ptr;
+        CUDA_OK(cudaMemcpyAsync(&lin_b[i], T_(m, p + "linear_layer.bias", {1}).ptr, 4, cudaMemcpyDeviceToHost, s));
+    }
+    const TensorRef& pb = T_(m, "variance_adaptor.pitch_bins", {255});
+    c->pitch_bins = pb.ptr;
+    c->energy_bins = T_(m, "variance_adaptor.energy_bins", {255}).ptr;
+    c->pitch_emb = T_(m, "variance_adaptor.pitch_embedding.weight", {256, 256}).ptr;
+    c->energy_emb = T_(m, "variance_adaptor.energy_embedding.weight", {256, 256}).ptr;
+    c->mel_linear = make_conv(c, s, T_(m, "mel_linear.weight", {80, 256}).ptr, T_(m, "mel_linear.bias", {80}).ptr, 80, 256, 1, 0, 1, nullptr, nullptr);
+    int chans[6] = {80, 512, 512, 512, 512, 80};
+    for (int i = 0; i < 5; ++i) {
+        std::string p = "postnet.convolutions." + std::to_string(i) + ".";
+        int ci = chans[i], co = chans[i + 1];
+        float* scale = dev_alloc<float>(c, co); float* fb = dev_alloc<float>(c, co);
+        launch_bn_fold(c, s, T_(m, p + "1.weight", {co}).ptr, T_(m, p + "1.bias", {co}).ptr, T_(m, p + "1.running_mean", {co}).ptr,
+                       T_(m, p + "1.running_var", {co}).ptr, T_(m, p + "0.conv.bias", {co}).ptr, co, scale, fb);
+        c->postnet[i] = make_conv(c, s, T_(m, p + "0.conv.weight", {co, ci, 5}).ptr, nullptr, co, ci, 5, 2, 1, scale, fb);
+    }
+    c->gmm_pi_w = T_(m, "speaker_enc.pi_linear.0.weight", {3, 4}).ptr; c->gmm_pi_b = T_(m, "speaker_enc.pi_linear.0.bias", {3}).ptr;
+    c->gmm_sig_w = T_(m, "speaker_enc.sigma_linear.0.weight", {768, 4}).ptr; c->gmm_sig_b = T_(m, "speaker_enc.sigma_linear.0.bias", {768}).ptr;
+    c->gmm_mu_w = T_(m, "speaker_enc.mu_linear.weight", {768, 4}).ptr; c->gmm_mu_b = T_(m, "speaker_enc.mu_linear.bias", {768}).ptr;
+    CUDA_OK(cudaStreamSynchronize(s));
+    for (int i = 0; i < 3; ++i) c->pred[i].lin_b = lin_b[i];
+    c->fs2_ready = true;
+}
+
+static const float* pos_table(masg_ctx* c, cudaStream_t s, bool decoder, int n) {
+    if (n <= c->max_seq_len) return decoder ? c->dec_pos : c->enc_pos;
+    if (n > c->pos_long_n) {                      // eval-mode rebuild for long sequences (Models.py:86-98,157-164)
+        int cap = n + 1024;
+        float* p = nullptr;
+        CUDA_OK(cudaMalloc(&p, (size_t)cap * 256 * sizeof(float)));
+        c->owned.push_back(p);
+        launch_pos_table(c, s, cap, p);
+        c->pos_long = p; c->pos_long_n = cap;
+    }
+    return c->pos_long;
+}
+
+// ---- fp32 building blocks ---------------------------------------------------------------------
+static void conv32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* X, int x_ld, int B, int T, float* Y,
+                   int out_act = ACT_NONE, const float* R1 = nullptr) {
+    ConvIO io;
+    io.X = X; io.x_ld = x_ld; io.x_bs = (long)T * x_ld; io.Tin = T;
+    io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
+    launch_conv_f32(c, s, d, io);
+}
+
+static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S) {
+    // in place on x: every consumer of the old x has been enqueued before the LayerNorm overwrites it
+    size_t rows = (size_t)B * S, mk = ar.mark();
+    float* qkv = ar.get<float>(rows * 768);
+    float* att = ar.get<float>(rows * 256);
+    float* y = ar.get<float>(rows * 256);
+    conv32(c, s, L.qkv, x, 256, B, S, qkv);
+    launch_attention_f32(c, s, qkv, lens, B, S, att);
+    conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                         // fc(out) + residual
+    launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x);        // LN + masked_fill (Layers.py:25)
+    ar.restore(mk);
+    float* h = ar.get<float>(rows * 1024);
+    float* y2 = ar.get<float>(rows * 256);
+    conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
+    conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
+    launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x);       // LN + masked_fill (Layers.py:28)
+    ar.restore(mk);
+}
+
+static void predictor_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const Predictor& P, const float* x, const int64_t* lens,
+                          int B, int L, float scale, float* out) {
+    size_t rows = (size_t)B * L, mk = ar.mark();
+    float* a = ar.get<float>(rows * 256); float* b = ar.get<float>(rows * 256);
+    conv32(c, s, P.c1, x, 256, B, L, a, ACT_RELU);
+    launch_layernorm(c, s, a, nullptr, P.ln1_g, P.ln1_b, nullptr, B, L, b);
+    conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU);
+    launch_layernorm(c, s, a, nullptr, P.ln2_g, P.ln2_b, nullptr, B, L, b);
+    launch_rowdot_mask(c, s, b, P.lin_w, P.lin_b, lens, B, L, scale, out);
+    ar.restore(mk);
+}
+
+void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
+                 const int64_t* src_lens, int B, int L, const float* spk, float p_ctl, float e_ctl, float d_ctl,
+                 const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded,
+                 int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax) {
+    MASG_CHECK(c->fs2_ready, "FastSpeech2 weights not committed (call masg_fs2_commit)");
+    MASG_CHECK(B > 0 && L > 0, "empty batch B=%d L=%d", B, L);
+    MASG_CHECK(accents != nullptr, "accents is required (transformer/Models.py:101 would raise on None)");
+    (void)e_ctl;   // accepted and ignored: energy is scaled by p_control (model/modules.py:123-125)
+    Arena& ar = c->arena;
+    ar.reset();
+    size_t rows = (size_t)B * L;
+    // persistent phase-A → phase-B state first
+    c->va_out = ar.get<float>(rows * 256);
+    c->d_rounded_dev = ar.get<float>(rows);
+    c->mel_lens_dev = ar.get<int64_t>(B + 1);
+    c->tap_enc = ar.get<float>(rows * 256);
+    c->B = B; c->L = L; c->src_lens_dev = src_lens;
+    if (src_mask) launch_mask(c, s, src_lens, B, L, src_mask);
+    const float* pos = pos_table(c, s, false, L);
+    if (c->precision == MASG_PREC_BF16) {
+        tc_fs2_encoder(c, s, ar, texts, accents, acc1d, src_lens, B, L, pos, c->tap_enc);
+    } else {
+        float* x = ar.get<float>(rows * 256);
+        launch_embed(c, s, texts, accents, acc1d, c->word_emb, c->accent_emb, pos, B, L, x);
+        for (auto& Lr : c->enc) fft_block_f32(c, s, ar, Lr, x, src_lens, B, L);
+        CUDA_OK(cudaMemcpyAsync(c->tap_enc, x, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    }
+    float* x = c->va_out;
+    CUDA_OK(cudaMemcpyAsync(x, c->tap_enc, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    launch_add_rowvec(c, s, x, spk, B, L, 256);                                 // pads too (fastspeech2.py:215-218)
+    auto predict = [&](int which, float scale, float* out) {
+        if (c->precision == MASG_PREC_BF16) tc_predictor(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
+        else predictor_f32(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
+    };
+    predict(0, 1.0f, log_d);
+    predict(1, p_ctl, pitch);
+    launch_bucket_add(c, s, pitch, c->pitch_bins, 255, c->pitch_emb, (int64_t)rows, 256, x, nullptr);
+    predict(2, p_ctl, energy);                                                  // p_control, sic (modules.py:123-125)
+    launch_bucket_add(c, s, energy, c->energy_bins, 255, c->energy_emb, (int64_t)rows, 256, x, nullptr);
+    if (d_target) CUDA_OK(cudaMemcpyAsync(c->d_rounded_dev, d_target, rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    else launch_duration(c, s, log_d, d_ctl, (int64_t)rows, c->d_rounded_dev);
+    if (d_rounded) CUDA_OK(cudaMemcpyAsync(d_rounded, c->d_rounded_dev, rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    launch_mel_lens(c, s, c->d_rounded_dev, B, L, c->mel_lens_dev, c->mel_lens_dev + B);
+    if (mel_lens) CUDA_OK(cudaMemcpyAsync(mel_lens, c->mel_lens_dev, B * sizeof(int64_t), cudaMemcpyDeviceToDevice, s));
+    if (h_tmax) {
+        CUDA_OK(cudaMemcpyAsync(c->h_pinned, c->mel_lens_dev + B, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));                                      // the single documented sync
+        *h_tmax = c->h_pinned[0];
+    }
+}
+
+void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, uint8_t* mel_mask) {
+    MASG_CHECK(c->fs2_ready && c->va_out, "phase B called without a preceding phase A");
+    MASG_CHECK(T > 0, "T=%d: no frames to synthesise (all durations zero)", T);
+    int B = c->B, L = c->L;
+    Arena& ar = c->arena_b;
+    ar.reset();
+    size_t rows = (size_t)B * T;
+    c->tap_lr = ar.get<float>(rows * 256);
+    c->tap_dec = ar.get<float>(rows * 256);
+    c->tap_T = T;
+    launch_length_regulate(c, s, c->va_out, c->d_rounded_dev, B, L, 256, T, nullptr, c->tap_lr, nullptr, mel_mask);
+    const float* pos = pos_table(c, s, true, T);
+    const int64_t* lens = c->mel_lens_dev;
+    if (c->precision == MASG_PREC_BF16) {
+        tc_fs2_decoder_mel(c, s, ar, c->tap_lr, pos, lens, B, T, c->tap_dec, mel, post);
+        return;
+    }
+    float* x = ar.get<float>(rows * 256);
+    CUDA_OK(cudaMemcpyAsync(x, c->tap_lr, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    launch_add_pos(c, s, x, pos, B, T, 256);
+    for (auto& Lr : c->dec) fft_block_f32(c, s, ar, Lr, x, lens, B, T);
+    CUDA_OK(cudaMemcpyAsync(c->tap_dec, x, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    conv32(c, s, c->mel_linear, x, 256, B, T, mel);                             // pads become bias (fastspeech2.py:242)
+    float* h1 = ar.get<float>(rows * 512); float* h2 = ar.get<float>(rows * 512);
+    conv32(c, s, c->postnet[0], mel, 80, B, T, h1, ACT_TANH);
+    conv32(c, s, c->postnet[1], h1, 512, B, T, h2, ACT_TANH);
+    conv32(c, s, c->postnet[2], h2, 512, B, T, h1, ACT_TANH);
+    conv32(c, s, c->postnet[3], h1, 512, B, T, h2, ACT_TANH);
+    conv32(c, s, c->postnet[4], h2, 512, B, T, post, ACT_NONE, mel);            // + residual (fastspeech2.py:244)
+}

@@ -1,0 +1,136 @@
+// HiFi-GAN V1 generator (hifigan/models.py:112-174): weight-norm folding + repacking at commit, and
+// the forward graph.  Activations are channels-last [B, S, C]; ConvTranspose1d runs as a 2-tap
+// phase-decomposed row GEMM (see conv_simt.cu header); leaky-relu is applied on operand load, the
+// residual add, the MRF sum and the 1/3 scale are folded into conv epilogues.
+#include "common.cuh"
+#include "tc.cuh"
+
+ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
+                   const float* scale, const float* bias_override);
+
+template <typename T> static T* dev_alloc(masg_ctx* c, size_t n) {
+    T* p = nullptr;
+    CUDA_OK(cudaMalloc(&p, n * sizeof(T)));
+    c->owned.push_back(p);
+    return p;
+}
+
+// folded fp32 weight for `name` ([n0][...]): accepts weight_g/weight_v (checkpoint layout) or weight
+static const float* folded_weight(masg_ctx* c, cudaStream_t s, const std::string& name, std::vector<int64_t>& shape) {
+    auto& m = c->hg_t;
+    auto iw = m.find(name + ".weight");
+    if (iw != m.end()) { shape = iw->second.shape; return iw->second.ptr; }
+    auto iv = m.find(name + ".weight_v"), ig = m.find(name + ".weight_g");
+    MASG_CHECK(iv != m.end() && ig != m.end(), "missing HiFi-GAN tensor '%s.weight' (or weight_g/weight_v)", name.c_str());
+    shape = iv->second.shape;
+    MASG_CHECK(shape.size() == 3 && ig->second.numel() == shape[0], "bad weight-norm shapes for '%s'", name.c_str());
+    int n0 = (int)shape[0], inner = (int)(shape[1] * shape[2]);
+    float* w = dev_alloc<float>(c, (size_t)n0 * inner);
+    launch_weight_norm_fold(c, s, iv->second.ptr, ig->second.ptr, n0, inner, w);
+    return w;
+}
+static const float* bias_of(masg_ctx* c, const std::string& name, int n) {
+    auto it = c->hg_t.find(name + ".bias");
+    MASG_CHECK(it != c->hg_t.end() && it->second.numel() == n, "missing/bad HiFi-GAN bias '%s.bias'", name.c_str());
+    return it->second.ptr;
+}
+
+void hifigan_commit(masg_ctx* c, cudaStream_t s) {
+    c->hg_ready = false;
+    std::vector<int64_t> sh;
+    const float* w = folded_weight(c, s, "conv_pre", sh);
+    MASG_CHECK(sh[0] == 512 && sh[1] == 80 && sh[2] == 7, "conv_pre must be (512,80,7): unsupported generator config");
+    c->hg_pre = make_conv(c, s, w, bias_of(c, "conv_pre", 512), 512, 80, 7, 3, 1, nullptr, nullptr);
+    for (int i = 0; i < 4; ++i) {
+        std::string name = "ups." + std::to_string(i);
+        int cin = c->hg_ch[i], cout = c->hg_ch[i + 1], k = c->hg_up_k[i], u = c->hg_up_rate[i];
+        w = folded_weight(c, s, name, sh);
+        MASG_CHECK(sh[0] == cin && sh[1] == cout && sh[2] == k && k == 2 * u, "%s must be (%d,%d,%d) with k = 2*stride", name.c_str(), cin, cout, k);
+        ConvDesc d;
+        d.Cin = cin; d.N = u * cout; d.taps = 2; d.off0 = 0; d.tstep = -1; d.bias_mod = cout;
+        d.orow = (long)u * cout; d.ooff = -(long)((k - u) / 2) * cout;
+        float* w32 = dev_alloc<float>(c, (size_t)2 * cin * u * cout);
+        launch_repack_convT_w(c, s, w, cin, cout, k, u, w32);
+        d.w32 = w32; d.bias = bias_of(c, name, cout);
+        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+        c->hg_ups[i] = d;
+        for (int j = 0; j < 3; ++j) {
+            int rb = i * 3 + j, kk = c->hg_rk[j];
+            for (int mth = 0; mth < 3; ++mth) {
+                int dil = c->hg_rd[mth];
+                std::string n1 = "resblocks." + std::to_string(rb) + ".convs1." + std::to_string(mth);
+                std::string n2 = "resblocks." + std::to_string(rb) + ".convs2." + std::to_string(mth);
+                w = folded_weight(c, s, n1, sh);
+                MASG_CHECK(sh[0] == cout && sh[1] == cout && sh[2] == kk, "%s has an unsupported shape", n1.c_str());
+                c->hg_c1[rb][mth] = make_conv(c, s, w, bias_of(c, n1, cout), cout, cout, kk, (kk * dil - dil) / 2, dil, nullptr, nullptr);
+                w = folded_weight(c, s, n2, sh);
+                MASG_CHECK(sh[0] == cout && sh[1] == cout && sh[2] == kk, "%s has an unsupported shape", n2.c_str());
+                c->hg_c2[rb][mth] = make_conv(c, s, w, bias_of(c, n2, cout), cout, cout, kk, (kk - 1) / 2, 1, nullptr, nullptr);
+            }
+        }
+    }
+    w = folded_weight(c, s, "conv_post", sh);
+    MASG_CHECK(sh[0] == 1 && sh[1] == 32 && sh[2] == 7, "conv_post must be (1,32,7)");
+    float* pw = dev_alloc<float>(c, 7 * 32);
+    launch_repack_conv_w(c, s, w, 1, 32, 7, nullptr, pw, 1, 0);               // → [7][32]
+    c->hg_post_w = pw;
+    float pb = 0.f;
+    CUDA_OK(cudaMemcpyAsync(&pb, bias_of(c, "conv_post", 1), 4, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    c->hg_post_b = pb;
+    c->hg_ready = true;
+}
+
+static void convS(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* X, int B, long Sin, float* Y, long Sout, int Cout,
+                  int in_act, float in_slope, const float* R1, const float* R2, float out_scale, int Q) {
+    ConvIO io;
+    io.X = X; io.x_ld = d.Cin; io.x_bs = Sin * d.Cin; io.Tin = (int)Sin;
+    io.Y = Y; io.y_bs = Sout * Cout; io.y_limit = Sout * Cout; io.B = B; io.Q = Q;
+    io.in_act = in_act; io.in_slope = in_slope; io.R1 = R1; io.R2 = R2; io.out_scale = out_scale;
+    launch_conv_f32(c, s, d, io);
+}
+
+void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16) {
+    MASG_CHECK(c->hg_ready, "HiFi-GAN weights not committed (call masg_hifigan_commit)");
+    MASG_CHECK(B > 0 && T > 0, "empty vocoder input B=%d T=%d", B, T);
+    Arena& ar = c->arena_b;
+    ar.reset();
+    const float* melT = mel;
+    if (!cl) {
+        float* t = ar.get<float>((size_t)B * T * 80);
+        launch_transpose_mel(c, s, mel, B, 80, T, t);
+        melT = t;
+    }
+    if (c->precision == MASG_PREC_BF16) { tc_hifigan_forward(c, s, ar, melT, B, T, wav, w16); return; }
+    long S = T;
+    float* x = ar.get<float>((size_t)B * S * 512);
+    convS(c, s, c->hg_pre, melT, B, S, x, S, 512, ACT_NONE, 0.f, nullptr, nullptr, 1.f, (int)S);
+    for (int i = 0; i < 4; ++i) {
+        int u = c->hg_up_rate[i], C = c->hg_ch[i + 1];
+        long So = S * u;
+        size_t n = (size_t)B * So * C;
+        float* xu = ar.get<float>(n); float* xs = ar.get<float>(n); float* h = ar.get<float>(n);
+        float* ya = ar.get<float>(n); float* yb = ar.get<float>(n);
+        // x = ups[i](leaky_relu(x, 0.1))   (models.py:152-153)
+        convS(c, s, c->hg_ups[i], x, B, S, xu, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)S + 1);
+        for (int j = 0; j < 3; ++j) {
+            int rb = i * 3 + j;
+            const float* y = xu;
+            for (int m = 0; m < 3; ++m) {
+                // xt = c2(lrelu(c1(lrelu(y)))); y = xt + y   (models.py:96-103)
+                convS(c, s, c->hg_c1[rb][m], y, B, So, h, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)So);
+                if (m < 2) {
+                    float* yn = (y == ya) ? yb : ya;
+                    convS(c, s, c->hg_c2[rb][m], h, B, So, yn, So, C, ACT_LRELU, 0.1f, y, nullptr, 1.f, (int)So);
+                    y = yn;
+                } else {
+                    // last pair of the block: fold the MRF sum (xs += block) and, on the last block, the /3 (models.py:155-160)
+                    convS(c, s, c->hg_c2[rb][m], h, B, So, xs, So, C, ACT_LRELU, 0.1f, y, j > 0 ? xs : nullptr,
+                          j == 2 ? (1.0f / 3.0f) : 1.f, (int)So);
+                }
+            }
+        }
+        x = xs; S = So;
+    }
+    launch_conv_post(c, s, x, c->hg_post_w, c->hg_post_b, B, S, 0.01f, wav, w16);   // F.leaky_relu default slope (models.py:161)
+}

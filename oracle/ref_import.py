@@ -1,0 +1,118 @@
+"""Import the *unmodified* reference (/root/reference) read-only, on CPU, with the five absent
+third-party modules stubbed.  Exists only in the build container: nothing run
+on the GPU box may call this (``available()`` is False there).
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).
+"""
+import json
+import os
+import shutil
+import sys
+import tempfile
+import types
+
+REF_ROOT = os.environ.get("MASG_REFERENCE_ROOT", "/root/reference")
+_CFG_REL = "config/JVS-VCTK_langemb_configs/JVS-VCTK_1"
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REF_ROOT, "model", "fastspeech2.py"))
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    for k, v in attrs.items():
+        setattr(m, k, v)
+    sys.modules.setdefault(name, m)
+    return sys.modules[name]
+
+
+def install_stubs(emd=None):
+    """Stub modules the reference imports but this image lacks.  None is touched by inference
+    maths except ``ot.emd`` (model/distributions.py:22), which is bound to the oracle's exact
+    transportation solver (POT is un-vendored and unpinned: absent from requirements.txt)."""
+    if emd is None:
+        from .restate import emd_exact as emd
+    ot = _stub("ot")
+    ot.emd = lambda a, b, M: emd(a, b, M)
+    mpl = _stub("matplotlib", use=lambda *a, **k: None)
+    plt = _stub("matplotlib.pyplot")
+    mpl.pyplot = plt
+    _stub("unidecode", unidecode=lambda s: s)
+    _stub("inflect", engine=lambda: None)
+    _stub("Multilingual-Speaker-Encoder-with-Domain-Adaptation", SpeechEmbedder=object, GE2ELoss=object)
+
+
+_loaded = {}
+
+
+def load():
+    """Returns a namespace with the reference classes (FastSpeech2, Generator, AttrDict,
+    InterpolateGMM, BarycenterGMM, get_mask_from_lengths)."""
+    if _loaded:
+        return _loaded["ns"]
+    if not available():
+        raise RuntimeError("reference tree not present at %s" % REF_ROOT)
+    install_stubs()
+    if REF_ROOT not in sys.path:
+        sys.path.insert(0, REF_ROOT)
+    import model as ref_model                     # noqa: model/__init__.py
+    import hifigan as ref_hifigan                 # noqa
+    from model import distributions as ref_dist  # noqa
+    from utils import tools as ref_tools          # noqa
+    ns = types.SimpleNamespace(
+        FastSpeech2=ref_model.FastSpeech2,
+        Generator=ref_hifigan.Generator,
+        AttrDict=ref_hifigan.AttrDict,
+        InterpolateGMM=ref_dist.InterpolateGMM,
+        BarycenterGMM=ref_dist.BarycenterGMM,
+        get_mask_from_lengths=ref_tools.get_mask_from_lengths,
+        vocoder_infer=__import__("utils.model", fromlist=["vocoder_infer"]).vocoder_infer,
+        root=REF_ROOT,
+    )
+    _loaded["ns"] = ns
+    return ns
+
+
+def load_configs():
+    import yaml
+    d = os.path.join(REF_ROOT, _CFG_REL)
+    pre = yaml.load(open(os.path.join(d, "preprocess.yaml")), Loader=yaml.FullLoader)
+    mod = yaml.load(open(os.path.join(d, "model.yaml")), Loader=yaml.FullLoader)
+    return pre, mod
+
+
+def hifigan_config():
+    return json.load(open(os.path.join(REF_ROOT, "hifigan", "config.json")))
+
+
+def build_fs2(state_dict, speakers_json, stats_json):
+    """Reference FastSpeech2 with a fabricated config dir (the shipped speakers.json/stats.json are
+    0-byte files) and the given weights; eval mode, CPU."""
+    ns = load()
+    pre, mod = load_configs()
+    tmp = tempfile.mkdtemp(prefix="masg_cfg_")
+    try:
+        json.dump(speakers_json, open(os.path.join(tmp, "speakers.json"), "w"))
+        json.dump(stats_json, open(os.path.join(tmp, "stats.json"), "w"))
+        m = ns.FastSpeech2(pre, mod, tmp)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    missing, unexpected = m.load_state_dict(state_dict, strict=False)
+    bad = [k for k in missing if "num_batches_tracked" not in k]
+    assert not bad and not unexpected, (bad, unexpected)
+    return m.eval()
+
+
+def build_hifigan(state_dict_weight_normed):
+    """Reference generator loaded the way utils/model.py:61-69 does: load weight-normed keys,
+    eval(), remove_weight_norm()."""
+    import contextlib
+    import io
+    ns = load()
+    g = ns.Generator(ns.AttrDict(hifigan_config()))
+    g.load_state_dict(state_dict_weight_normed)
+    g.eval()
+    with contextlib.redirect_stdout(io.StringIO()):
+        g.remove_weight_norm()
+    return g

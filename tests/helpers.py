@@ -1,0 +1,63 @@
+"""Shared test helpers: build the drop-in modules on the GPU from seeded weights, run the oracle."""
+import json
+import os
+import tempfile
+
+import numpy as np
+import torch
+
+import masg_b200  # noqa: F401
+from masg_b200 import synthetic as syn
+
+_cfg_dir = None
+
+
+def config_dir():
+    """Fabricated config dir (the reference's speakers.json/stats.json are 0-byte files)."""
+    global _cfg_dir
+    if _cfg_dir is None:
+        _cfg_dir = tempfile.mkdtemp(prefix="masg_cfg_")
+        json.dump(syn.speakers_json(), open(os.path.join(_cfg_dir, "speakers.json"), "w"))
+        json.dump(syn.STATS_JSON, open(os.path.join(_cfg_dir, "stats.json"), "w"))
+    return _cfg_dir
+
+
+_models = {}
+
+
+def fs2_on_gpu(seed, duration_mode, precision):
+    from masg_b200.fastspeech2 import FastSpeech2
+    key = ("fs2", seed, duration_mode, precision)
+    if key not in _models:
+        sd = syn.make_fs2_state_dict(seed=seed, duration_mode=duration_mode)
+        m = FastSpeech2(syn.PREPROCESS_CONFIG, syn.MODEL_CONFIG, config_dir(), precision=precision)
+        m.load_state_dict(sd)
+        m.eval().to("cuda:0")
+        _models[key] = (m, sd)
+    return _models[key]
+
+
+def hifigan_on_gpu(seed, precision):
+    from masg_b200.hifigan import Generator, AttrDict
+    key = ("hg", seed, precision)
+    if key not in _models:
+        sd = syn.make_hifigan_state_dict(seed=seed)
+        g = Generator(AttrDict(syn.HIFIGAN_CONFIG), precision=precision)
+        g.load_state_dict(sd)
+        g.eval()
+        import contextlib, io
+        with contextlib.redirect_stdout(io.StringIO()):
+            g.remove_weight_norm()
+        g.to("cuda:0")
+        _models[key] = (g, sd)
+    return _models[key]
+
+
+def snr_db(ref, out):
+    ref = np.asarray(ref, dtype=np.float64)
+    out = np.asarray(out, dtype=np.float64)
+    return 10.0 * np.log10((ref ** 2).sum() / max(((ref - out) ** 2).sum(), 1e-30))
+
+
+def to_gpu(batch):
+    return {k: (v.to("cuda:0") if torch.is_tensor(v) else v) for k, v in batch.items()}

@@ -1,0 +1,352 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI
+(ctypes → libmasg.so), against the CPU oracle on the same seeded inputs and weights, against the
+reference-generated golden fixtures, and — at BASELINE.json's full sizes — through size-independent
+properties.  Tolerances are the ones BASELINE.json's north_star states:
+  durations / LengthRegulator / bucketize / masks: bit-exact
+  mel: max-abs <= 1e-4 (fp32 mode), <= 1e-2 (bf16 tcgen05 mode)
+  waveform: SNR >= 30 dB
+"""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import masg_b200  # noqa: F401
+from masg_b200 import synthetic as syn
+from oracle import restate
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+MEL_TOL = {"fp32": 1e-4, "bf16": 1e-2}
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from masg_b200 import _lib
+    return _lib.default_context(DEV, "fp32")
+
+
+def P(t):
+    from masg_b200 import _lib
+    return _lib.ptr(t)
+
+
+# ------------------------------------------------------------------------------------------------
+# bit-exact integer / index kernels
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("B,L,C", [(3, 7, 8), (1, 1, 256), (64, 200, 256), (16, 1000, 256), (5, 33, 64)])
+def test_length_regulator_bit_exact(ctx, B, L, C):
+    g = torch.Generator().manual_seed(B * 1000 + L)
+    x = torch.randn(B, L, C, generator=g)
+    d = torch.round(torch.rand(B, L, generator=g) * 6) * (1.3 if L != 200 else 1.0)    # fractional products, zeros
+    d[:, ::5] = 0.0
+    if B > 2:
+        d[1] = 0.0                                                                    # an all-pad utterance
+    want, want_len = restate.length_regulate(x, d)
+    T = want.shape[1]
+    if T == 0:
+        pytest.skip("degenerate")
+    xg, dg = x.to(DEV), d.to(DEV)
+    out = torch.full((B, T, C), 7.0, device=DEV)
+    lens = torch.empty(B, dtype=torch.int64, device=DEV)
+    mask = torch.empty(B, T, dtype=torch.uint8, device=DEV)
+    ctx.check(ctx.lib.masg_length_regulate(ctx.h, ctx.stream(), P(xg), P(dg), B, L, C, T, P(out), P(lens), P(mask)), "lr")
+    assert torch.equal(lens.cpu(), want_len)
+    assert torch.equal(out.cpu(), want)                                               # bit-exact gather + zero pad
+    assert torch.equal(mask.cpu().bool(), restate.mask_from_lengths(want_len, T))
+    assert int(want_len.sum()) == int(d.to(torch.float64).trunc().clamp(min=0).sum())  # conservation
+    lens2 = torch.empty(B, dtype=torch.int64, device=DEV)
+    ctx.check(ctx.lib.masg_mel_lengths(ctx.h, ctx.stream(), P(dg), B, L, P(lens2)), "mel_lengths")
+    assert torch.equal(lens2.cpu(), want_len)
+    # explicit max_len larger than the batch max: zero padded (utils/tools.py:363-381)
+    out2 = torch.full((B, T + 5, C), 7.0, device=DEV)
+    ctx.check(ctx.lib.masg_length_regulate(ctx.h, ctx.stream(), P(xg), P(dg), B, L, C, T + 5, P(out2), None, None), "lr")
+    assert torch.equal(out2.cpu(), restate.length_regulate(x, d, T + 5)[0])
+
+
+@pytest.mark.parametrize("d_ctl", [1.0, 1.3, 0.5])
+def test_duration_rounding_bit_exact(ctx, d_ctl):
+    g = torch.Generator().manual_seed(3)
+    log_d = torch.randn(20000, generator=g) * 1.5 + 1.0
+    halves = torch.log(torch.arange(1, 40, dtype=torch.float32) + 0.5)                # exp(x)-1 lands on .5 boundaries
+    log_d = torch.cat([log_d, halves, torch.tensor([0.0, -10.0, -0.0, 5.0])])
+    want = restate.duration_round(log_d, d_ctl)
+    out = torch.empty_like(log_d, device=DEV)
+    ctx.check(ctx.lib.masg_duration_round(ctx.h, ctx.stream(), P(log_d.to(DEV)), d_ctl, log_d.numel(), P(out)), "dur")
+    out = out.cpu()
+    # identical except where a 1-ulp difference in exp() straddles a rounding boundary (none expected on
+    # the random part; the engineered .5 cases depend on the CPU libm and are allowed to differ by one step)
+    n_rand = 20000
+    assert torch.equal(out[:n_rand], want[:n_rand])
+    assert (out[n_rand:] - want[n_rand:]).abs().max() <= d_ctl + 1e-6
+    assert torch.equal(out[-4:], want[-4:])
+
+
+def test_bucketize_embedding_bit_exact(ctx):
+    g = torch.Generator().manual_seed(4)
+    bins = torch.linspace(-2.5, 8.0, 255)
+    v = torch.cat([torch.randn(5000, generator=g) * 3 + 2, bins[::7], torch.tensor([-100.0, 100.0, 0.0, -2.5, 8.0])])
+    table = torch.randn(256, 256, generator=g)
+    x = torch.randn(v.numel(), 256, generator=g)
+    want_idx = torch.bucketize(v, bins)
+    assert torch.equal(want_idx, restate.bucketize(v, bins))
+    want = x + table[want_idx]
+    xg = x.to(DEV)
+    idx = torch.empty(v.numel(), dtype=torch.int64, device=DEV)
+    ctx.check(ctx.lib.masg_bucketize_embed_add(ctx.h, ctx.stream(), P(v.to(DEV)), P(bins.to(DEV)), 255, P(table.to(DEV)),
+                                               v.numel(), 256, P(xg), P(idx)), "bucket")
+    assert torch.equal(idx.cpu(), want_idx)
+    assert torch.equal(xg.cpu(), want)
+
+
+# ------------------------------------------------------------------------------------------------
+# FastSpeech2
+# ------------------------------------------------------------------------------------------------
+def _run_fs2(model, batch, emb, **kw):
+    gb = helpers.to_gpu(batch)
+    out = model.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], batch["max_src_len"], accents=gb["accents"],
+                                            speaker_emb=emb.to(DEV), **kw)
+    torch.cuda.synchronize()
+    return out
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_fs2_matches_oracle_ragged_batch(precision):
+    model, sd = helpers.fs2_on_gpu(11, "spread", precision)
+    b = syn.make_batch(4, 40, seed=21, lens=[40, 31, 17, 5])
+    g = torch.Generator().manual_seed(2)
+    emb = torch.randn(4, 256, generator=g) * 0.5
+    taps = {}
+    ref = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 40, emb, p_control=0.9, d_control=1.2, taps=taps)
+    out = _run_fs2(model, b, emb, p_control=0.9, d_control=1.2)
+    tol = MEL_TOL[precision]
+    enc = model._context().tap("encoder_out", (4, 40, 256)).cpu()
+    assert (enc - taps["encoder_out"]).abs().max() <= tol * 2
+    for i, name in ((2, "pitch"), (3, "energy"), (4, "log_d")):
+        assert (out[i].cpu() - ref[i]).abs().max() <= tol * 4, name
+    flips = int((out[5].cpu() != ref[5]).sum())
+    print("un-forced duration flips (%s): %d of %d" % (precision, flips, ref[5].numel()))
+    assert torch.equal(out[6].cpu(), ref[6]) and torch.equal(out[8].cpu(), b["src_lens"])
+    if precision == "fp32":
+        assert flips == 0
+    # mel parity on the same padded batch with the oracle's durations teacher-forced
+    ref_t = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 40, emb, p_control=0.9, d_control=1.2, d_target=ref[5])
+    out_t = _run_fs2(model, b, emb, p_control=0.9, d_control=1.2, d_targets=ref[5].to(DEV))
+    assert torch.equal(out_t[9].cpu(), ref_t[9]) and torch.equal(out_t[7].cpu(), ref_t[7])
+    assert out_t[0].shape == ref_t[0].shape and out_t[0].dtype == torch.float32 and out_t[9].dtype == torch.int64
+    e0 = (out_t[0].cpu() - ref_t[0]).abs().max().item()
+    e1 = (out_t[1].cpu() - ref_t[1]).abs().max().item()                        # valid AND padded frames
+    print("mel max-abs err %s: mel %.3e postnet %.3e (tol %.0e)" % (precision, e0, e1, tol))
+    assert e0 <= tol and e1 <= tol
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["fs2_ragged", "fs2_c1"])
+def test_fs2_matches_reference_golden(golden_dir, precision, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    model, sd = helpers.fs2_on_gpu(int(g["weights_seed"]), str(g["duration_mode"]), precision)
+    texts = torch.from_numpy(g["texts"]).to(DEV)
+    out = model.synthesize_from_speaker_emb(
+        ["raw text is ignored"], texts, torch.from_numpy(g["src_lens"]).to(DEV), texts.shape[1],
+        accents=torch.from_numpy(g["accents"]).to(DEV), speaker_emb=torch.from_numpy(g["speaker_emb"]).to(DEV),
+        p_control=float(g["p_control"]), d_control=float(g["d_control"]),
+        d_targets=None if precision == "fp32" else torch.from_numpy(g["d_rounded"]).to(DEV))
+    assert torch.equal(out[9].cpu(), torch.from_numpy(g["mel_lens"]))
+    assert torch.equal(out[5].cpu(), torch.from_numpy(g["d_rounded"]))
+    tol = MEL_TOL[precision]
+    assert np.abs(out[0].cpu().numpy() - g["mel"]).max() <= tol
+    assert np.abs(out[1].cpu().numpy() - g["postnet_mel"]).max() <= tol
+    assert torch.equal(out[7].cpu(), torch.from_numpy(g["mel_mask"]))
+
+
+def test_fs2_forward_signature_and_speaker_lookup():
+    model, sd = helpers.fs2_on_gpu(11, "spread", "fp32")
+    b = syn.make_batch(2, 9, seed=3, lens=[9, 6])
+    gb = helpers.to_gpu(b)
+    speakers = torch.tensor([3, 150], device=DEV)
+    out = model(speakers, gb["texts"], gb["src_lens"], 9, accents=gb["accents"], speaker_meta=gb["speaker_meta"])
+    assert len(out) == 12
+    emb = sd["speaker_emb.weight"][speakers.cpu()]
+    ref = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 9, emb)
+    assert (out[1].cpu() - ref[1]).abs().max() <= 1e-4 and torch.equal(out[9].cpu(), ref[9])
+    assert torch.equal(out[11].cpu(), emb)
+    pi, mu, sigma = restate.gmm_params(sd, b["speaker_meta"])
+    assert (out[10].component_distribution.base_dist.loc.cpu() - mu).abs().max() < 1e-5
+    # accents given as a 1-D [L] tensor broadcast over the batch (synthesize.py:234)
+    acc1 = torch.full((9,), 4, dtype=torch.int64)
+    out1 = model.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], 9, accents=acc1.to(DEV), speaker_emb=emb.to(DEV))
+    ref1 = restate.fs2_forward(sd, b["texts"], acc1, b["src_lens"], 9, emb)
+    assert (out1[1].cpu() - ref1[1]).abs().max() <= 1e-4
+    with pytest.raises(TypeError):
+        model.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], 9, speaker_emb=emb.to(DEV))
+    with pytest.raises(RuntimeError):
+        model.synthesize_from_speaker_emb(None, b["texts"], b["src_lens"], 9, accents=b["accents"], speaker_emb=emb)   # CPU tensors
+
+
+def test_fs2_long_sequence_position_table():
+    """L and T beyond max_seq_len=1000: the rebuilt sinusoid table path (transformer/Models.py:86-98,157-164)."""
+    model, sd = helpers.fs2_on_gpu(1234, "fixed3", "fp32")
+    b = syn.make_batch(1, 1010, seed=8)
+    emb = torch.zeros(1, 256)
+    ref = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 1010, emb)
+    out = _run_fs2(model, b, emb)
+    assert out[0].shape == (1, 3030, 80) and torch.equal(out[9].cpu(), ref[9])
+    assert (out[1].cpu() - ref[1]).abs().max() <= 2e-4
+
+
+# ------------------------------------------------------------------------------------------------
+# HiFi-GAN
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_hifigan_matches_oracle_and_golden(golden_dir, precision):
+    voc, hsd = helpers.hifigan_on_gpu(4321, precision)
+    g = np.load(os.path.join(golden_dir, "hifigan_small.npz"))
+    mel = torch.from_numpy(g["mel"])
+    wav, w16 = voc(mel.to(DEV), return_int16=True)
+    torch.cuda.synchronize()
+    assert wav.shape == (2, 1, 20 * 256) and wav.dtype == torch.float32
+    snr = min(helpers.snr_db(g["wav"][i], wav[i].cpu().numpy()) for i in range(2))
+    print("HiFi-GAN %s: SNR vs reference golden %.1f dB, max-abs %.3e" % (precision, snr, np.abs(wav.cpu().numpy() - g["wav"]).max()))
+    assert snr >= (80.0 if precision == "fp32" else 30.0)
+    if precision == "fp32":
+        assert np.abs(wav.cpu().numpy() - g["wav"]).max() <= 1e-4
+    # int16 conversion is exactly the reference's numpy cast of OUR float waveform (utils/model.py:82-85)
+    assert np.array_equal(w16.cpu().numpy(), restate.wav_to_int16(wav.squeeze(1)))
+    # ragged, odd T and channels-last input
+    g2 = torch.Generator().manual_seed(5)
+    mel2 = torch.randn(3, 80, 37, generator=g2)
+    ref2 = restate.hifigan_forward(hsd, mel2)
+    out2 = voc(mel2.transpose(1, 2).contiguous().to(DEV), channels_last=True)
+    assert out2.shape == (3, 1, 37 * 256)
+    snr2 = min(helpers.snr_db(ref2[i].numpy(), out2[i].cpu().numpy()) for i in range(3))
+    assert snr2 >= (80.0 if precision == "fp32" else 30.0)
+
+
+def test_vocoder_infer_dropin():
+    from masg_b200.hifigan import vocoder_infer
+    voc, hsd = helpers.hifigan_on_gpu(4321, "fp32")
+    g2 = torch.Generator().manual_seed(6)
+    mel = torch.randn(2, 80, 16, generator=g2)
+    wavs = vocoder_infer(mel.to(DEV), voc, syn.MODEL_CONFIG, syn.PREPROCESS_CONFIG, lengths=[16 * 256, 9 * 256])
+    ref = restate.wav_to_int16(restate.hifigan_forward(hsd, mel).squeeze(1))
+    assert wavs[0].dtype == np.int16 and len(wavs[0]) == 16 * 256 and len(wavs[1]) == 9 * 256
+    assert np.abs(wavs[0].astype(np.int32) - ref[0].astype(np.int32)).max() <= 4
+    assert np.abs(wavs[1].astype(np.int32) - ref[1][: 9 * 256].astype(np.int32)).max() <= 4
+
+
+# ------------------------------------------------------------------------------------------------
+# speaker prior
+# ------------------------------------------------------------------------------------------------
+def test_gmm_params_sampling_and_interpolation(golden_dir):
+    from masg_b200.fastspeech2 import gmm_sample
+    from masg_b200.distributions import InterpolateGMM, BarycenterGMM
+    model, sd = helpers.fs2_on_gpu(1234, "fixed3", "fp32")
+    gold = np.load(os.path.join(golden_dir, "gmm_prior.npz"))
+    metas = torch.tensor(syn.META_COMBOS, dtype=torch.float32, device=DEV)
+    pi, mu, sigma = model.speaker_enc.params(metas)
+    assert np.abs(pi.cpu().numpy() - gold["pi"]).max() < 1e-6
+    assert np.abs(mu.cpu().numpy() - gold["mu"]).max() < 1e-6 and np.abs(sigma.cpu().numpy() - gold["sigma"]).max() < 1e-6
+    dist = model.speaker_distribution(metas)
+    assert dist.batch_shape == (4,) and dist.event_shape == (256,)
+    # exact sampling with injected draws
+    gen = torch.Generator().manual_seed(1)
+    N = 64
+    meta_n = metas[torch.arange(N) % 4]
+    pn, mn, sn = model.speaker_enc.params(meta_n)
+    k = torch.randint(0, 3, (N,), generator=gen).to(torch.int32)
+    eps = torch.randn(N, 256, generator=gen)
+    out = gmm_sample(model._context(), pn, mn, sn, N, k_inject=k, eps_inject=eps)
+    want = restate.gmm_sample_injected(mn.cpu(), sn.cpu(), k.long(), eps)
+    assert torch.equal(out.cpu(), want)
+    # internal Philox RNG: deterministic per seed, distributionally right (component frequencies, moments)
+    Nbig = 20000
+    p1, m1, s1 = pi[:1], mu[:1], sigma[:1]
+    a, ka = gmm_sample(model._context(), p1, m1, s1, Nbig, seed=123, return_k=True)
+    b2 = gmm_sample(model._context(), p1, m1, s1, Nbig, seed=123)
+    c2 = gmm_sample(model._context(), p1, m1, s1, Nbig, seed=124)
+    assert torch.equal(a, b2) and not torch.equal(a, c2)
+    freq = torch.bincount(ka.long().cpu(), minlength=3).double() / Nbig
+    assert (freq - pi[0].cpu().double()).abs().max() < 4 * 0.5 / np.sqrt(Nbig)
+    mix_mean = (pi[0, :, None] * mu[0]).sum(0).cpu()
+    mix_var = (pi[0, :, None] * (sigma[0] ** 2 + mu[0] ** 2)).sum(0).cpu() - mix_mean ** 2
+    assert ((a.mean(0).cpu() - mix_mean).abs() < 5 * mix_var.sqrt() / np.sqrt(Nbig)).all()
+    assert ((a.var(0).cpu() / mix_var) - 1).abs().max() < 0.15
+    s = model.speaker_gen(metas)
+    assert s.shape == (4, 256) and s.dtype == torch.float32
+    # InterpolateGMM against the reference-generated fixture
+    da, db = model.speaker_distribution(metas[0:1]), model.speaker_distribution(metas[3:4])
+    ig = InterpolateGMM(da, db)
+    assert np.abs(np.array(ig.ot_Cost) - gold["cost"]).max() / np.abs(gold["cost"]).max() < 1e-5
+    assert np.abs(ig.mixture_distribution.probs[0].cpu().numpy() - gold["weights"]).max() < 1e-6
+    assert np.abs(ig.component_distribution.base_dist.loc[0].cpu().numpy() - gold["mu_050"]).max() < 1e-6
+    assert np.abs(ig.component_distribution.base_dist.scale[0].cpu().numpy() / gold["scale_050"] - 1).max() < 1e-5
+    ig.interpolate_rate(0.25)
+    assert np.abs(ig.component_distribution.base_dist.loc[0].cpu().numpy() - gold["mu_025"]).max() < 1e-6
+    assert np.abs(ig.component_distribution.base_dist.scale[0].cpu().numpy() / gold["scale_025"] - 1).max() < 1e-5
+    smp = ig.sample()
+    assert smp.shape == (1, 256)
+    import io
+    buf = io.BytesIO(); torch.save(ig, buf); buf.seek(0)
+    ig2 = torch.load(buf, weights_only=False)
+    assert torch.equal(ig2.component_distribution.base_dist.loc, ig.component_distribution.base_dist.loc)
+    # BarycenterGMM against the oracle's restatement of the maths
+    bg = BarycenterGMM(model)
+    w, bm, bs, keys = restate.barycenter_gmm([p for p in pi.cpu()], [m for m in mu.cpu()], [s_ for s_ in sigma.cpu()])
+    assert bg.mixture_distribution.probs.shape[-1] == len(keys)
+    assert (bg.mixture_distribution.probs[0].cpu() - w / w.sum()).abs().max() < 1e-5
+    assert (bg.component_distribution.base_dist.loc[0].cpu() - bm).abs().max() < 1e-5
+    assert (bg.component_distribution.base_dist.scale[0].cpu() - bs).abs().max() < 1e-5
+    assert bg.sample().shape == (1, 256)
+
+
+# ------------------------------------------------------------------------------------------------
+# end to end through the host-buffer C-ABI call; full-size properties
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_end_to_end_host_call_matches_staged_calls(precision):
+    from masg_b200.synth import Synthesizer
+    fs2, sd = helpers.fs2_on_gpu(1234, "fixed3", precision)
+    voc, hsd = helpers.hifigan_on_gpu(4321, precision)
+    syn_ = Synthesizer(fs2, voc, precision)
+    b = syn.make_batch(3, 20, seed=12, lens=[20, 14, 6])
+    g = torch.Generator().manual_seed(9)
+    emb = torch.randn(3, 256, generator=g) * 0.5
+    h_w, h_m, T, h2d, d2h = syn_.synthesize_host(b["texts"], b["accents"], b["src_lens"], emb, t_cap=64)
+    assert T == 60 and h_m.tolist() == [60, 42, 18] and h2d > 0 and d2h == 3 * 60 * 256 * 2 + 24
+    gb = helpers.to_gpu(b)
+    w16, mel_lens, post = syn_.synthesize(gb["texts"], gb["accents"], gb["src_lens"], emb.to(DEV))
+    assert torch.equal(h_w[:, : 256 * T], w16.cpu())                       # same kernels, same result, bit for bit
+    ref = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 20, emb)
+    ref_wav = restate.hifigan_forward(hsd, ref[1].transpose(1, 2))
+    for i, ml in enumerate([60, 42, 18]):
+        n = ml * 256
+        snr = helpers.snr_db(ref_wav[i, 0, :n].numpy(), h_w[i, :n].float().numpy() / 32768.0)
+        print("e2e %s utt %d SNR %.1f dB" % (precision, i, snr))
+        assert snr >= 30.0                                                   # end-to-end waveform SNR over valid samples
+
+
+@pytest.mark.parametrize("B,L", [(64, 200), (16, 1000)])
+def test_full_size_properties_bf16(B, L):
+    """BASELINE configs 3 and 5 at full size: properties that do not need the (slow) CPU oracle."""
+    fs2, sd = helpers.fs2_on_gpu(1234, "fixed3", "bf16")
+    voc, hsd = helpers.hifigan_on_gpu(4321, "bf16")
+    b = syn.make_batch(B, L, seed=1234 + B)
+    gb = helpers.to_gpu(b)
+    g = torch.Generator().manual_seed(1)
+    emb = (torch.randn(B, 256, generator=g) * 0.5).to(DEV)
+    out = fs2.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], L, accents=gb["accents"], speaker_emb=emb)
+    assert out[0].shape == (B, 3 * L, 80) and torch.equal(out[9].cpu(), torch.full((B,), 3 * L))
+    assert torch.equal(out[5].cpu(), torch.full((B, L), 3.0)) and not out[7].any()
+    assert torch.isfinite(out[1]).all()
+    nb = min(B, 8)
+    wav, w16 = voc(out[1][:nb], channels_last=True, return_int16=True)
+    assert wav.shape == (nb, 1, 256 * 3 * L) and torch.isfinite(wav).all() and wav.abs().max() <= 1.0
+    # batch-composition invariance for equal-length utterances: rows depend only on their own inputs
+    out2 = fs2.synthesize_from_speaker_emb(None, gb["texts"][:2], gb["src_lens"][:2], L, accents=gb["accents"][:2], speaker_emb=emb[:2])
+    assert (out2[1] - out[1][:2]).abs().max() <= 1e-5
+    wav2 = voc(out[1][:2], channels_last=True)
+    assert (wav2 - wav[:2]).abs().max() <= 1e-5

@@ -1,0 +1,141 @@
+"""CPU tests: the C-ABI library loads and exports every symbol include/masg.h declares, the product
+path fails loudly without a GPU (no CPU fallback), drop-in state_dict layouts match the reference's,
+and the batch scheduler / multi-rank sharding logic (gloo, world_size 2)."""
+import ctypes
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import masg_b200  # noqa: F401
+from masg_b200 import synthetic as syn
+from masg_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib_path():
+    import __graft_entry__ as ge
+    ge.build()
+    from masg_b200 import _lib
+    return _lib.LIB_PATH
+
+
+def test_library_exports_every_header_symbol(lib_path):
+    header = open(os.path.join(ROOT, "include", "masg.h")).read()
+    declared = set(re.findall(r"\b(masg_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(lib_path)
+    for name in declared:
+        assert hasattr(lib, name), "libmasg.so does not export %s" % name
+    from masg_b200 import _lib
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    lib.masg_version.restype = ctypes.c_char_p
+    assert b"sm_100a" in lib.masg_version()
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback(lib_path):
+    from masg_b200 import _lib
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _lib.Context("cuda:0")
+    from tests.helpers import config_dir
+    from masg_b200.fastspeech2 import FastSpeech2
+    m = FastSpeech2(syn.PREPROCESS_CONFIG, syn.MODEL_CONFIG, config_dir()).eval()
+    b = syn.make_batch(1, 5, seed=0)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m.synthesize_from_speaker_emb(None, b["texts"], b["src_lens"], 5, accents=b["accents"], speaker_emb=torch.zeros(1, 256))
+    from masg_b200.hifigan import Generator, AttrDict
+    with pytest.raises(RuntimeError, match="CUDA"):
+        Generator(AttrDict(syn.HIFIGAN_CONFIG))(torch.zeros(1, 80, 4))
+
+
+def test_dropin_state_dict_layouts():
+    from tests.helpers import config_dir
+    from masg_b200.fastspeech2 import FastSpeech2
+    from masg_b200.hifigan import Generator, AttrDict
+    m = FastSpeech2(syn.PREPROCESS_CONFIG, syn.MODEL_CONFIG, config_dir())
+    sd = syn.make_fs2_state_dict(seed=0)
+    msd = m.state_dict()
+    assert set(msd) == set(sd) and len(sd) == 242
+    for k in sd:
+        assert tuple(msd[k].shape) == tuple(sd[k].shape), k
+    assert sum(p.numel() for p in m.parameters()) == 35239248
+    m.load_state_dict(sd)
+    g = Generator(AttrDict(syn.HIFIGAN_CONFIG))
+    hsd = syn.make_hifigan_state_dict(seed=0)
+    assert set(g.state_dict()) == set(hsd) and len(hsd) == 234
+    g.load_state_dict(hsd)
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()):
+        g.remove_weight_norm()
+    folded = syn.fold_weight_norm(hsd)
+    gsd = g.state_dict()
+    assert set(gsd) == set(folded) and len(folded) == 156
+    for k in folded:
+        assert torch.allclose(gsd[k], folded[k], atol=1e-6), k
+    assert sum(v.numel() for v in folded.values()) == 13926017
+
+
+def test_unsupported_config_is_an_error():
+    import copy
+    from tests.helpers import config_dir
+    from masg_b200.fastspeech2 import FastSpeech2
+    cfg = copy.deepcopy(syn.MODEL_CONFIG)
+    cfg["jdit"]["use_jdit"] = True
+    with pytest.raises(NotImplementedError):
+        FastSpeech2(syn.PREPROCESS_CONFIG, cfg, config_dir())
+
+
+def test_scheduler_covers_all_utterances_and_balances():
+    lens = syn.c4_lengths()
+    assert lens.sum() * 3 == 1978896
+    batches = synth.plan_batches(lens, frame_budget=40000, max_batch=64)
+    flat = np.concatenate(batches)
+    assert sorted(flat.tolist()) == list(range(4096))
+    for b in batches:
+        assert len(b) <= 64 and len(b) * lens[b].max() * 3 <= 40000
+    for ws in (1, 2, 4, 8):
+        plan = synth.assign_batches(batches, lens, ws)
+        assert sorted(sum(plan, [])) == list(range(len(batches)))
+        loads = [sum(synth.utterance_cost(lens[i]) for bi in p for i in batches[bi]) for p in plan]
+        assert max(loads) / (sum(loads) / ws) < 1.05                         # LPT keeps ranks within 5 %
+    assert [synth.shard_batch(64, r, 8) for r in range(8)] == [(8 * r, 8 * r + 8) for r in range(8)]
+    assert synth.shard_batch(16, 7, 8) == (14, 16) and synth.shard_batch(3, 3, 4) == (3, 3)
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    lens = syn.c4_lengths(256)
+    batches = synth.plan_batches(lens, frame_budget=20000, max_batch=32)
+    mine = synth.assign_batches(batches, lens, world)[rank]
+    frames = torch.tensor([float(sum(int(lens[i]) * 3 for bi in mine for i in batches[bi]))])
+    count = torch.tensor([float(sum(len(batches[bi]) for bi in mine))])
+    dist.all_reduce(frames); dist.all_reduce(count)
+    # max-over-ranks timing reduction used by bench.py
+    t = torch.tensor([1.0 + rank]); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    q.put((rank, frames.item(), count.item(), t.item()))
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharding_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue(); port = _free_port()
+    ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = [q.get(timeout=120) for _ in ps]
+    [p.join(timeout=60) for p in ps]
+    lens = syn.c4_lengths(256)
+    for rank, frames, count, tmax in res:
+        assert frames == float(lens.sum() * 3) and count == 256.0 and tmax == 2.0
