@@ -6,6 +6,9 @@
 #include <cmath>
 #include <algorithm>
 
+ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
+                   const float* scale, const float* bias_override);
+
 static thread_local std::string g_err;
 
 #define API_BEGIN(ctx)                                                                   \
@@ -288,6 +291,44 @@ int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, cons
     if (h_mel_lens) CUDA_OK(cudaMemcpyAsync(h_mel_lens, mel_lens, B * 8, cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
     if (h_tmax) *h_tmax = tmax;
+    API_END(c)
+}
+
+// Single Conv1d / ConvTranspose1d through the context's dense-contraction kernel (diagnostic + micro-benchmark hook).
+int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin, const float* w, const float* bias, int Cout,
+                int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int reps, float* y, float* ms_out) {
+    API_BEGIN(c)
+    cudaStream_t s = (cudaStream_t)stream;
+    MASG_CHECK(x && w && y && B > 0 && T > 0 && reps >= 1, "bad argument");
+    const size_t keep = c->owned.size();
+    ConvDesc d; int Q = T; long So = T;
+    if (stride_transposed > 0) {
+        const int u = stride_transposed;
+        MASG_CHECK(k == 2 * u, "transposed conv needs k = 2*stride");
+        d.Cin = Cin; d.N = u * Cout; d.taps = 2; d.off0 = 0; d.tstep = -1; d.bias_mod = Cout;
+        d.orow = (long)u * Cout; d.ooff = -(long)((k - u) / 2) * Cout;
+        float* w32 = nullptr; CUDA_OK(cudaMalloc(&w32, (size_t)2 * Cin * u * Cout * 4)); c->owned.push_back(w32);
+        launch_repack_convT_w(c, s, w, Cin, Cout, k, u, w32);
+        d.w32 = w32; d.bias = bias;
+        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+        Q = T + 1; So = (long)T * u;
+    } else {
+        d = make_conv(c, s, w, bias, Cout, Cin, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr);
+    }
+    ConvIO io;
+    io.X = x; io.x_ld = Cin; io.x_bs = (long)T * Cin; io.Tin = T; io.Y = y; io.y_bs = So * Cout; io.y_limit = So * Cout;
+    io.B = B; io.Q = Q; io.out_act = out_act;
+    if (in_lrelu_slope != 0.f) { io.in_act = ACT_LRELU; io.in_slope = in_lrelu_slope; }
+    launch_conv(c, s, d, io);                                  // warm-up / result
+    cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));
+    CUDA_OK(cudaEventRecord(e0, s));
+    for (int r = 0; r < reps; ++r) launch_conv(c, s, d, io);
+    CUDA_OK(cudaEventRecord(e1, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms_out) *ms_out = ms / reps;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }
     API_END(c)
 }
 

@@ -50,9 +50,9 @@ struct ConvDesc {
     long orow = 0, ooff = 0;          // output row stride / offset in elements (0 → N / 0)
     const float* w32 = nullptr;       // [taps*Cin][N] fp32 (SIMT path)
     const float* bias = nullptr;      // [bias_mod]
-    // tcgen05 path: bf16 weights, K-major [Npad][taps*Cin_pad]
-    const bf16* w16 = nullptr; int Cin_pad = 0, Npad = 0;
-    void* tmap_w = nullptr;           // CUtensorMap* (host copy, 128B)
+    // tcgen05 path (conv_tc.cu): bf16 weights pre-tiled into UMMA no-swizzle K-major blobs
+    // [n_tile = N/NT][ci = Cin/KW][tap][KW/8][NT][8]; one blob = one (channel slab, tap) B operand
+    const bf16* w16 = nullptr; int NT = 0, KW = 0;
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc
@@ -103,14 +103,16 @@ struct masg_ctx {
 // kernel launchers (each increments ctx->launches)
 // ------------------------------------------------------------------------------------------------
 struct ConvIO {
-    const float* X = nullptr; long x_bs = 0; int x_ld = 0; int Tin = 0;     // input rows [B][Tin][x_ld]
-    float* Y = nullptr; long y_bs = 0; long y_limit = 0;                    // output, valid elements per batch
+    const void* X = nullptr; int x_bf16 = 0; long x_bs = 0; int x_ld = 0; int Tin = 0;   // input rows [B][Tin][x_ld] (fp32 or bf16)
+    float* Y = nullptr; bf16* Y16 = nullptr; long y_bs = 0; long y_limit = 0;  // fp32 and/or bf16 output, valid elements per batch
     int B = 1, Q = 0;                                                        // rows computed per batch
     int in_act = ACT_NONE; float in_slope = 0.f;
     int out_act = ACT_NONE; float out_slope = 0.f;
-    const float* R1 = nullptr; const float* R2 = nullptr; float out_scale = 1.f;
+    const void* R1 = nullptr; const void* R2 = nullptr; int r_bf16 = 0; float out_scale = 1.f;   // residuals (fp32 or bf16)
 };
 void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
+// precision dispatch: MASG_PREC_FP32 → conv_simt.cu, MASG_PREC_BF16 → conv_tc.cu (tcgen05)
+void launch_conv(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
 
 void launch_embed(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
                   const float* wemb, const float* aemb, const float* pos, int B, int L, float* out);
@@ -132,7 +134,7 @@ void launch_length_regulate(masg_ctx* c, cudaStream_t s, const float* x, const f
                             uint8_t* mask);
 void launch_attention_f32(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out);
 void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int B, int C, int T, float* out_btc);
-void launch_conv_post(masg_ctx* c, cudaStream_t s, const float* x, const float* w, float bias, int B, long S,
+void launch_conv_post(masg_ctx* c, cudaStream_t s, const void* x, int x_bf16, const float* w, float bias, int B, long S,
                       float in_slope, float* wav, int16_t* wav16);
 void launch_pos_table(masg_ctx* c, cudaStream_t s, int n, float* out);
 void launch_add2(masg_ctx* c, cudaStream_t s, const float* a, const float* b, float* out, int64_t n);

@@ -113,16 +113,17 @@ k_conv_f32(ConvArgs a) {
 
 void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
     MASG_CHECK(d.w32 != nullptr, "conv_f32: fp32 weights not committed");
+    MASG_CHECK(!io.x_bf16 && !io.r_bf16 && io.Y16 == nullptr && io.Y != nullptr, "conv_f32: the fp32 path takes fp32 tensors only");
     MASG_CHECK(d.Cin % TK == 0 && d.N % 4 == 0, "conv_f32: Cin=%d must be a multiple of 16 and N=%d of 4", d.Cin, d.N);
     MASG_CHECK(io.x_ld % 4 == 0, "conv_f32: x_ld=%d must be a multiple of 4", io.x_ld);
     if (io.Q <= 0 || io.B <= 0) return;
     ConvArgs a;
-    a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
+    a.X = (const float*)io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
     a.W = d.w32; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
     a.Y = io.Y; a.y_bs = io.y_bs; a.y_limit = io.y_limit; a.orow = d.orow ? d.orow : d.N; a.ooff = d.ooff; a.Q = io.Q;
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
-    a.R1 = io.R1; a.R2 = io.R2; a.out_scale = io.out_scale;
+    a.R1 = (const float*)io.R1; a.R2 = (const float*)io.R2; a.out_scale = io.out_scale;
     dim3 grid((io.Q + TM - 1) / TM, (d.N + TN - 1) / TN, io.B);
     k_conv_f32<<<grid, 256, 0, s>>>(a);
     c->launches++;

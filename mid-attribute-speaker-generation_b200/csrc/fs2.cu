@@ -1,6 +1,7 @@
 // FastSpeech2 inference orchestration (model/fastspeech2.py:187-303): weight repacking at commit and
-// the two-phase forward.  Host code only; every tensor op is a kernel from kernels_mem.cu /
-// conv_simt.cu (fp32 mode) or conv_tc.cu / attn_tc.cu (bf16 tcgen05 mode).
+// the two-phase forward.  Host code only; every tensor op is a kernel from kernels_mem.cu and, for the
+// dense contractions, conv_simt.cu (MASG_PREC_FP32) or the tcgen05 kernel of conv_tc.cu (MASG_PREC_BF16:
+// bf16 operands, fp32 accumulation; activations stay fp32 in HBM and are converted while staged).
 #include "common.cuh"
 #include "tc.cuh"
 #include <cmath>
@@ -159,7 +160,7 @@ static void conv32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* 
     ConvIO io;
     io.X = X; io.x_ld = x_ld; io.x_bs = (long)T * x_ld; io.Tin = T;
     io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
-    launch_conv_f32(c, s, d, io);
+    launch_conv(c, s, d, io);
 }
 
 static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S) {
@@ -212,20 +213,16 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
     c->B = B; c->L = L; c->src_lens_dev = src_lens;
     if (src_mask) launch_mask(c, s, src_lens, B, L, src_mask);
     const float* pos = pos_table(c, s, false, L);
-    if (c->precision == MASG_PREC_BF16) {
-        tc_fs2_encoder(c, s, ar, texts, accents, acc1d, src_lens, B, L, pos, c->tap_enc);
-    } else {
-        float* x = ar.get<float>(rows * 256);
+    {
+        float* x = c->tap_enc;
         launch_embed(c, s, texts, accents, acc1d, c->word_emb, c->accent_emb, pos, B, L, x);
         for (auto& Lr : c->enc) fft_block_f32(c, s, ar, Lr, x, src_lens, B, L);
-        CUDA_OK(cudaMemcpyAsync(c->tap_enc, x, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     }
     float* x = c->va_out;
     CUDA_OK(cudaMemcpyAsync(x, c->tap_enc, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     launch_add_rowvec(c, s, x, spk, B, L, 256);                                 // pads too (fastspeech2.py:215-218)
     auto predict = [&](int which, float scale, float* out) {
-        if (c->precision == MASG_PREC_BF16) tc_predictor(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
-        else predictor_f32(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
+        predictor_f32(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
     };
     predict(0, 1.0f, log_d);
     predict(1, p_ctl, pitch);
@@ -257,15 +254,10 @@ void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, ui
     launch_length_regulate(c, s, c->va_out, c->d_rounded_dev, B, L, 256, T, nullptr, c->tap_lr, nullptr, mel_mask);
     const float* pos = pos_table(c, s, true, T);
     const int64_t* lens = c->mel_lens_dev;
-    if (c->precision == MASG_PREC_BF16) {
-        tc_fs2_decoder_mel(c, s, ar, c->tap_lr, pos, lens, B, T, c->tap_dec, mel, post);
-        return;
-    }
-    float* x = ar.get<float>(rows * 256);
+    float* x = c->tap_dec;
     CUDA_OK(cudaMemcpyAsync(x, c->tap_lr, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     launch_add_pos(c, s, x, pos, B, T, 256);
     for (auto& Lr : c->dec) fft_block_f32(c, s, ar, Lr, x, lens, B, T);
-    CUDA_OK(cudaMemcpyAsync(c->tap_dec, x, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     conv32(c, s, c->mel_linear, x, 256, B, T, mel);                             // pads become bias (fastspeech2.py:242)
     float* h1 = ar.get<float>(rows * 512); float* h2 = ar.get<float>(rows * 512);
     conv32(c, s, c->postnet[0], mel, 80, B, T, h1, ACT_TANH);

@@ -81,18 +81,23 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
     c->hg_ready = true;
 }
 
-static void convS(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* X, int B, long Sin, float* Y, long Sout, int Cout,
-                  int in_act, float in_slope, const float* R1, const float* R2, float out_scale, int Q) {
+// activations are fp32 (MASG_PREC_FP32) or bf16 (MASG_PREC_BF16) channels-last [B, S, C]
+static void convS(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const void* X, bool x_bf16, int B, long Sin, void* Y, long Sout,
+                  int Cout, int in_act, float in_slope, const void* R1, const void* R2, float out_scale, int Q) {
+    const bool bf = c->precision == MASG_PREC_BF16;
     ConvIO io;
-    io.X = X; io.x_ld = d.Cin; io.x_bs = Sin * d.Cin; io.Tin = (int)Sin;
-    io.Y = Y; io.y_bs = Sout * Cout; io.y_limit = Sout * Cout; io.B = B; io.Q = Q;
-    io.in_act = in_act; io.in_slope = in_slope; io.R1 = R1; io.R2 = R2; io.out_scale = out_scale;
-    launch_conv_f32(c, s, d, io);
+    io.X = X; io.x_bf16 = x_bf16; io.x_ld = d.Cin; io.x_bs = Sin * d.Cin; io.Tin = (int)Sin;
+    if (bf) io.Y16 = (bf16*)Y; else io.Y = (float*)Y;
+    io.y_bs = Sout * Cout; io.y_limit = Sout * Cout; io.B = B; io.Q = Q;
+    io.in_act = in_act; io.in_slope = in_slope; io.R1 = R1; io.R2 = R2; io.r_bf16 = bf; io.out_scale = out_scale;
+    launch_conv(c, s, d, io);
 }
 
 void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16) {
     MASG_CHECK(c->hg_ready, "HiFi-GAN weights not committed (call masg_hifigan_commit)");
     MASG_CHECK(B > 0 && T > 0, "empty vocoder input B=%d T=%d", B, T);
+    const bool bf = c->precision == MASG_PREC_BF16;
+    const size_t esz = bf ? 2 : 4;
     Arena& ar = c->arena_b;
     ar.reset();
     const float* melT = mel;
@@ -101,36 +106,35 @@ void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int 
         launch_transpose_mel(c, s, mel, B, 80, T, t);
         melT = t;
     }
-    if (c->precision == MASG_PREC_BF16) { tc_hifigan_forward(c, s, ar, melT, B, T, wav, w16); return; }
     long S = T;
-    float* x = ar.get<float>((size_t)B * S * 512);
-    convS(c, s, c->hg_pre, melT, B, S, x, S, 512, ACT_NONE, 0.f, nullptr, nullptr, 1.f, (int)S);
+    char* x = (char*)ar.alloc((size_t)B * S * 512 * esz);
+    convS(c, s, c->hg_pre, melT, false, B, S, x, S, 512, ACT_NONE, 0.f, nullptr, nullptr, 1.f, (int)S);
     for (int i = 0; i < 4; ++i) {
         int u = c->hg_up_rate[i], C = c->hg_ch[i + 1];
         long So = S * u;
-        size_t n = (size_t)B * So * C;
-        float* xu = ar.get<float>(n); float* xs = ar.get<float>(n); float* h = ar.get<float>(n);
-        float* ya = ar.get<float>(n); float* yb = ar.get<float>(n);
+        size_t n = (size_t)B * So * C * esz;
+        char* xu = (char*)ar.alloc(n); char* xs = (char*)ar.alloc(n); char* h = (char*)ar.alloc(n);
+        char* ya = (char*)ar.alloc(n); char* yb = (char*)ar.alloc(n);
         // x = ups[i](leaky_relu(x, 0.1))   (models.py:152-153)
-        convS(c, s, c->hg_ups[i], x, B, S, xu, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)S + 1);
+        convS(c, s, c->hg_ups[i], x, bf, B, S, xu, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)S + 1);
         for (int j = 0; j < 3; ++j) {
             int rb = i * 3 + j;
-            const float* y = xu;
+            const char* y = xu;
             for (int m = 0; m < 3; ++m) {
                 // xt = c2(lrelu(c1(lrelu(y)))); y = xt + y   (models.py:96-103)
-                convS(c, s, c->hg_c1[rb][m], y, B, So, h, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)So);
+                convS(c, s, c->hg_c1[rb][m], y, bf, B, So, h, So, C, ACT_LRELU, 0.1f, nullptr, nullptr, 1.f, (int)So);
                 if (m < 2) {
-                    float* yn = (y == ya) ? yb : ya;
-                    convS(c, s, c->hg_c2[rb][m], h, B, So, yn, So, C, ACT_LRELU, 0.1f, y, nullptr, 1.f, (int)So);
+                    char* yn = (y == ya) ? yb : ya;
+                    convS(c, s, c->hg_c2[rb][m], h, bf, B, So, yn, So, C, ACT_LRELU, 0.1f, y, nullptr, 1.f, (int)So);
                     y = yn;
                 } else {
                     // last pair of the block: fold the MRF sum (xs += block) and, on the last block, the /3 (models.py:155-160)
-                    convS(c, s, c->hg_c2[rb][m], h, B, So, xs, So, C, ACT_LRELU, 0.1f, y, j > 0 ? xs : nullptr,
+                    convS(c, s, c->hg_c2[rb][m], h, bf, B, So, xs, So, C, ACT_LRELU, 0.1f, y, j > 0 ? xs : nullptr,
                           j == 2 ? (1.0f / 3.0f) : 1.f, (int)So);
                 }
             }
         }
         x = xs; S = So;
     }
-    launch_conv_post(c, s, x, c->hg_post_w, c->hg_post_b, B, S, 0.01f, wav, w16);   // F.leaky_relu default slope (models.py:161)
+    launch_conv_post(c, s, x, bf, c->hg_post_w, c->hg_post_b, B, S, 0.01f, wav, w16);   // F.leaky_relu default slope (models.py:161)
 }

@@ -432,20 +432,28 @@ void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int
 // utils/model.py:82-85).  256 samples per CTA; the (256+6)x32 input window is staged once in shared
 // memory (stride 33: conflict-free) with the activation applied on the way in.
 // ------------------------------------------------------------------------------------------------
+template <bool XBF>
 __global__ void __launch_bounds__(256)
-k_conv_post(const float* __restrict__ x, const float* __restrict__ w, float bias, long S, float slope,
+k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias, long S, float slope,
             float* __restrict__ wav, int16_t* __restrict__ wav16) {
     __shared__ float xs[262 * 33];
     __shared__ float ws[7 * 32];
     int b = blockIdx.y; long s0 = (long)blockIdx.x * 256;
     int tid = threadIdx.x;
     if (tid < 224) ws[tid] = w[tid];
-    const float* xb = x + (long)b * S * 32;
     for (int i = tid; i < 262 * 8; i += 256) {
         int r = i >> 3, c4 = i & 7;
         long srow = s0 + r - 3;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (srow >= 0 && srow < S) v = ((const float4*)(xb + srow * 32))[c4];
+        if (srow >= 0 && srow < S) {
+            if (XBF) {
+                uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(xv) + ((long)b * S + srow) * 32 + c4 * 4);
+                float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.x)), b2 = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.y));
+                v = make_float4(a.x, a.y, b2.x, b2.y);
+            } else {
+                v = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xv) + ((long)b * S + srow) * 32)[c4];
+            }
+        }
         v.x = v.x > 0.f ? v.x : v.x * slope; v.y = v.y > 0.f ? v.y : v.y * slope;
         v.z = v.z > 0.f ? v.z : v.z * slope; v.w = v.w > 0.f ? v.w : v.w * slope;
         float* dst = &xs[r * 33 + c4 * 4];
@@ -465,10 +473,11 @@ k_conv_post(const float* __restrict__ x, const float* __restrict__ w, float bias
     if (wav) wav[(long)b * S + sidx] = y;
     if (wav16) wav16[(long)b * S + sidx] = (int16_t)__float2int_rz(y * 32768.0f);
 }
-void launch_conv_post(masg_ctx* c, cudaStream_t s, const float* x, const float* w, float bias, int B, long S,
+void launch_conv_post(masg_ctx* c, cudaStream_t s, const void* x, int x_bf16, const float* w, float bias, int B, long S,
                       float in_slope, float* wav, int16_t* wav16) {
     dim3 grid(cdiv(S, 256), B);
-    k_conv_post<<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16);
+    if (x_bf16) k_conv_post<true><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16);
+    else k_conv_post<false><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16);
     c->launches++;
 }
 
@@ -541,7 +550,9 @@ __global__ void k_gmm_sample(const float* __restrict__ pi, const float* __restri
     const float* m = mu + ((long)np * K + k) * D + d0;
     const float* sc = scale + ((long)np * K + k) * D + d0;
     float4 r;
-    r.x = m[0] + sc[0] * e.x; r.y = m[1] + sc[1] * e.y; r.z = m[2] + sc[2] * e.z; r.w = m[3] + sc[3] * e.w;
+    // separate multiply and add (no FMA contraction): bit-identical to loc + scale * eps evaluated by torch
+    r.x = __fadd_rn(m[0], __fmul_rn(sc[0], e.x)); r.y = __fadd_rn(m[1], __fmul_rn(sc[1], e.y));
+    r.z = __fadd_rn(m[2], __fmul_rn(sc[2], e.z)); r.w = __fadd_rn(m[3], __fmul_rn(sc[3], e.w));
     *(float4*)(out + (long)n * D + d0) = r;
 }
 void launch_gmm_sample(masg_ctx* c, cudaStream_t s, const float* pi, const float* mu, const float* scale, int N, int Np,

@@ -76,7 +76,8 @@ def test_duration_rounding_bit_exact(ctx, d_ctl):
     log_d = torch.cat([log_d, halves, torch.tensor([0.0, -10.0, -0.0, 5.0])])
     want = restate.duration_round(log_d, d_ctl)
     out = torch.empty_like(log_d, device=DEV)
-    ctx.check(ctx.lib.masg_duration_round(ctx.h, ctx.stream(), P(log_d.to(DEV)), d_ctl, log_d.numel(), P(out)), "dur")
+    log_dg = log_d.to(DEV)                                                            # keep alive across the call
+    ctx.check(ctx.lib.masg_duration_round(ctx.h, ctx.stream(), P(log_dg), d_ctl, log_d.numel(), P(out)), "dur")
     out = out.cpu()
     # identical except where a 1-ulp difference in exp() straddles a rounding boundary (none expected on
     # the random part; the engineered .5 cases depend on the CPU libm and are allowed to differ by one step)
@@ -97,7 +98,8 @@ def test_bucketize_embedding_bit_exact(ctx):
     want = x + table[want_idx]
     xg = x.to(DEV)
     idx = torch.empty(v.numel(), dtype=torch.int64, device=DEV)
-    ctx.check(ctx.lib.masg_bucketize_embed_add(ctx.h, ctx.stream(), P(v.to(DEV)), P(bins.to(DEV)), 255, P(table.to(DEV)),
+    vg, bg, tg = v.to(DEV), bins.to(DEV), table.to(DEV)                               # keep alive across the call
+    ctx.check(ctx.lib.masg_bucketize_embed_add(ctx.h, ctx.stream(), P(vg), P(bg), 255, P(tg),
                                                v.numel(), 256, P(xg), P(idx)), "bucket")
     assert torch.equal(idx.cpu(), want_idx)
     assert torch.equal(xg.cpu(), want)
@@ -350,3 +352,49 @@ def test_full_size_properties_bf16(B, L):
     assert (out2[1] - out[1][:2]).abs().max() <= 1e-5
     wav2 = voc(out[1][:2], channels_last=True)
     assert (wav2 - wav[:2]).abs().max() <= 1e-5
+
+
+# ------------------------------------------------------------------------------------------------
+# the dense-contraction kernel alone (tcgen05 implicit GEMM in bf16 mode) against torch conv1d on the CPU
+# ------------------------------------------------------------------------------------------------
+CONV_CASES = [
+    # B, T, Cin, Cout, k, dil, transposed stride, in-lrelu slope, out act
+    (2, 200, 256, 256, 1, 1, 0, 0.0, 0),      # fc / w_2-style linear
+    (2, 150, 256, 768, 1, 1, 0, 0.0, 0),      # QKV
+    (1, 300, 256, 1024, 9, 1, 0, 0.0, 1),     # FFN w_1 + ReLU
+    (2, 131, 1024, 256, 1, 1, 0, 0.0, 0),     # FFN w_2, multi-chunk K
+    (3, 77, 80, 512, 5, 1, 0, 0.0, 2),        # PostNet first conv + tanh, Cin = 80
+    (2, 90, 512, 80, 5, 1, 0, 0.0, 0),        # PostNet last conv, N = 80
+    (2, 1000, 128, 128, 11, 5, 0, 0.1, 0),    # HiFi-GAN dilated ResBlock conv
+    (2, 1500, 32, 32, 3, 1, 0, 0.1, 0),       # HiFi-GAN stage 4
+    (1, 2100, 64, 64, 7, 3, 0, 0.1, 0),
+    (2, 37, 512, 256, 16, 1, 8, 0.1, 0),      # ConvTranspose1d ups[0]
+    (2, 300, 64, 32, 4, 1, 2, 0.1, 0),        # ConvTranspose1d ups[3]
+]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_kernel_matches_torch(precision, case):
+    import torch.nn.functional as F
+    from masg_b200 import _lib
+    B, T, Cin, Cout, k, dil, ups, slope, act = case
+    cx = _lib.default_context(DEV, precision)
+    g = torch.Generator().manual_seed(hash(case) % 1000)
+    x = torch.randn(B, T, Cin, generator=g)
+    w = torch.randn((Cin, Cout, k) if ups else (Cout, Cin, k), generator=g) / (Cin * (2 if ups else k)) ** 0.5
+    bias = torch.randn(Cout, generator=g)
+    xin = F.leaky_relu(x, slope) if slope else x
+    if ups:
+        ref = F.conv_transpose1d(xin.transpose(1, 2), w, bias, stride=ups, padding=(k - ups) // 2)
+    else:
+        ref = F.conv1d(xin.transpose(1, 2), w, bias, dilation=dil, padding=(k * dil - dil) // 2)
+    ref = [ref, torch.relu(ref), torch.tanh(ref)][act].transpose(1, 2).contiguous()
+    xg, wg, bg = x.to(DEV), w.to(DEV), bias.to(DEV)
+    y = torch.full(ref.shape, 7.0, device=DEV)
+    ms = ctypes.c_float(0)
+    cx.check(cx.lib.masg_conv1d(cx.h, cx.stream(), P(xg), B, T, Cin, P(wg), P(bg), Cout, k, dil, ups, slope, act, 1, P(y),
+                                ctypes.byref(ms)), "conv1d")
+    err = (y.cpu() - ref).abs().max().item()
+    print("conv %s %s: max-abs err %.3e, %.3f ms" % (precision, case, err, ms.value))
+    assert err <= (2e-4 if precision == "fp32" else 4e-2)
