@@ -39,7 +39,7 @@ SIGNATURES = {
     "masg_gmm_barycenter": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P]),
     "masg_synthesize_host": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_int, P, P,
                                      ctypes.POINTER(c_i64)]),
-    "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, P,
+    "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, c_int, P,
                             ctypes.POINTER(c_float)]),
     "masg_launch_count": (c_i64, [P, c_int]),
     "masg_debug_tap": (c_int, [P, P, c_char_p, P, c_i64]),

@@ -7,7 +7,7 @@
 #include <algorithm>
 
 ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
-                   const float* scale, const float* bias_override);
+                   const float* scale, const float* bias_override, bool split);
 
 static thread_local std::string g_err;
 
@@ -296,7 +296,8 @@ int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, cons
 
 // Single Conv1d / ConvTranspose1d through the context's dense-contraction kernel (diagnostic + micro-benchmark hook).
 int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin, const float* w, const float* bias, int Cout,
-                int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int reps, float* y, float* ms_out) {
+                int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int split, int reps, float* y,
+                float* ms_out) {
     API_BEGIN(c)
     cudaStream_t s = (cudaStream_t)stream;
     MASG_CHECK(x && w && y && B > 0 && T > 0 && reps >= 1, "bad argument");
@@ -310,10 +311,10 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         float* w32 = nullptr; CUDA_OK(cudaMalloc(&w32, (size_t)2 * Cin * u * Cout * 4)); c->owned.push_back(w32);
         launch_repack_convT_w(c, s, w, Cin, Cout, k, u, w32);
         d.w32 = w32; d.bias = bias;
-        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d, split != 0);
         Q = T + 1; So = (long)T * u;
     } else {
-        d = make_conv(c, s, w, bias, Cout, Cin, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr);
+        d = make_conv(c, s, w, bias, Cout, Cin, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, split != 0);
     }
     ConvIO io;
     io.X = x; io.x_ld = Cin; io.x_bs = (long)T * Cin; io.Tin = T; io.Y = y; io.y_bs = So * Cout; io.y_limit = So * Cout;

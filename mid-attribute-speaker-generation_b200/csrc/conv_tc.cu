@@ -19,6 +19,11 @@
 //     one thread with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx) through a 4-stage ring.
 //   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators;
 //     tcgen05.commit releases weight stages / activation buffers and finally signals the epilogue.
+//   * split mode (FastSpeech2 layers): both operands are carried as bf16 hi + bf16 lo (x = hi + lo to 16 mantissa
+//     bits) and each K step issues three MMAs, hi*hi + lo*hi + hi*lo, into the same fp32 accumulator.  That keeps
+//     the bucketize / duration-rounding decisions and the mel within 1e-4 of the fp32 oracle while still running
+//     on the bf16 tensor pipe (plain bf16 operands give a 0.45 max-abs mel error on random-init weights because
+//     pitch/energy bucket indices flip).  HiFi-GAN layers use plain bf16.
 //   * 4 epilogue warps read TMEM (tcgen05.ld 32x32b), add bias, apply the activation, residuals and scale, and
 //     store fp32 and/or bf16 rows.
 #include "common.cuh"
@@ -44,7 +49,7 @@ struct TcArgs {
     const bf16* Wt; const float* bias; int bias_mod;
     int Cin, N, taps, off0, tstep;
     int KW, KC, G, n_abuf, a_bytes, stage_bytes, blob_bytes, n_blobs;
-    int msub, rows, Rp, off_lo, tmem_cols;
+    int msub, rows, Rp, off_lo, tmem_cols, split, a_half;
     float* Y; bf16* Y16; long y_bs; long y_limit; long orow; long ooff; int Q;
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale;
@@ -124,8 +129,9 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
 // A staging: one 16-byte piece = 8 consecutive channels of one row
 // ---------------------------------------------------------------------------------------------
 template <bool XF32>
-__device__ __forceinline__ uint4 load_piece(const TcArgs& a, const uint8_t* Xb, int t, int ch) {
+__device__ __forceinline__ uint4 load_piece(const TcArgs& a, const uint8_t* Xb, int t, int ch, uint4& lo) {
     uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    lo = o;
     if (t < 0 || t >= a.Tin) return o;
     float f[8];
     if (XF32) {
@@ -143,6 +149,11 @@ __device__ __forceinline__ uint4 load_piece(const TcArgs& a, const uint8_t* Xb, 
         for (int i = 0; i < 8; ++i) f[i] = act_apply(f[i], a.in_act, a.in_slope);
     }
     o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+    if (XF32 && a.split) {                                  // residual of the bf16 rounding, itself rounded to bf16
+        float2 h0 = unpack_bf16(o.x), h1 = unpack_bf16(o.y), h2 = unpack_bf16(o.z), h3 = unpack_bf16(o.w);
+        lo.x = pack_bf16(f[0] - h0.x, f[1] - h0.y); lo.y = pack_bf16(f[2] - h1.x, f[3] - h1.y);
+        lo.z = pack_bf16(f[4] - h2.x, f[5] - h2.y); lo.w = pack_bf16(f[6] - h3.x, f[7] - h3.y);
+    }
     return o;
 }
 
@@ -196,17 +207,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const int ch0 = kc * a.KC;
             int r = tid / cpr, cc = tid % cpr;
             for (int i = tid; i < total; i += 4 * A_THREADS) {
-                uint4 v[4]; int rr[4], cs[4];
+                uint4 v[4], vl[4]; int rr[4], cs[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     rr[u] = r; cs[u] = cc;
-                    v[u] = (i + u * A_THREADS < total) ? load_piece<XF32>(a, Xb, q_lo + r, ch0 + cc * 8) : make_uint4(0u, 0u, 0u, 0u);
+                    vl[u] = make_uint4(0u, 0u, 0u, 0u);
+                    v[u] = (i + u * A_THREADS < total) ? load_piece<XF32>(a, Xb, q_lo + r, ch0 + cc * 8, vl[u]) : make_uint4(0u, 0u, 0u, 0u);
                     r += dr; cc += dc;
                     if (cc >= cpr) { cc -= cpr; ++r; }
                 }
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
-                    if (i + u * A_THREADS < total) *reinterpret_cast<uint4*>(dst + ((size_t)cs[u] * a.Rp + rr[u]) * 16) = v[u];
+                    if (i + u * A_THREADS < total) {
+                        const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
+                        *reinterpret_cast<uint4*>(dst + o) = v[u];
+                        if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl[u];
+                    }
             }
             fence_proxy_async();                          // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(A_FULL(buf));
@@ -245,10 +261,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     const int rowoff = a.off0 + j * a.tstep - a.off_lo;
                     for (int ks = 0; ks < a.KW / 16; ++ks) {
                         const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
-                        const uint64_t bdesc = umma_desc(wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo, w_lbo, 128u);
+                        const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
+                        const uint64_t bdesc = umma_desc(waddr, w_lbo, 128u);
                         const uint32_t acc = (blob > 0 || ks > 0) ? 1u : 0u;
-                        for (int ms = 0; ms < a.msub; ++ms)
-                            tc_mma(tmem_base + (uint32_t)(ms * NT), umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u), bdesc, idesc, acc);
+                        if (!a.split) {
+                            for (int ms = 0; ms < a.msub; ++ms)
+                                tc_mma(tmem_base + (uint32_t)(ms * NT), umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u), bdesc, idesc, acc);
+                        } else {
+                            const uint64_t bdesc_lo = umma_desc(waddr + (uint32_t)(a.blob_bytes >> 1), w_lbo, 128u);
+                            for (int ms = 0; ms < a.msub; ++ms) {
+                                const uint64_t ad_hi = umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u);
+                                const uint64_t ad_lo = umma_desc(aaddr + (uint32_t)a.a_half + (uint32_t)ms * 2048u, a_lbo, 128u);
+                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
+                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
+                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
+                            }
+                        }
                     }
                     if (rem == blobs_per_chunk - 1) tc_commit(A_EMPTY(buf));     // chunk consumed -> producers may overwrite
                 }
@@ -333,8 +361,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     }
 }
 
-// fp32 GEMM-B matrix [taps*Cin][N] -> bf16 blobs [N/NT][Cin/KW][taps][KW/8][NT][8]
-__global__ void k_tile_w(const float* __restrict__ w32, bf16* __restrict__ out, int Cin, int N, int taps, int NT, int KW) {
+// fp32 GEMM-B matrix [taps*Cin][N] -> bf16 blobs [N/NT][Cin/KW][taps][P][KW/8][NT][8]; P = 1, or 2 = (hi, lo) when split
+__global__ void k_tile_w(const float* __restrict__ w32, bf16* __restrict__ out, int Cin, int N, int taps, int NT, int KW, int split) {
     long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
     long total = (long)taps * Cin * N;
     if (i >= total) return;
@@ -344,7 +372,12 @@ __global__ void k_tile_w(const float* __restrict__ w32, bf16* __restrict__ out, 
     int j = (int)(r % taps); r /= taps;
     int ci = (int)(r % (Cin / KW)); int t = (int)(r / (Cin / KW));
     long row = (long)j * Cin + (long)ci * KW + k8 * 8 + e;
-    out[i] = __float2bfloat16_rn(w32[row * N + (long)t * NT + n]);
+    float w = w32[row * N + (long)t * NT + n];
+    bf16 hi = __float2bfloat16_rn(w);
+    if (!split) { out[i] = hi; return; }
+    long blob = i / ((long)KW * NT), within = i % ((long)KW * NT);
+    out[blob * 2 * KW * NT + within] = hi;
+    out[blob * 2 * KW * NT + (long)KW * NT + within] = __float2bfloat16_rn(w - __bfloat162float(hi));
 }
 
 template <int NT, bool XF32>
@@ -356,7 +389,7 @@ void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
 
 }  // namespace
 
-void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d) {
+void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
     MASG_CHECK(d.w32 != nullptr, "tc_prepare_weights: fp32 GEMM weights missing");
     int NT = 0;
     const int cands[5] = {256, 128, 80, 64, 32};
@@ -364,14 +397,15 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d) {
     MASG_CHECK(NT != 0, "conv_tc: N=%d is not a multiple of 32/64/80/128/256 (unsupported configuration)", d.N);
     int KW = (d.Cin % 64 == 0) ? 64 : (d.Cin % 32 == 0 ? 32 : 16);
     if (NT == 256 && KW == 64) KW = 32;                     // keep one blob <= 16 KB
+    while (split && NT * KW * 4 > W_STAGE_BYTES && KW > 16) KW /= 2;
     MASG_CHECK(d.Cin % KW == 0, "conv_tc: Cin=%d must be a multiple of 16", d.Cin);
     size_t n = (size_t)d.taps * d.Cin * d.N;
     bf16* w16 = nullptr;
-    CUDA_OK(cudaMalloc(&w16, n * sizeof(bf16)));
+    CUDA_OK(cudaMalloc(&w16, n * sizeof(bf16) * (split ? 2 : 1)));
     c->owned.push_back(w16);
-    k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, w16, d.Cin, d.N, d.taps, NT, KW);
+    k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, w16, d.Cin, d.N, d.taps, NT, KW, split ? 1 : 0);
     c->launches++;
-    d.w16 = w16; d.NT = NT; d.KW = KW;
+    d.w16 = w16; d.NT = NT; d.KW = KW; d.split = split ? 1 : 0;
 }
 
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
@@ -383,8 +417,10 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
     a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
-    a.KW = d.KW;
+    a.KW = d.KW; a.split = d.split;
+    MASG_CHECK(!d.split || !io.x_bf16, "conv_tc: split-bf16 layers take fp32 activations");
     const int NT = d.NT;
+    const size_t a_mul = d.split ? 2 : 1;
     int off_lo = d.off0, off_hi = d.off0;
     for (int j = 0; j < d.taps; ++j) { int o = d.off0 + j * d.tstep; off_lo = std::min(off_lo, o); off_hi = std::max(off_hi, o); }
     const int halo = off_hi - off_lo;
@@ -404,13 +440,13 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
             while ((rp % 8) != want && !(cpr >= 8 && (rp & 1))) ++rp;
             return rp;
         };
-        if ((size_t)pad_rows(d.Cin) * d.Cin * 2 <= (size_t)A_BUDGET) { KC = d.Cin; n_abuf = 1; Rp = pad_rows(KC); }
+        if ((size_t)pad_rows(d.Cin) * d.Cin * 2 * a_mul <= (size_t)A_BUDGET) { KC = d.Cin; n_abuf = 1; Rp = pad_rows(KC); }
         else {
             for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
                 if ((d.Cin / d.KW) % m) continue;
                 const int kc = m * d.KW;
                 if (kc == d.Cin) continue;
-                if ((size_t)pad_rows(kc) * kc * 2 * 2 <= (size_t)A_BUDGET) { KC = kc; n_abuf = 2; Rp = pad_rows(kc); }
+                if ((size_t)pad_rows(kc) * kc * 2 * 2 * a_mul <= (size_t)A_BUDGET) { KC = kc; n_abuf = 2; Rp = pad_rows(kc); }
             }
         }
         if (KC || msub == 1) break;
@@ -418,8 +454,9 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     }
     MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
     a.msub = msub; a.rows = msub * 128 + halo; a.Rp = Rp; a.KC = KC; a.n_abuf = n_abuf;
-    a.a_bytes = (((KC / 8) * Rp * 16) + 127) & ~127;
-    a.blob_bytes = d.KW * NT * 2;
+    a.a_half = (((KC / 8) * Rp * 16) + 127) & ~127;
+    a.a_bytes = a.a_half * (int)a_mul;
+    a.blob_bytes = d.KW * NT * 2 * (int)a_mul;
     a.G = std::max(1, W_STAGE_BYTES / a.blob_bytes);
     a.stage_bytes = a.G * a.blob_bytes;
     a.n_blobs = (d.Cin / d.KW) * d.taps;

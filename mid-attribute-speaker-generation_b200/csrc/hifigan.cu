@@ -6,7 +6,7 @@
 #include "tc.cuh"
 
 ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
-                   const float* scale, const float* bias_override);
+                   const float* scale, const float* bias_override, bool split);
 
 template <typename T> static T* dev_alloc(masg_ctx* c, size_t n) {
     T* p = nullptr;
@@ -40,7 +40,7 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
     std::vector<int64_t> sh;
     const float* w = folded_weight(c, s, "conv_pre", sh);
     MASG_CHECK(sh[0] == 512 && sh[1] == 80 && sh[2] == 7, "conv_pre must be (512,80,7): unsupported generator config");
-    c->hg_pre = make_conv(c, s, w, bias_of(c, "conv_pre", 512), 512, 80, 7, 3, 1, nullptr, nullptr);
+    c->hg_pre = make_conv(c, s, w, bias_of(c, "conv_pre", 512), 512, 80, 7, 3, 1, nullptr, nullptr, false);
     for (int i = 0; i < 4; ++i) {
         std::string name = "ups." + std::to_string(i);
         int cin = c->hg_ch[i], cout = c->hg_ch[i + 1], k = c->hg_up_k[i], u = c->hg_up_rate[i];
@@ -52,7 +52,7 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
         float* w32 = dev_alloc<float>(c, (size_t)2 * cin * u * cout);
         launch_repack_convT_w(c, s, w, cin, cout, k, u, w32);
         d.w32 = w32; d.bias = bias_of(c, name, cout);
-        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d);
+        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d, false);
         c->hg_ups[i] = d;
         for (int j = 0; j < 3; ++j) {
             int rb = i * 3 + j, kk = c->hg_rk[j];
@@ -62,10 +62,10 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
                 std::string n2 = "resblocks." + std::to_string(rb) + ".convs2." + std::to_string(mth);
                 w = folded_weight(c, s, n1, sh);
                 MASG_CHECK(sh[0] == cout && sh[1] == cout && sh[2] == kk, "%s has an unsupported shape", n1.c_str());
-                c->hg_c1[rb][mth] = make_conv(c, s, w, bias_of(c, n1, cout), cout, cout, kk, (kk * dil - dil) / 2, dil, nullptr, nullptr);
+                c->hg_c1[rb][mth] = make_conv(c, s, w, bias_of(c, n1, cout), cout, cout, kk, (kk * dil - dil) / 2, dil, nullptr, nullptr, false);
                 w = folded_weight(c, s, n2, sh);
                 MASG_CHECK(sh[0] == cout && sh[1] == cout && sh[2] == kk, "%s has an unsupported shape", n2.c_str());
-                c->hg_c2[rb][mth] = make_conv(c, s, w, bias_of(c, n2, cout), cout, cout, kk, (kk - 1) / 2, 1, nullptr, nullptr);
+                c->hg_c2[rb][mth] = make_conv(c, s, w, bias_of(c, n2, cout), cout, cout, kk, (kk - 1) / 2, 1, nullptr, nullptr, false);
             }
         }
     }

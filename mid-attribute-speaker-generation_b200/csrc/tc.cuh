@@ -3,6 +3,7 @@
 #include "common.cuh"
 
 // bf16 pre-tiled weight copy of a ConvDesc (called at commit in MASG_PREC_BF16 mode): fills d.w16/NT/KW.
-void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d);
+// split: carry the weights as bf16 hi + lo and issue 3 MMAs per K step (FastSpeech2 layers; ~fp32 accuracy)
+void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split);
 // same row-GEMM contract as launch_conv_f32 (see ConvDesc / ConvIO in common.cuh)
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);

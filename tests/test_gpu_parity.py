@@ -373,13 +373,14 @@ CONV_CASES = [
 ]
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16-split"])
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_conv_kernel_matches_torch(precision, case):
     import torch.nn.functional as F
     from masg_b200 import _lib
     B, T, Cin, Cout, k, dil, ups, slope, act = case
-    cx = _lib.default_context(DEV, precision)
+    split = precision == "bf16-split"
+    cx = _lib.default_context(DEV, "bf16" if split else precision)
     g = torch.Generator().manual_seed(hash(case) % 1000)
     x = torch.randn(B, T, Cin, generator=g)
     w = torch.randn((Cin, Cout, k) if ups else (Cout, Cin, k), generator=g) / (Cin * (2 if ups else k)) ** 0.5
@@ -393,8 +394,8 @@ def test_conv_kernel_matches_torch(precision, case):
     xg, wg, bg = x.to(DEV), w.to(DEV), bias.to(DEV)
     y = torch.full(ref.shape, 7.0, device=DEV)
     ms = ctypes.c_float(0)
-    cx.check(cx.lib.masg_conv1d(cx.h, cx.stream(), P(xg), B, T, Cin, P(wg), P(bg), Cout, k, dil, ups, slope, act, 1, P(y),
+    cx.check(cx.lib.masg_conv1d(cx.h, cx.stream(), P(xg), B, T, Cin, P(wg), P(bg), Cout, k, dil, ups, slope, act, int(split), 1, P(y),
                                 ctypes.byref(ms)), "conv1d")
     err = (y.cpu() - ref).abs().max().item()
     print("conv %s %s: max-abs err %.3e, %.3f ms" % (precision, case, err, ms.value))
-    assert err <= (2e-4 if precision == "fp32" else 4e-2)
+    assert err <= {"fp32": 2e-4, "bf16-split": 2e-4, "bf16": 4e-2}[precision]
