@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""Benchmark of the batched synthesis hot path (BASELINE.json: audio-sec/sec, FS2 + HiFi-GAN, bs64).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision bf16|fp32]
+
+One "step" = one pass of the hot path over one synthetic batch of config 3 (BASELINE.json configs[2]):
+64 speakers (32 sampled from the TacoSpawn GMM prior + 32 from InterpolateGMM mid-attribute priors) x 200
+phonemes -> FastSpeech2 (3 frames/phoneme, T = 600) -> HiFi-GAN -> int16 waveforms (445.8 s of audio).
+N > 1 (launched by torch.distributed.run, one rank per GPU): every rank runs its own 64-utterance batch
+(weak scaling, no data-path collective); the time is the max over ranks.
+
+Printed JSON (rank 0, one line): `value` = audio-s/s with inputs resident in HBM, device-timed with CUDA
+events; `e2e` = the same metric through the host-buffer C-ABI call (masg_synthesize_host: H2D of ids/lengths/
+embeddings, D2H of int16 audio inside the timed region); `roofline` = the tcgen05 implicit-GEMM kernel's
+achieved algorithmic TFLOP/s, measured with per-launch CUDA events on one extra identical step, against
+MEASURED_PEAKS.json; `cpu_baseline` = the CPU oracle (oracle/restate.py, the reference's fp32 PyTorch
+algorithm) on a bounded sample on this box's host cores.
+
+--impl reference: the reference's CPU path (the oracle port; /root/reference itself cannot travel to the
+GPU box) timed on all host threads, each step a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "audio-sec/sec (FS2+HiFi-GAN, bs64)"
+UNIT = "audio-s/s"
+B_C3, L_C3 = 64, 200
+WORKLOAD = "C3: 64 sampled/interpolated speakers x 200 phonemes, FastSpeech2 + HiFi-GAN, 3 frames/phoneme (T=600), int16 audio out"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"tflops": d.get("bf16_tflops_sustained", 1400.0), "hbm": d.get("hbm_gbs", 6650.0), "src": "measured (MEASURED_PEAKS.json, sustained bf16)"}
+    return {"tflops": 1400.0, "hbm": 6650.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, reasons, mx = [], set(), None
+        try:
+            for line in open(self.path):
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1])); mx = float(c[2])
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def _dist_setup(n_gpus):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if n_gpus > 1 and world == 1:
+        # plain `python bench.py --gpus N`: re-launch under torch.distributed.run, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n_gpus), "--master-addr", "127.0.0.1",
+               "--master-port", os.environ.get("MASTER_PORT", "29531"), os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return world, rank, local
+
+
+# ----------------------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the oracle port on the host cores (the only place bench.py executes oracle/)
+# ----------------------------------------------------------------------------------------------------------
+def cpu_reference_run(n_utts, L, reps, warm=True):
+    import torch
+    import masg_b200  # noqa: F401
+    from masg_b200 import synthetic as syn
+    from oracle import restate
+    torch.set_num_threads(os.cpu_count() or 1)
+    sd = syn.make_fs2_state_dict(seed=1234, duration_mode="fixed3")
+    hsd = restate.fold_weight_norm(syn.make_hifigan_state_dict(seed=4321))
+
+    def run(b, emb):
+        out = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], b["max_src_len"], emb)
+        wav = restate.hifigan_forward(hsd, out[1].transpose(1, 2))
+        restate.wav_to_int16(wav.squeeze(1))
+        return float(out[9].sum()) * syn.HOP / syn.SAMPLING_RATE
+
+    g = torch.Generator().manual_seed(1)
+    if warm:
+        run(syn.make_batch(1, 16, seed=3), torch.randn(1, 256, generator=g) * 0.5)
+    b = syn.make_batch(n_utts, L, seed=1234 + 2)
+    emb = torch.randn(n_utts, 256, generator=g) * 0.5
+    times, audio = [], 0.0
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        audio = run(b, emb)
+        times.append(time.perf_counter() - t0)
+    return audio, times, torch.get_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n_utts = 2
+    audio, times, cores = cpu_reference_run(n_utts, L_C3, args.warmup + args.steps)
+    timed = times[args.warmup:]
+    sec = sum(timed) / len(timed)
+    val = audio / sec
+    sample = "%d of the 64 utterances of the C3 batch per step (200 phonemes, 600 frames each), fp32 PyTorch CPU ops, %d threads" % (n_utts, cores)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------------------
+def build_models(precision, device):
+    import torch
+    import masg_b200  # noqa: F401
+    from masg_b200 import synthetic as syn
+    from masg_b200.fastspeech2 import FastSpeech2
+    from masg_b200.hifigan import Generator, AttrDict
+    from masg_b200.synth import Synthesizer
+    d = tempfile.mkdtemp(prefix="masg_cfg_")
+    json.dump(syn.speakers_json(), open(os.path.join(d, "speakers.json"), "w"))
+    json.dump(syn.STATS_JSON, open(os.path.join(d, "stats.json"), "w"))
+    fs2 = FastSpeech2(syn.PREPROCESS_CONFIG, syn.MODEL_CONFIG, d, precision=precision)
+    fs2.load_state_dict(syn.make_fs2_state_dict(seed=1234, duration_mode="fixed3"))
+    fs2.eval().to(device)
+    voc = Generator(AttrDict(syn.HIFIGAN_CONFIG), precision=precision)
+    voc.load_state_dict(syn.make_hifigan_state_dict(seed=4321))
+    voc.eval()
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()):
+        voc.remove_weight_norm()
+    voc.to(device)
+    return fs2, voc, Synthesizer(fs2, voc, precision)
+
+
+class SpeakerSampler:
+    """Config-3 speaker set, one batch per call: 32 embeddings from speaker_gen (8 per metadata combo) + 32 from the
+    InterpolateGMM mid-attribute priors over the 6 unordered combo pairs x t in {.25,.5,.75}.
+    The priors are built once (as the reference loads a pickled distribution once); sampling runs every step."""
+
+    def __init__(self, fs2, n_sampled, n_interp, seed):
+        import torch
+        from masg_b200 import synthetic as syn
+        from masg_b200.distributions import InterpolateGMM
+        self.fs2, self.ctx, self.seed, self.calls = fs2, fs2._context(), seed, 0
+        dev = self.ctx.device
+        self.meta = torch.tensor([syn.META_COMBOS[i % 4] for i in range(n_sampled)], dtype=torch.float32, device=dev)
+        combos = torch.tensor(syn.META_COMBOS, dtype=torch.float32, device=dev)
+        dists = [fs2.speaker_distribution(combos[i:i + 1]) for i in range(4)]
+        pairs = [(a, b) for a in range(4) for b in range(a + 1, 4)]
+        rates = (0.25, 0.5, 0.75)
+        cache, pis, mus, scs = {}, [], [], []
+        for i in range(n_interp):
+            a, b = pairs[i % len(pairs)]
+            t = rates[(i // len(pairs)) % len(rates)]
+            if (a, b) not in cache:
+                cache[(a, b)] = InterpolateGMM(dists[a], dists[b])
+            ig = cache[(a, b)]
+            ig.interpolate_rate(t)
+            comp = ig.component_distribution.base_dist
+            pis.append(ig.mixture_distribution.probs.reshape(1, -1).clone())
+            mus.append(comp.loc.reshape(1, -1, 256).clone())
+            scs.append(comp.scale.reshape(1, -1, 256).clone())
+        self.n_interp = n_interp
+        if n_interp:
+            self.pi, self.mu, self.sc = torch.cat(pis).contiguous(), torch.cat(mus).contiguous(), torch.cat(scs).contiguous()
+
+    def sample(self):
+        import torch
+        from masg_b200.fastspeech2 import gmm_sample
+        self.calls += 1
+        embs = [self.fs2.speaker_gen(self.meta, seed=self.seed + 2 * self.calls)]
+        if self.n_interp:
+            embs.append(gmm_sample(self.ctx, self.pi, self.mu, self.sc, self.n_interp, seed=self.seed + 2 * self.calls + 1))
+        return torch.cat(embs, 0)
+
+
+def run_ours(args):
+    import torch
+    world, rank, local = _dist_setup(args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); the synthesis path has no CPU fallback")
+    import masg_b200  # noqa: F401
+    from masg_b200 import synthetic as syn
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    fs2, voc, synth = build_models(args.precision, dev)
+    ctx = synth.ctx
+    B, L = B_C3, L_C3
+    batch = syn.make_batch(B, L, seed=1234 + 2 + 1000 * rank)
+    texts, accents, lens = batch["texts"].to(dev), batch["accents"].to(dev), batch["src_lens"].to(dev)
+    sampler = SpeakerSampler(fs2, B // 2, B - B // 2, seed=77 + 100000 * rank)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)            # > 126 MB L2
+    audio_per_step = B * 3 * L * syn.HOP / syn.SAMPLING_RATE
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([x], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def step_device():
+        emb = sampler.sample()
+        w16, mel_lens, _ = synth.synthesize(texts, accents, lens, emb)
+        return w16, mel_lens
+
+    # ---- device-resident throughput -----------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    if args.profile_range:
+        # ncu --profile-from-start off: exactly one step between cudaProfilerStart/Stop, nothing else measured
+        torch.cuda.profiler.start()
+        step_device()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        if rank == 0:
+            print(json.dumps({"profile_range": "one C3 step between cudaProfilerStart/Stop", "precision": args.precision}))
+        return 0
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ctx.launch_count(reset=True)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)                                                # L2 flush between timed iterations (untimed)
+        ev[i][0].record()
+        w16, mel_lens = step_device()
+        ev[i][1].record()
+    barrier()
+    launches = ctx.launch_count()
+    ms_dev = sum(a.elapsed_time(b) for a, b in ev)
+    ms_dev = max_over_ranks(ms_dev)
+    assert int(mel_lens.sum().item()) == B * 3 * L, "unexpected mel lengths (benchmark shape is 3 frames/phoneme)"
+    value = world * audio_per_step * args.steps / (ms_dev / 1e3)
+
+    # ---- end to end through the host-buffer C-ABI call ------------------------------------------------
+    t_cap = 3 * L + 8
+    pin_emb = torch.empty(B, 256, dtype=torch.float32).pin_memory()
+    h_texts, h_acc, h_lens = batch["texts"], batch["accents"], batch["src_lens"]
+
+    def step_host():
+        emb = sampler.sample()
+        pin_emb.copy_(emb, non_blocking=True)
+        torch.cuda.current_stream().synchronize()                             # embeddings reach the host (examples_gen.py:268 does .cpu())
+        return synth.synthesize_host(h_texts, h_acc, h_lens, pin_emb, t_cap)
+
+    for _ in range(3):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        h_w, h_m, T, h2d, d2h = step_host()
+    e1.record()
+    barrier()
+    # the call blocks the host until the audio is back, so host wall-clock between the two barriers is the end-to-end time
+    # (the CUDA-event span over the same region is reported beside it)
+    ms_e2e = max_over_ranks(max((time.perf_counter() - t0) * 1e3, e0.elapsed_time(e1)))
+    e2e_value = world * audio_per_step * args.steps / (ms_e2e / 1e3)
+    d2h += B * 256 * 4                # sampled embeddings copied to the pinned host buffer (their H2D is counted by synthesize_host)
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- roofline of the dominant kernel: one extra identical step with per-launch CUDA events ---------
+    barrier()
+    ctx.profile(True)
+    step_device()
+    k_ms, k_flops, k_n = ctx.profile_read()
+    ctx.profile(False)
+    e0.record(); step_device(); e1.record(); torch.cuda.synchronize()
+    step_ms_plain = e0.elapsed_time(e1)
+    pk = _peaks()
+
+    # ---- p50 per-utterance latency (config 2: batch 1, 50 phonemes, host ids in -> int16 audio on the host) ----
+    b1 = syn.make_batch(1, 50, seed=1235, accents_const=4)
+    emb1 = sampler.sample()[:1].cpu().pin_memory()
+    lat = []
+    for i in range(25):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        synth.synthesize_host(b1["texts"], b1["accents"], b1["src_lens"], emb1, 160)
+        lat.append((time.perf_counter() - t0) * 1e3)
+    lat = sorted(lat[5:])
+
+    if rank != 0:
+        return 0
+    # ---- CPU baseline (oracle port) on this box's host cores, bounded sample, N = 1 only ----------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        audio, times, cores = cpu_reference_run(2, L, 1)
+        cpu = {"value": audio / times[-1], "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "2 of the 64 C3 utterances (200 phonemes, 600 frames each), one pass after a tiny warm-up, fp32 PyTorch CPU ops"}
+    ach = k_flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "global_batch": B * world, "phonemes": L, "frames_per_utt": 3 * L, "parallelism": "dp%d" % world,
+                   "precision": args.precision + (" (HiFi-GAN plain bf16; FastSpeech2 split-bf16 hi/lo, 3 MMAs per K step)" if args.precision == "bf16" else ""),
+                   "weights": "seeded random init (no checkpoint in the reference tree)",
+                   "l2": "256 MiB flush buffer written before every timed step; activations (GBs per step) far exceed the 126 MB L2"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "roofline": {"bound": "tensor", "kernel": "k_conv_tc (tcgen05 implicit-GEMM conv1d/linear/convT)", "achieved": ach, "peak": pk["tflops"],
+                     "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": None, "peak_source": pk["src"],
+                     "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": step_ms_plain,
+                     "share_of_step": k_ms / step_ms_plain if step_ms_plain else None,
+                     "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per launch"},
+        "cpu_baseline": cpu,
+        "latency_p50_ms": {"value": lat[len(lat) // 2], "config": "C2: batch 1, 50 phonemes, host ids -> int16 audio on host (masg_synthesize_host), 20 runs"},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-range", action="store_true", help="warm up, then run ONE step inside cudaProfilerStart/Stop and exit (for ncu)")
+    args = ap.parse_args()
+    import __graft_entry__
+    __graft_entry__.build_if_needed()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -143,6 +143,13 @@ int masg_conv1d(masg_ctx* ctx, void* stream, const float* x, int B, int T, int C
                 int Cout, int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int split,
                 int reps, float* y, float* h_ms);
 
+/* Roofline accounting for bench.py (no reference counterpart): while enabled, every launch of the dense-
+ * contraction kernel is bracketed by CUDA events on its stream and its algorithmic FLOPs (2 x rows x K x N) are
+ * recorded.  masg_profile_read synchronises the stream, returns the summed device milliseconds, FLOPs and the
+ * launch count since the last read, and clears the records. */
+int masg_profile(masg_ctx* ctx, int enable);
+int masg_profile_read(masg_ctx* ctx, void* stream, double* h_ms_total, double* h_flops_total, int64_t* h_launches);
+
 /* Counters for the benchmark harness: number of kernels this context launched since the last reset. */
 int64_t masg_launch_count(masg_ctx* ctx, int reset);
 /* Intermediate tap for parity tests: copies a named internal fp32 buffer of the last forward

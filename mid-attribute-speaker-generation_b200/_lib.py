@@ -41,6 +41,8 @@ SIGNATURES = {
                                      ctypes.POINTER(c_i64)]),
     "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, c_int, P,
                             ctypes.POINTER(c_float)]),
+    "masg_profile": (c_int, [P, c_int]),
+    "masg_profile_read": (c_int, [P, P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64)]),
     "masg_launch_count": (c_i64, [P, c_int]),
     "masg_debug_tap": (c_int, [P, P, c_char_p, P, c_i64]),
 }
@@ -127,6 +129,16 @@ class Context:
 
     def launch_count(self, reset=False):
         return int(self.lib.masg_launch_count(self.h, 1 if reset else 0))
+
+    def profile(self, enable):
+        self.check(self.lib.masg_profile(self.h, 1 if enable else 0), "masg_profile")
+
+    def profile_read(self):
+        """→ (device ms, algorithmic FLOPs, launches) of the dense-contraction kernel since the last read."""
+        ms, fl, n = ctypes.c_double(0), ctypes.c_double(0), c_i64(0)
+        self.check(self.lib.masg_profile_read(self.h, self.stream(), ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(n)),
+                   "masg_profile_read")
+        return ms.value, fl.value, int(n.value)
 
     def tap(self, name, shape):
         out = torch.empty(shape, dtype=torch.float32, device=self.device)

@@ -333,6 +333,27 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     API_END(c)
 }
 
+int masg_profile(masg_ctx* c, int enable) {
+    API_BEGIN(c)
+    c->profiling = enable != 0;
+    API_END(c)
+}
+int masg_profile_read(masg_ctx* c, void* stream, double* h_ms_total, double* h_flops_total, int64_t* h_launches) {
+    API_BEGIN(c)
+    CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    double ms = 0, fl = 0;
+    for (auto& r : c->prof) {
+        float t = 0.f; CUDA_OK(cudaEventElapsedTime(&t, r.e0, r.e1));
+        ms += t; fl += r.flops;
+        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+    }
+    if (h_ms_total) *h_ms_total = ms;
+    if (h_flops_total) *h_flops_total = fl;
+    if (h_launches) *h_launches = (int64_t)c->prof.size();
+    c->prof.clear();
+    API_END(c)
+}
+
 int64_t masg_launch_count(masg_ctx* c, int reset) {
     if (!c) return -1;
     int64_t n = c->launches;

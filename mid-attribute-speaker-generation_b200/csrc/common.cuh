@@ -72,6 +72,10 @@ struct masg_ctx {
     int device = 0, precision = 0;
     std::string err;
     int64_t launches = 0;
+    // per-launch device timing of the dense-contraction kernel (masg_profile): event pairs + algorithmic FLOPs
+    bool profiling = false;
+    struct ProfRec { cudaEvent_t e0, e1; double flops; };
+    std::vector<ProfRec> prof;
     Arena arena;                      // per-forward workspace
     std::vector<void*> owned;         // repacked weights
     std::map<std::string, TensorRef> fs2_t, hg_t;

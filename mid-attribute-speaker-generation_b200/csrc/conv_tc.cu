@@ -483,6 +483,13 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
 }
 
 void launch_conv(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
+    masg_ctx::ProfRec rec;
+    if (c->profiling) {
+        CUDA_OK(cudaEventCreate(&rec.e0)); CUDA_OK(cudaEventCreate(&rec.e1));
+        rec.flops = 2.0 * io.B * (double)io.Q * d.taps * d.Cin * d.N;      // algorithmic: one multiply-add per (row, k, n)
+        CUDA_OK(cudaEventRecord(rec.e0, s));
+    }
     if (c->precision == MASG_PREC_BF16) launch_conv_tc(c, s, d, io);
     else launch_conv_f32(c, s, d, io);
+    if (c->profiling) { CUDA_OK(cudaEventRecord(rec.e1, s)); c->prof.push_back(rec); }
 }
