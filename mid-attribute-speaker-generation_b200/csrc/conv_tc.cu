@@ -8,7 +8,10 @@
 // predictor convs (model/modules.py:209-240), mel_linear (model/fastspeech2.py:242), PostNet (transformer/
 // Layers.py:129-137) and every Conv1d / ConvTranspose1d of the HiFi-GAN generator (hifigan/models.py:149-165).
 //
-// One CTA computes a (128*msub rows) x (NT columns) output tile of one utterance:
+// Persistent, warp-specialised kernel: one CTA per SM walks a list of (128*msub rows) x (NT columns) output tiles
+// (tile = one utterance's row range x one column tile).  Activation staging, weight streaming, MMA issue and the
+// epilogue run as four concurrent roles connected by mbarrier rings, and the TMEM accumulators are double-buffered,
+// so the epilogue of tile i overlaps the loads and MMAs of tile i+1:
 //   * A operand (activations): the tile's rows PLUS the conv halo are staged ONCE per channel chunk in shared memory
 //     in the UMMA no-swizzle K-major layout [KC/8][Rp rows][8 ch] (16-byte pieces).  In that layout a conv tap is a
 //     16-byte-granular shift of the descriptor start address, so all taps (and dilations, and the two taps of a
@@ -17,39 +20,43 @@
 //     leaky-relu on the way (hifigan/models.py:98,100,152), zero-filling rows outside [0, Tin) (= conv padding).
 //   * B operand (weights): pre-tiled at commit (k_tile_w) into contiguous blobs already in UMMA layout, streamed by
 //     one thread with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx) through a 4-stage ring.
-//   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators;
-//     tcgen05.commit releases weight stages / activation buffers and finally signals the epilogue.
+//   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators of the
+//     current accumulator set; tcgen05.commit releases weight stages / activation slots and signals the epilogue.
 //   * split mode (FastSpeech2 layers): both operands are carried as bf16 hi + bf16 lo (x = hi + lo to 16 mantissa
 //     bits) and each K step issues three MMAs, hi*hi + lo*hi + hi*lo, into the same fp32 accumulator.  That keeps
 //     the bucketize / duration-rounding decisions and the mel within 1e-4 of the fp32 oracle while still running
 //     on the bf16 tensor pipe (plain bf16 operands give a 0.45 max-abs mel error on random-init weights because
 //     pitch/energy bucket indices flip).  HiFi-GAN layers use plain bf16.
-//   * 4 epilogue warps read TMEM (tcgen05.ld 32x32b), add bias, apply the activation, residuals and scale, and
-//     store fp32 and/or bf16 rows.
+//   * 8 epilogue warps (two per TMEM lane quadrant, half the columns each) prefetch the residual rows, read TMEM
+//     (tcgen05.ld 32x32b), add the smem-staged bias, apply the activation, residuals and scale, store fp32 and/or bf16
+//     rows and hand the accumulator set back to the MMA thread.
 #include "common.cuh"
 #include "tc.cuh"
 
 namespace {
 
-constexpr int EPI_WARPS = 4;
-constexpr int MMA_WARP = 4;
-constexpr int W_WARP = 5;
-constexpr int A_WARP0 = 6;
+// warp roles of the persistent CTA (576 threads, one CTA per SM)
+constexpr int EPI_WARPS = 8;            // warps 0-7: epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column half)
+constexpr int MMA_WARP = 8;
+constexpr int W_WARP = 9;
+constexpr int A_WARP0 = 10;
 constexpr int A_WARPS = 8;
 constexpr int A_THREADS = A_WARPS * 32;
-constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 448
+constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 576
 constexpr int W_STAGES = 4;
 constexpr int W_STAGE_BYTES = 16384;
 constexpr int SMEM_HDR = 1024;
-constexpr int A_BUDGET = 144 * 1024;
+constexpr int BIAS_MAX = 2048;                          // floats staged per CTA (N <= 2048)
+constexpr int A_SLOT_BUDGET = 72 * 1024;                // two activation slots
 constexpr int MAX_SMEM = 227 * 1024;
 
 struct TcArgs {
     const void* X; long x_bs; int x_ld; int Tin;
     const bf16* Wt; const float* bias; int bias_mod;
     int Cin, N, taps, off0, tstep;
-    int KW, KC, G, n_abuf, a_bytes, stage_bytes, blob_bytes, n_blobs;
+    int KW, KC, G, a_bytes, stage_bytes, blob_bytes, n_blobs;
     int msub, rows, Rp, off_lo, tmem_cols, split, a_half;
+    int B, row_tiles, n_ntiles, total_tiles;
     float* Y; bf16* Y16; long y_bs; long y_limit; long orow; long ooff; int Q;
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale;
@@ -160,29 +167,34 @@ __device__ __forceinline__ uint4 load_piece(const TcArgs& a, const uint8_t* Xb, 
 template <int NT, bool XF32>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    // header: mbarriers + TMEM base
+    // header: mbarriers + TMEM base; then the bias row, the two activation slots and the weight ring
     const uint32_t bar0 = smem_u32(smem);
-    auto A_FULL = [&](int i) { return bar0 + 8u * i; };             // 2
-    auto A_EMPTY = [&](int i) { return bar0 + 8u * (2 + i); };      // 2
-    auto W_FULL = [&](int i) { return bar0 + 8u * (4 + i); };       // W_STAGES
-    auto W_EMPTY = [&](int i) { return bar0 + 8u * (4 + W_STAGES + i); };
-    const uint32_t ACC_FULL = bar0 + 8u * (4 + 2 * W_STAGES);
+    auto A_FULL = [&](int i) { return bar0 + 8u * i; };                       // 2
+    auto A_EMPTY = [&](int i) { return bar0 + 8u * (2 + i); };                // 2
+    auto W_FULL = [&](int i) { return bar0 + 8u * (4 + i); };                 // W_STAGES
+    auto W_EMPTY = [&](int i) { return bar0 + 8u * (4 + W_STAGES + i); };     // W_STAGES
+    auto ACC_FULL = [&](int i) { return bar0 + 8u * (4 + 2 * W_STAGES + i); };        // 2
+    auto ACC_EMPTY = [&](int i) { return bar0 + 8u * (6 + 2 * W_STAGES + i); };       // 2
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + 512);
-    uint8_t* A_smem = smem + SMEM_HDR;
-    uint8_t* W_smem = A_smem + (size_t)a.n_abuf * a.a_bytes;
+    float* bias_s = reinterpret_cast<float*>(smem + SMEM_HDR);
+    uint8_t* A_smem = smem + SMEM_HDR + BIAS_MAX * 4;
+    uint8_t* W_smem = A_smem + 2 * (size_t)a.a_bytes;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.z, n0 = blockIdx.y * NT, q0 = blockIdx.x * a.msub * 128;
     const int n_chunks = a.Cin / a.KC;
     const int blobs_per_chunk = (a.KC / a.KW) * a.taps;
     const int n_stages = (a.n_blobs + a.G - 1) / a.G;
+    const int acc_cols = a.msub * NT;                      // TMEM columns of one accumulator set (two sets)
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) { mbar_init(A_FULL(i), A_THREADS); mbar_init(A_EMPTY(i), 1); }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(A_FULL(i), A_THREADS); mbar_init(A_EMPTY(i), 1);
+            mbar_init(ACC_FULL(i), 1); mbar_init(ACC_EMPTY(i), EPI_WARPS);
+        }
         for (int i = 0; i < W_STAGES; ++i) { mbar_init(W_FULL(i), 1); mbar_init(W_EMPTY(i), 1); }
-        mbar_init(ACC_FULL, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = threadIdx.x; i < a.N; i += NTHREADS) bias_s[i] = a.bias ? a.bias[i % a.bias_mod] : 0.f;
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(a.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -192,52 +204,62 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // tile id -> (batch b, row tile rt, column tile nt); a CTA walks ids blockIdx.x, blockIdx.x + gridDim.x, ...
     if (warp >= A_WARP0) {
-        // ===== activation producers =====
+        // ===== activation producers: stage rows [q0 + off_lo, q0 + off_lo + rows) x KC channels per chunk =====
         const int tid = threadIdx.x - A_WARP0 * 32;
-        const uint8_t* Xb = reinterpret_cast<const uint8_t*>(a.X) + (size_t)b * a.x_bs * (XF32 ? 4 : 2);
         const int cpr = a.KC >> 3;                       // 16-byte pieces per row
         const int total = cpr * a.rows;
         const int dr = A_THREADS / cpr, dc = A_THREADS % cpr;
-        const int q_lo = q0 + a.off_lo;
-        for (int kc = 0; kc < n_chunks; ++kc) {
-            const int buf = kc % a.n_abuf;
-            mbar_wait(A_EMPTY(buf), ((kc / a.n_abuf) & 1) ^ 1);
-            uint8_t* dst = A_smem + (size_t)buf * a.a_bytes;
-            const int ch0 = kc * a.KC;
-            int r = tid / cpr, cc = tid % cpr;
-            for (int i = tid; i < total; i += 4 * A_THREADS) {
-                uint4 v[4], vl[4]; int rr[4], cs[4];
+        int ia = 0;                                      // running chunk counter -> slot / parity
+        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+            const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+            const uint8_t* Xb = reinterpret_cast<const uint8_t*>(a.X) + (size_t)b * a.x_bs * (XF32 ? 4 : 2);
+            const int q_lo = rt * a.msub * 128 + a.off_lo;
+            for (int kc = 0; kc < n_chunks; ++kc, ++ia) {
+                const int slot = ia & 1;
+                mbar_wait(A_EMPTY(slot), ((ia >> 1) & 1) ^ 1);
+                uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
+                const int ch0 = kc * a.KC;
+                int r = tid / cpr, cc = tid % cpr;
+                constexpr int U = XF32 ? 4 : 8;            // loads in flight per thread (fp32 pieces are 32 bytes + hi/lo)
+                for (int i = tid; i < total; i += U * A_THREADS) {
+                    uint4 v[U], vl[U]; int rr[U], cs[U];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    rr[u] = r; cs[u] = cc;
-                    vl[u] = make_uint4(0u, 0u, 0u, 0u);
-                    v[u] = (i + u * A_THREADS < total) ? load_piece<XF32>(a, Xb, q_lo + r, ch0 + cc * 8, vl[u]) : make_uint4(0u, 0u, 0u, 0u);
-                    r += dr; cc += dc;
-                    if (cc >= cpr) { cc -= cpr; ++r; }
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (i + u * A_THREADS < total) {
-                        const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
-                        *reinterpret_cast<uint4*>(dst + o) = v[u];
-                        if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl[u];
+                    for (int u = 0; u < U; ++u) {
+                        rr[u] = r; cs[u] = cc;
+                        vl[u] = make_uint4(0u, 0u, 0u, 0u);
+                        v[u] = (i + u * A_THREADS < total) ? load_piece<XF32>(a, Xb, q_lo + r, ch0 + cc * 8, vl[u]) : make_uint4(0u, 0u, 0u, 0u);
+                        r += dr; cc += dc;
+                        if (cc >= cpr) { cc -= cpr; ++r; }
                     }
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        if (i + u * A_THREADS < total) {
+                            const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
+                            *reinterpret_cast<uint4*>(dst + o) = v[u];
+                            if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl[u];
+                        }
+                }
+                fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core (async proxy)
+                mbar_arrive(A_FULL(slot));
             }
-            fence_proxy_async();                          // generic-proxy stores -> visible to the tensor core (async proxy)
-            mbar_arrive(A_FULL(buf));
         }
     } else if (warp == W_WARP) {
         // ===== weight producer: 1-D bulk copies of pre-tiled blobs =====
         if (lane == 0) {
-            const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)blockIdx.y * a.n_blobs * a.blob_bytes;
-            for (int st = 0; st < n_stages; ++st) {
-                const int slot = st % W_STAGES;
-                mbar_wait(W_EMPTY(slot), ((st / W_STAGES) & 1) ^ 1);
-                const int nb = min(a.G, a.n_blobs - st * a.G);
-                const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
-                mbar_expect_tx(W_FULL(slot), bytes);
-                bulk_g2s(smem_u32(W_smem + (size_t)slot * a.stage_bytes), src + (size_t)st * a.G * a.blob_bytes, bytes, W_FULL(slot));
+            int iw = 0;
+            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+                const int nt = tile % a.n_ntiles;
+                const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
+                for (int st = 0; st < n_stages; ++st, ++iw) {
+                    const int slot = iw % W_STAGES;
+                    mbar_wait(W_EMPTY(slot), ((iw / W_STAGES) & 1) ^ 1);
+                    const int nb = min(a.G, a.n_blobs - st * a.G);
+                    const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
+                    mbar_expect_tx(W_FULL(slot), bytes);
+                    bulk_g2s(smem_u32(W_smem + (size_t)slot * a.stage_bytes), src + (size_t)st * a.G * a.blob_bytes, bytes, W_FULL(slot));
+                }
             }
         }
     } else if (warp == MMA_WARP) {
@@ -246,111 +268,141 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             const uint32_t a_lbo = (uint32_t)a.Rp * 16u, w_lbo = (uint32_t)NT * 16u;
-            int blob = 0;
-            for (int st = 0; st < n_stages; ++st) {
-                const int slot = st % W_STAGES;
-                mbar_wait(W_FULL(slot), (st / W_STAGES) & 1);
+            int iw = 0, ia = 0, it = 0;
+            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+                const int accb = it & 1;
+                mbar_wait(ACC_EMPTY(accb), ((it >> 1) & 1) ^ 1);          // epilogue has drained this accumulator set
                 tc_fence_after();
-                const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
-                for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
-                    const int kc = blob / blobs_per_chunk, rem = blob % blobs_per_chunk;
-                    const int sub = rem / a.taps, j = rem % a.taps;
-                    const int buf = kc % a.n_abuf;
-                    if (rem == 0) { mbar_wait(A_FULL(buf), (kc / a.n_abuf) & 1); tc_fence_after(); }
-                    const uint32_t abase = smem_u32(A_smem + (size_t)buf * a.a_bytes);
-                    const int rowoff = a.off0 + j * a.tstep - a.off_lo;
-                    for (int ks = 0; ks < a.KW / 16; ++ks) {
-                        const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
-                        const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
-                        const uint64_t bdesc = umma_desc(waddr, w_lbo, 128u);
-                        const uint32_t acc = (blob > 0 || ks > 0) ? 1u : 0u;
-                        if (!a.split) {
-                            for (int ms = 0; ms < a.msub; ++ms)
-                                tc_mma(tmem_base + (uint32_t)(ms * NT), umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u), bdesc, idesc, acc);
-                        } else {
-                            const uint64_t bdesc_lo = umma_desc(waddr + (uint32_t)(a.blob_bytes >> 1), w_lbo, 128u);
-                            for (int ms = 0; ms < a.msub; ++ms) {
-                                const uint64_t ad_hi = umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u);
-                                const uint64_t ad_lo = umma_desc(aaddr + (uint32_t)a.a_half + (uint32_t)ms * 2048u, a_lbo, 128u);
-                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
-                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
-                                tc_mma(tmem_base + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
+                const uint32_t tacc = tmem_base + (uint32_t)(accb * acc_cols);
+                int blob = 0;
+                for (int st = 0; st < n_stages; ++st, ++iw) {
+                    const int slot = iw % W_STAGES;
+                    mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
+                    tc_fence_after();
+                    const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
+                    for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
+                        const int rem = blob % blobs_per_chunk;
+                        const int sub = rem / a.taps, j = rem % a.taps;
+                        const int aslot = ia & 1;
+                        if (rem == 0) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
+                        const uint32_t abase = smem_u32(A_smem + (size_t)aslot * a.a_bytes);
+                        const int rowoff = a.off0 + j * a.tstep - a.off_lo;
+                        for (int ks = 0; ks < a.KW / 16; ++ks) {
+                            const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
+                            const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
+                            const uint64_t bdesc = umma_desc(waddr, w_lbo, 128u);
+                            const uint32_t acc = (blob > 0 || ks > 0) ? 1u : 0u;
+                            if (!a.split) {
+                                for (int ms = 0; ms < a.msub; ++ms)
+                                    tc_mma(tacc + (uint32_t)(ms * NT), umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u), bdesc, idesc, acc);
+                            } else {
+                                const uint64_t bdesc_lo = umma_desc(waddr + (uint32_t)(a.blob_bytes >> 1), w_lbo, 128u);
+                                for (int ms = 0; ms < a.msub; ++ms) {
+                                    const uint64_t ad_hi = umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u);
+                                    const uint64_t ad_lo = umma_desc(aaddr + (uint32_t)a.a_half + (uint32_t)ms * 2048u, a_lbo, 128u);
+                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
+                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
+                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
+                                }
                             }
                         }
+                        if (rem == blobs_per_chunk - 1) { tc_commit(A_EMPTY(aslot)); ++ia; }   // chunk consumed -> slot may be overwritten
                     }
-                    if (rem == blobs_per_chunk - 1) tc_commit(A_EMPTY(buf));     // chunk consumed -> producers may overwrite
+                    tc_commit(W_EMPTY(slot));
                 }
-                tc_commit(W_EMPTY(slot));
+                tc_commit(ACC_FULL(accb));
             }
-            tc_commit(ACC_FULL);
         }
     } else {
-        // ===== epilogue: TMEM -> registers -> bias / activation / residual / scale -> global =====
-        mbar_wait(ACC_FULL, 0);
-        tc_fence_after();
+        // ===== epilogue (8 warps): TMEM -> registers -> bias / activation / residual / scale -> global =====
+        const int quad = warp & 3, half = warp >> 2;
+        const int c_split = ((NT / 16 + 1) / 2) * 16;
+        const int c_begin = half ? c_split : 0, c_end = half ? NT : c_split;
         const float* R1f = reinterpret_cast<const float*>(a.R1); const bf16* R1h = reinterpret_cast<const bf16*>(a.R1);
         const float* R2f = reinterpret_cast<const float*>(a.R2); const bf16* R2h = reinterpret_cast<const bf16*>(a.R2);
-        const long boff = (long)b * a.y_bs;
-        for (int ms = 0; ms < a.msub; ++ms) {
-            const int q = q0 + ms * 128 + warp * 32 + lane;
-            const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ms * NT);
-#pragma unroll 1
-            for (int c0 = 0; c0 < NT; c0 += 16) {
-                float v[16];
-                tmem_ld16(trow + (uint32_t)c0, v);
-                const long e = (long)q * a.orow + a.ooff + n0 + c0;
-                if (q < a.Q && e >= 0 && e + 16 <= a.y_limit) {
-                    const float* bp = a.bias ? a.bias + ((n0 + c0) % a.bias_mod) : nullptr;
+        const int gc = ((a.R1 || a.R2) && !a.r_bf16) ? 16 : 32;     // columns per residual prefetch group (4 x 16 bytes)
+        int it = 0;
+        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+            const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+            const int n0 = nt * NT, q0 = rt * a.msub * 128;
+            const int accb = it & 1;
+            mbar_wait(ACC_FULL(accb), (it >> 1) & 1);
+            tc_fence_after();
+            const long boff = (long)b * a.y_bs;
+            for (int ms = 0; ms < a.msub; ++ms) {
+                const int q = q0 + ms * 128 + quad * 32 + lane;
+                const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT);
+                for (int cg = c_begin; cg < c_end; cg += gc) {
+                    const int ncol = min(gc, c_end - cg);
+                    const long eg = (long)q * a.orow + a.ooff + n0 + cg;
+                    const bool rowok = q < a.Q;
+                    // prefetch the residual values of this column group (up to 4 x 16 bytes each) before touching TMEM
+                    uint4 r1[4], r2[4];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i] + (bp ? __ldg(bp + i) : 0.f), a.out_act, a.out_slope);
-                    if (a.R1) {
-                        if (a.r_bf16) {
-                            const uint4* p = reinterpret_cast<const uint4*>(R1h + boff + e);
+                    for (int h = 0; h < 4; ++h) {
+                        r1[h] = make_uint4(0u, 0u, 0u, 0u); r2[h] = r1[h];
+                        const int col = a.r_bf16 ? h * 8 : h * 4;                       // first column covered by piece h
+                        const long e = eg + (col & ~15);
+                        const bool ok = rowok && col < ncol && e >= 0 && e + 16 <= a.y_limit;
+                        if (ok && a.R1) r1[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R1h + boff + eg + col)
+                                                        : *reinterpret_cast<const uint4*>(R1f + boff + eg + col);
+                        if (ok && a.R2) r2[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R2h + boff + eg + col)
+                                                        : *reinterpret_cast<const uint4*>(R2f + boff + eg + col);
+                    }
 #pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                uint4 u = p[h]; float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
-                                v[h * 8 + 0] += t0.x; v[h * 8 + 1] += t0.y; v[h * 8 + 2] += t1.x; v[h * 8 + 3] += t1.y;
-                                v[h * 8 + 4] += t2.x; v[h * 8 + 5] += t2.y; v[h * 8 + 6] += t3.x; v[h * 8 + 7] += t3.y;
+                    for (int k16 = 0; k16 < 2; ++k16) {
+                        const int cc = k16 * 16;
+                        if (cc < ncol) {                                   // warp-uniform
+                            float v[16];
+                            tmem_ld16(trow + (uint32_t)(cg + cc), v);
+                            const long e = eg + cc;
+                            if (rowok && e >= 0 && e + 16 <= a.y_limit) {
+                                const float* bp = bias_s + n0 + cg + cc;
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i] + bp[i], a.out_act, a.out_slope);
+                                if (a.R1 || a.R2) {
+                                    if (a.r_bf16) {
+#pragma unroll
+                                        for (int h = 0; h < 2; ++h) {
+                                            const uint4 u = r1[(k16 * 2 + h) & 3], w = r2[(k16 * 2 + h) & 3];
+                                            float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
+                                            float2 s0 = unpack_bf16(w.x), s1 = unpack_bf16(w.y), s2 = unpack_bf16(w.z), s3 = unpack_bf16(w.w);
+                                            v[h * 8 + 0] += t0.x + s0.x; v[h * 8 + 1] += t0.y + s0.y; v[h * 8 + 2] += t1.x + s1.x; v[h * 8 + 3] += t1.y + s1.y;
+                                            v[h * 8 + 4] += t2.x + s2.x; v[h * 8 + 5] += t2.y + s2.y; v[h * 8 + 6] += t3.x + s3.x; v[h * 8 + 7] += t3.y + s3.y;
+                                        }
+                                    } else {
+#pragma unroll
+                                        for (int h = 0; h < 4; ++h) {
+                                            const uint4 u = r1[(k16 * 4 + h) & 3], w = r2[(k16 * 4 + h) & 3];
+                                            v[h * 4 + 0] += __uint_as_float(u.x) + __uint_as_float(w.x); v[h * 4 + 1] += __uint_as_float(u.y) + __uint_as_float(w.y);
+                                            v[h * 4 + 2] += __uint_as_float(u.z) + __uint_as_float(w.z); v[h * 4 + 3] += __uint_as_float(u.w) + __uint_as_float(w.w);
+                                        }
+                                    }
+                                }
+                                if (a.out_scale != 1.f) {
+#pragma unroll
+                                    for (int i = 0; i < 16; ++i) v[i] *= a.out_scale;
+                                }
+                                if (a.Y) {
+                                    float4* p = reinterpret_cast<float4*>(a.Y + boff + e);
+#pragma unroll
+                                    for (int h = 0; h < 4; ++h) p[h] = make_float4(v[h * 4], v[h * 4 + 1], v[h * 4 + 2], v[h * 4 + 3]);
+                                }
+                                if (a.Y16) {
+                                    uint4* p = reinterpret_cast<uint4*>(a.Y16 + boff + e);
+#pragma unroll
+                                    for (int h = 0; h < 2; ++h)
+                                        p[h] = make_uint4(pack_bf16(v[h * 8], v[h * 8 + 1]), pack_bf16(v[h * 8 + 2], v[h * 8 + 3]),
+                                                          pack_bf16(v[h * 8 + 4], v[h * 8 + 5]), pack_bf16(v[h * 8 + 6], v[h * 8 + 7]));
+                                }
                             }
-                        } else {
-                            const float4* p = reinterpret_cast<const float4*>(R1f + boff + e);
-#pragma unroll
-                            for (int h = 0; h < 4; ++h) { float4 u = p[h]; v[h * 4] += u.x; v[h * 4 + 1] += u.y; v[h * 4 + 2] += u.z; v[h * 4 + 3] += u.w; }
                         }
-                    }
-                    if (a.R2) {
-                        if (a.r_bf16) {
-                            const uint4* p = reinterpret_cast<const uint4*>(R2h + boff + e);
-#pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                uint4 u = p[h]; float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
-                                v[h * 8 + 0] += t0.x; v[h * 8 + 1] += t0.y; v[h * 8 + 2] += t1.x; v[h * 8 + 3] += t1.y;
-                                v[h * 8 + 4] += t2.x; v[h * 8 + 5] += t2.y; v[h * 8 + 6] += t3.x; v[h * 8 + 7] += t3.y;
-                            }
-                        } else {
-                            const float4* p = reinterpret_cast<const float4*>(R2f + boff + e);
-#pragma unroll
-                            for (int h = 0; h < 4; ++h) { float4 u = p[h]; v[h * 4] += u.x; v[h * 4 + 1] += u.y; v[h * 4 + 2] += u.z; v[h * 4 + 3] += u.w; }
-                        }
-                    }
-                    if (a.out_scale != 1.f) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] *= a.out_scale;
-                    }
-                    if (a.Y) {
-                        float4* p = reinterpret_cast<float4*>(a.Y + boff + e);
-#pragma unroll
-                        for (int h = 0; h < 4; ++h) p[h] = make_float4(v[h * 4], v[h * 4 + 1], v[h * 4 + 2], v[h * 4 + 3]);
-                    }
-                    if (a.Y16) {
-                        uint4* p = reinterpret_cast<uint4*>(a.Y16 + boff + e);
-#pragma unroll
-                        for (int h = 0; h < 2; ++h)
-                            p[h] = make_uint4(pack_bf16(v[h * 8], v[h * 8 + 1]), pack_bf16(v[h * 8 + 2], v[h * 8 + 3]),
-                                              pack_bf16(v[h * 8 + 4], v[h * 8 + 5]), pack_bf16(v[h * 8 + 6], v[h * 8 + 7]));
                     }
                 }
             }
+            tc_fence_before();                              // order this warp's tcgen05.ld before the release below
+            __syncwarp();
+            if (lane == 0) mbar_arrive(ACC_EMPTY(accb));
         }
     }
     tc_fence_before();
@@ -412,6 +464,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     MASG_CHECK(d.w16 != nullptr && d.NT > 0, "conv_tc: bf16 weights not committed");
     MASG_CHECK(io.x_ld % 8 == 0 && io.x_bs % 8 == 0, "conv_tc: x_ld=%d / batch stride must be multiples of 8", io.x_ld);
     MASG_CHECK(io.Y != nullptr || io.Y16 != nullptr, "conv_tc: no output tensor");
+    MASG_CHECK(d.N <= BIAS_MAX, "conv_tc: N=%d exceeds the staged bias row (%d)", d.N, BIAS_MAX);
     if (io.Q <= 0 || io.B <= 0) return;
     TcArgs a;
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
@@ -425,12 +478,13 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     for (int j = 0; j < d.taps; ++j) { int o = d.off0 + j * d.tstep; off_lo = std::min(off_lo, o); off_hi = std::max(off_hi, o); }
     const int halo = off_hi - off_lo;
     a.off_lo = off_lo;
-    // rows per CTA: as many 128-row sub-tiles as TMEM holds (msub * NT <= 512 columns), fewer when that would leave SMs idle
-    int msub = std::min(std::min(512 / NT, 8), (io.Q + 127) / 128);
+    // rows per tile: two accumulator sets share the 512 TMEM columns (2 * msub * NT <= 512); fewer sub-tiles when that
+    // would leave SMs without a tile
+    int msub = std::min(std::max(256 / NT, 1), (io.Q + 127) / 128);
     const int ntiles_n = d.N / NT;
     while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub = (msub + 1) / 2;
-    // channel chunk: the whole Cin when it fits (single buffer), else the largest multiple of KW that double-buffers
-    int KC = 0, n_abuf = 1, Rp = 0;
+    // channel chunk: the largest multiple of KW dividing Cin whose staged tile (rows + halo) fits one activation slot
+    int KC = 0, Rp = 0;
     for (;;) {
         const int rows = msub * 128 + halo;
         auto pad_rows = [&](int kc) {
@@ -440,36 +494,37 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
             while ((rp % 8) != want && !(cpr >= 8 && (rp & 1))) ++rp;
             return rp;
         };
-        if ((size_t)pad_rows(d.Cin) * d.Cin * 2 * a_mul <= (size_t)A_BUDGET) { KC = d.Cin; n_abuf = 1; Rp = pad_rows(KC); }
-        else {
-            for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
-                if ((d.Cin / d.KW) % m) continue;
-                const int kc = m * d.KW;
-                if (kc == d.Cin) continue;
-                if ((size_t)pad_rows(kc) * kc * 2 * 2 * a_mul <= (size_t)A_BUDGET) { KC = kc; n_abuf = 2; Rp = pad_rows(kc); }
-            }
+        for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
+            if ((d.Cin / d.KW) % m) continue;
+            const int kc = m * d.KW;
+            if ((size_t)pad_rows(kc) * kc * 2 * a_mul <= (size_t)A_SLOT_BUDGET) { KC = kc; Rp = pad_rows(kc); }
         }
         if (KC || msub == 1) break;
         msub = (msub + 1) / 2;
     }
     MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
-    a.msub = msub; a.rows = msub * 128 + halo; a.Rp = Rp; a.KC = KC; a.n_abuf = n_abuf;
+    a.msub = msub; a.rows = msub * 128 + halo; a.Rp = Rp; a.KC = KC;
     a.a_half = (((KC / 8) * Rp * 16) + 127) & ~127;
     a.a_bytes = a.a_half * (int)a_mul;
     a.blob_bytes = d.KW * NT * 2 * (int)a_mul;
     a.G = std::max(1, W_STAGE_BYTES / a.blob_bytes);
     a.stage_bytes = a.G * a.blob_bytes;
     a.n_blobs = (d.Cin / d.KW) * d.taps;
-    int cols = 32; while (cols < msub * NT) cols *= 2;
+    int cols = 32; while (cols < 2 * msub * NT) cols *= 2;
+    MASG_CHECK(cols <= 512, "conv_tc: %d TMEM columns needed", cols);
     a.tmem_cols = cols;
+    a.B = io.B; a.row_tiles = (io.Q + msub * 128 - 1) / (msub * 128); a.n_ntiles = ntiles_n;
+    a.total_tiles = io.B * a.row_tiles * ntiles_n;
     a.Y = io.Y; a.Y16 = io.Y16; a.y_bs = io.y_bs; a.y_limit = io.y_limit; a.orow = d.orow ? d.orow : d.N; a.ooff = d.ooff; a.Q = io.Q;
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale;
     MASG_CHECK(a.orow % 16 == 0 && a.ooff % 16 == 0 && a.y_bs % 16 == 0 && a.bias_mod % 16 == 0,
                "conv_tc: output row stride/offset/bias period must be multiples of 16");
-    const size_t smem = SMEM_HDR + (size_t)n_abuf * a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
+    const size_t smem = SMEM_HDR + BIAS_MAX * 4 + 2 * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
-    dim3 grid((io.Q + msub * 128 - 1) / (msub * 128), ntiles_n, io.B);
+    static int n_sm = 0;
+    if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
+    dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
     const bool xf32 = !io.x_bf16;
 #define MASG_TC_CASE(NTV)                                                                       \
     case NTV: if (xf32) launch_inst<NTV, true>(a, grid, smem, s); else launch_inst<NTV, false>(a, grid, smem, s); break;
