@@ -296,11 +296,13 @@ int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, cons
 
 // Single Conv1d / ConvTranspose1d through the context's dense-contraction kernel (diagnostic + micro-benchmark hook).
 int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin, const float* w, const float* bias, int Cout,
-                int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int split, int reps, float* y,
+                int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int flags, int reps, float* y,
                 float* ms_out) {
     API_BEGIN(c)
     cudaStream_t s = (cudaStream_t)stream;
     MASG_CHECK(x && w && y && B > 0 && T > 0 && reps >= 1, "bad argument");
+    const int split = flags & 1, act_bf16 = (flags & 2) && c->precision == MASG_PREC_BF16, residual = flags & 4;
+    MASG_CHECK(!residual || (Cin == Cout && stride_transposed == 0), "residual needs Cin == Cout and a plain conv");
     const size_t keep = c->owned.size();
     ConvDesc d; int Q = T; long So = T;
     if (stride_transposed > 0) {
@@ -319,6 +321,14 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     ConvIO io;
     io.X = x; io.x_ld = Cin; io.x_bs = (long)T * Cin; io.Tin = T; io.Y = y; io.y_bs = So * Cout; io.y_limit = So * Cout;
     io.B = B; io.Q = Q; io.out_act = out_act;
+    bf16 *x16 = nullptr, *y16 = nullptr;
+    if (act_bf16) {                                           // HiFi-GAN style: bf16 activations in HBM
+        CUDA_OK(cudaMalloc(&x16, (size_t)B * T * Cin * 2)); c->owned.push_back(x16);
+        CUDA_OK(cudaMalloc(&y16, (size_t)B * So * Cout * 2)); c->owned.push_back(y16);
+        launch_f32_to_bf16(c, s, x, x16, (long)B * T * Cin);
+        io.X = x16; io.x_bf16 = 1; io.Y = nullptr; io.Y16 = y16;
+    }
+    if (residual) { io.R1 = io.X; io.r_bf16 = act_bf16; }
     if (in_lrelu_slope != 0.f) { io.in_act = ACT_LRELU; io.in_slope = in_lrelu_slope; }
     launch_conv(c, s, d, io);                                  // warm-up / result
     cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));
@@ -329,6 +339,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
     if (ms_out) *ms_out = ms / reps;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (act_bf16) { launch_bf16_to_f32(c, s, y16, y, (long)B * So * Cout); CUDA_OK(cudaStreamSynchronize(s)); }
     while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }
     API_END(c)
 }

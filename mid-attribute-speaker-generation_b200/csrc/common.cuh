@@ -155,6 +155,8 @@ void launch_gmm_bary(masg_ctx* c, cudaStream_t s, const float* mu, const float* 
 void launch_gmm_bary_assign(masg_ctx* c, cudaStream_t s, const float* mu, const float* sigma, const float* bmean,
                             const float* bstd, int A, int K, int D, int nb, int32_t* assign);
 
+void launch_f32_to_bf16(masg_ctx* c, cudaStream_t s, const float* in, bf16* out, long n);
+void launch_bf16_to_f32(masg_ctx* c, cudaStream_t s, const bf16* in, float* out, long n);
 // repack helpers (device side)
 void launch_repack_conv_w(masg_ctx* c, cudaStream_t s, const float* w /*[Cout][Cin][k]*/, int Cout, int Cin, int k,
                           const float* scale /*nullable per-Cout*/, float* out /*[k*Cin][ldn] at col0*/, int ldn, int col0);

@@ -86,6 +86,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// one lane of the (converged) warp; the same lane every time, so MMAs and their commits come from one thread
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -115,6 +121,12 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | ((uint64_t)1 << 46);
 }
+// streaming 128-bit global load (read-only path, no L1 allocation: every activation byte is used once per tile)
+__device__ __forceinline__ uint4 ld_nc(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ float act_apply(float v, int act, float slope) {
     switch (act) {
         case ACT_RELU: return fmaxf(v, 0.f);
@@ -133,25 +145,28 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// A staging: one 16-byte piece = 8 consecutive channels of one row
+// A staging: one 16-byte piece = 8 consecutive channels of one row.  Loads and transforms are separate so the
+// producer loop can put U independent 128-bit loads in flight before the first use.
 // ---------------------------------------------------------------------------------------------
 template <bool XF32>
-__device__ __forceinline__ uint4 load_piece(const TcArgs& a, const uint8_t* Xb, int t, int ch, uint4& lo) {
+__device__ __forceinline__ uint4 transform_piece(const TcArgs& a, const uint4 (&raw)[XF32 ? 2 : 1], bool ok, uint4& lo) {
     uint4 o = make_uint4(0u, 0u, 0u, 0u);
     lo = o;
-    if (t < 0 || t >= a.Tin) return o;
+    if (!ok) return o;                                   // row outside [0, Tin): conv zero padding
     float f[8];
     if (XF32) {
-        const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(Xb) + (long)t * a.x_ld + ch);
-        float4 u = __ldg(p), w = __ldg(p + 1);
-        f[0] = u.x; f[1] = u.y; f[2] = u.z; f[3] = u.w; f[4] = w.x; f[5] = w.y; f[6] = w.z; f[7] = w.w;
+        f[0] = __uint_as_float(raw[0].x); f[1] = __uint_as_float(raw[0].y); f[2] = __uint_as_float(raw[0].z); f[3] = __uint_as_float(raw[0].w);
+        f[4] = __uint_as_float(raw[XF32 ? 1 : 0].x); f[5] = __uint_as_float(raw[XF32 ? 1 : 0].y);
+        f[6] = __uint_as_float(raw[XF32 ? 1 : 0].z); f[7] = __uint_as_float(raw[XF32 ? 1 : 0].w);
     } else {
-        uint4 u = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(Xb) + (long)t * a.x_ld + ch));
-        if (a.in_act == ACT_NONE) return u;
-        float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
+        if (a.in_act == ACT_NONE) return raw[0];
+        float2 t0 = unpack_bf16(raw[0].x), t1 = unpack_bf16(raw[0].y), t2 = unpack_bf16(raw[0].z), t3 = unpack_bf16(raw[0].w);
         f[0] = t0.x; f[1] = t0.y; f[2] = t1.x; f[3] = t1.y; f[4] = t2.x; f[5] = t2.y; f[6] = t3.x; f[7] = t3.y;
     }
-    if (a.in_act != ACT_NONE) {
+    if (a.in_act == ACT_LRELU) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * a.in_slope;
+    } else if (a.in_act != ACT_NONE) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = act_apply(f[i], a.in_act, a.in_slope);
     }
@@ -222,23 +237,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                 uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
                 const int ch0 = kc * a.KC;
                 int r = tid / cpr, cc = tid % cpr;
-                constexpr int U = XF32 ? 4 : 8;            // loads in flight per thread (fp32 pieces are 32 bytes + hi/lo)
+                constexpr int U = XF32 ? 4 : 8;            // independent 128-bit loads in flight per thread (x2 for fp32 pieces)
+                constexpr int RW = XF32 ? 2 : 1;
+                const int tmax = a.Tin - 1;
                 for (int i = tid; i < total; i += U * A_THREADS) {
-                    uint4 v[U], vl[U]; int rr[U], cs[U];
+                    uint4 raw[U][RW]; int rr[U], cs[U]; bool ok[U];
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
                         rr[u] = r; cs[u] = cc;
-                        vl[u] = make_uint4(0u, 0u, 0u, 0u);
-                        v[u] = (i + u * A_THREADS < total) ? load_piece<XF32>(a, Xb, q_lo + r, ch0 + cc * 8, vl[u]) : make_uint4(0u, 0u, 0u, 0u);
+                        const int t = q_lo + r;
+                        ok[u] = t >= 0 && t <= tmax;
+                        const int tcl = min(max(t, 0), tmax);          // clamped: the load is always legal, the value is dropped when !ok
+                        const uint4* p = reinterpret_cast<const uint4*>(Xb + ((size_t)tcl * a.x_ld + ch0 + cc * 8) * (XF32 ? 4 : 2));
+                        raw[u][0] = ld_nc(p);
+                        if (XF32) raw[u][RW - 1] = ld_nc(p + 1);
                         r += dr; cc += dc;
                         if (cc >= cpr) { cc -= cpr; ++r; }
                     }
 #pragma unroll
                     for (int u = 0; u < U; ++u)
                         if (i + u * A_THREADS < total) {
+                            uint4 vl;
+                            const uint4 v = transform_piece<XF32>(a, raw[u], ok[u], vl);
                             const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
-                            *reinterpret_cast<uint4*>(dst + o) = v[u];
-                            if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl[u];
+                            *reinterpret_cast<uint4*>(dst + o) = v;
+                            if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl;
                         }
                 }
                 fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core (async proxy)
@@ -263,55 +286,68 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             }
         }
     } else if (warp == MMA_WARP) {
-        // ===== MMA issuer (one thread) =====
-        if (lane == 0) {
-            // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            const uint32_t a_lbo = (uint32_t)a.Rp * 16u, w_lbo = (uint32_t)NT * 16u;
-            int iw = 0, ia = 0, it = 0;
-            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-                const int accb = it & 1;
-                mbar_wait(ACC_EMPTY(accb), ((it >> 1) & 1) ^ 1);          // epilogue has drained this accumulator set
+        // ===== MMA issuer: the whole warp walks the (warp-uniform) loops, one elected lane issues tcgen05.mma / commit =====
+        // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t w_lbo = (uint32_t)NT * 16u;
+        // descriptor halves: hi = SBO (128 B) | version 1; lo = start address | LBO — advancing an operand = adding to lo
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);
+        const uint32_t a_lo_base = (((uint32_t)a.Rp * 16u) >> 4) << 16, w_lo_base = (w_lbo >> 4) << 16;
+        int iw = 0, ia = 0, it = 0;
+        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+            const int accb = it & 1;
+            mbar_wait(ACC_EMPTY(accb), ((it >> 1) & 1) ^ 1);          // epilogue has drained this accumulator set
+            tc_fence_after();
+            const uint32_t tacc = tmem_base + (uint32_t)(accb * acc_cols);
+            int blob = 0;
+            for (int st = 0; st < n_stages; ++st, ++iw) {
+                const int slot = iw % W_STAGES;
+                mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
                 tc_fence_after();
-                const uint32_t tacc = tmem_base + (uint32_t)(accb * acc_cols);
-                int blob = 0;
-                for (int st = 0; st < n_stages; ++st, ++iw) {
-                    const int slot = iw % W_STAGES;
-                    mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
-                    tc_fence_after();
-                    const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
-                    for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
-                        const int rem = blob % blobs_per_chunk;
-                        const int sub = rem / a.taps, j = rem % a.taps;
-                        const int aslot = ia & 1;
-                        if (rem == 0) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
-                        const uint32_t abase = smem_u32(A_smem + (size_t)aslot * a.a_bytes);
-                        const int rowoff = a.off0 + j * a.tstep - a.off_lo;
+                const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
+                for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
+                    const int rem = blob % blobs_per_chunk;
+                    const int sub = rem / a.taps, j = rem % a.taps;
+                    const int aslot = ia & 1;
+                    if (rem == 0) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
+                    const uint32_t abase = smem_u32(A_smem + (size_t)aslot * a.a_bytes);
+                    const int rowoff = a.off0 + j * a.tstep - a.off_lo;
+                    if (elect_one()) {
                         for (int ks = 0; ks < a.KW / 16; ++ks) {
                             const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
                             const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
-                            const uint64_t bdesc = umma_desc(waddr, w_lbo, 128u);
+                            const uint32_t a_lo = a_lo_base | (aaddr >> 4), w_lo = w_lo_base | (waddr >> 4);
+                            const uint64_t bdesc = ((uint64_t)desc_hi << 32) | w_lo;
                             const uint32_t acc = (blob > 0 || ks > 0) ? 1u : 0u;
                             if (!a.split) {
-                                for (int ms = 0; ms < a.msub; ++ms)
-                                    tc_mma(tacc + (uint32_t)(ms * NT), umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u), bdesc, idesc, acc);
+#pragma unroll
+                                for (int ms = 0; ms < 8; ++ms)
+                                    if (ms < a.msub)
+                                        tc_mma(tacc + (uint32_t)(ms * NT), ((uint64_t)desc_hi << 32) | (a_lo + (uint32_t)ms * 128u), bdesc, idesc, acc);
                             } else {
-                                const uint64_t bdesc_lo = umma_desc(waddr + (uint32_t)(a.blob_bytes >> 1), w_lbo, 128u);
-                                for (int ms = 0; ms < a.msub; ++ms) {
-                                    const uint64_t ad_hi = umma_desc(aaddr + (uint32_t)ms * 2048u, a_lbo, 128u);
-                                    const uint64_t ad_lo = umma_desc(aaddr + (uint32_t)a.a_half + (uint32_t)ms * 2048u, a_lbo, 128u);
-                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
-                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
-                                    tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
-                                }
+                                const uint64_t bdesc_lo = ((uint64_t)desc_hi << 32) | (w_lo + (uint32_t)(a.blob_bytes >> 5));
+                                const uint32_t a_lo2 = a_lo + (uint32_t)(a.a_half >> 4);
+#pragma unroll
+                                for (int ms = 0; ms < 8; ++ms)
+                                    if (ms < a.msub) {
+                                        const uint64_t ad_hi = ((uint64_t)desc_hi << 32) | (a_lo + (uint32_t)ms * 128u);
+                                        const uint64_t ad_lo = ((uint64_t)desc_hi << 32) | (a_lo2 + (uint32_t)ms * 128u);
+                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
+                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
+                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
+                                    }
                             }
                         }
-                        if (rem == blobs_per_chunk - 1) { tc_commit(A_EMPTY(aslot)); ++ia; }   // chunk consumed -> slot may be overwritten
+                        if (rem == blobs_per_chunk - 1) tc_commit(A_EMPTY(aslot));     // chunk consumed -> slot may be overwritten
                     }
-                    tc_commit(W_EMPTY(slot));
+                    __syncwarp();
+                    if (rem == blobs_per_chunk - 1) ++ia;
                 }
-                tc_commit(ACC_FULL(accb));
+                if (elect_one()) tc_commit(W_EMPTY(slot));
+                __syncwarp();
             }
+            if (elect_one()) tc_commit(ACC_FULL(accb));
+            __syncwarp();
         }
     } else {
         // ===== epilogue (8 warps): TMEM -> registers -> bias / activation / residual / scale -> global =====

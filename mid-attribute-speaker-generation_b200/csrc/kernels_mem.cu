@@ -674,6 +674,22 @@ void launch_gmm_bary_assign(masg_ctx* c, cudaStream_t s, const float* mu, const 
     c->launches++;
 }
 
+// fp32 <-> bf16 tensor conversion (diagnostic hook masg_conv1d with bf16 activations)
+__global__ void k_f32_to_bf16(const float* __restrict__ in, bf16* __restrict__ out, long n) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __float2bfloat16_rn(in[i]);
+}
+__global__ void k_bf16_to_f32(const bf16* __restrict__ in, float* __restrict__ out, long n) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __bfloat162float(in[i]);
+}
+void launch_f32_to_bf16(masg_ctx* c, cudaStream_t s, const float* in, bf16* out, long n) {
+    k_f32_to_bf16<<<cdiv(n, 256), 256, 0, s>>>(in, out, n); c->launches++;
+}
+void launch_bf16_to_f32(masg_ctx* c, cudaStream_t s, const bf16* in, float* out, long n) {
+    k_bf16_to_f32<<<cdiv(n, 256), 256, 0, s>>>(in, out, n); c->launches++;
+}
+
 // ------------------------------------------------------------------------------------------------
 // weight repacking (load time only)
 // ------------------------------------------------------------------------------------------------

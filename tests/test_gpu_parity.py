@@ -373,14 +373,16 @@ CONV_CASES = [
 ]
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16-split"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16-split", "bf16-act"])
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_conv_kernel_matches_torch(precision, case):
     import torch.nn.functional as F
     from masg_b200 import _lib
     B, T, Cin, Cout, k, dil, ups, slope, act = case
     split = precision == "bf16-split"
-    cx = _lib.default_context(DEV, "bf16" if split else precision)
+    residual = precision == "bf16-act" and Cin == Cout and not ups       # bf16 activations in HBM + residual add (HiFi-GAN style)
+    flags = (1 if split else 0) | (2 if precision == "bf16-act" else 0) | (4 if residual else 0)
+    cx = _lib.default_context(DEV, "bf16" if precision.startswith("bf16") else precision)
     g = torch.Generator().manual_seed(hash(case) % 1000)
     x = torch.randn(B, T, Cin, generator=g)
     w = torch.randn((Cin, Cout, k) if ups else (Cout, Cin, k), generator=g) / (Cin * (2 if ups else k)) ** 0.5
@@ -391,11 +393,13 @@ def test_conv_kernel_matches_torch(precision, case):
     else:
         ref = F.conv1d(xin.transpose(1, 2), w, bias, dilation=dil, padding=(k * dil - dil) // 2)
     ref = [ref, torch.relu(ref), torch.tanh(ref)][act].transpose(1, 2).contiguous()
+    if residual:
+        ref = ref + x
     xg, wg, bg = x.to(DEV), w.to(DEV), bias.to(DEV)
     y = torch.full(ref.shape, 7.0, device=DEV)
     ms = ctypes.c_float(0)
-    cx.check(cx.lib.masg_conv1d(cx.h, cx.stream(), P(xg), B, T, Cin, P(wg), P(bg), Cout, k, dil, ups, slope, act, int(split), 1, P(y),
+    cx.check(cx.lib.masg_conv1d(cx.h, cx.stream(), P(xg), B, T, Cin, P(wg), P(bg), Cout, k, dil, ups, slope, act, flags, 1, P(y),
                                 ctypes.byref(ms)), "conv1d")
     err = (y.cpu() - ref).abs().max().item()
     print("conv %s %s: max-abs err %.3e, %.3f ms" % (precision, case, err, ms.value))
-    assert err <= {"fp32": 2e-4, "bf16-split": 2e-4, "bf16": 4e-2}[precision]
+    assert err <= {"fp32": 2e-4, "bf16-split": 2e-4, "bf16": 4e-2, "bf16-act": 8e-2}[precision]
