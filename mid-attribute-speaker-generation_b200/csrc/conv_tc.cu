@@ -60,6 +60,7 @@ struct TcArgs {
     float* Y; bf16* Y16; long y_bs; long y_limit; long orow; long ooff; int Q;
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale;
+    int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -233,6 +234,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const int q_lo = rt * a.msub * 128 + a.off_lo;
             for (int kc = 0; kc < n_chunks; ++kc, ++ia) {
                 const int slot = ia & 1;
+                if (a.dbg & 2) continue;
                 mbar_wait(A_EMPTY(slot), ((ia >> 1) & 1) ^ 1);
                 uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
                 const int ch0 = kc * a.KC;
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         }
     } else if (warp == W_WARP) {
         // ===== weight producer: 1-D bulk copies of pre-tiled blobs =====
-        if (lane == 0) {
+        if (lane == 0 && !(a.dbg & 1)) {
             int iw = 0;
             for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                 const int nt = tile % a.n_ntiles;
@@ -302,18 +304,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             int blob = 0;
             for (int st = 0; st < n_stages; ++st, ++iw) {
                 const int slot = iw % W_STAGES;
-                mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
+                if (!(a.dbg & 1)) mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
                 tc_fence_after();
                 const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
                 for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
                     const int rem = blob % blobs_per_chunk;
                     const int sub = rem / a.taps, j = rem % a.taps;
                     const int aslot = ia & 1;
-                    if (rem == 0) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
+                    if (rem == 0 && !(a.dbg & 2)) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
                     const uint32_t abase = smem_u32(A_smem + (size_t)aslot * a.a_bytes);
                     const int rowoff = a.off0 + j * a.tstep - a.off_lo;
                     if (elect_one()) {
-                        for (int ks = 0; ks < a.KW / 16; ++ks) {
+                        for (int ks = 0; ks < a.KW / 16 && !(a.dbg & 8); ++ks) {
                             const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
                             const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
                             const uint32_t a_lo = a_lo_base | (aaddr >> 4), w_lo = w_lo_base | (waddr >> 4);
@@ -338,12 +340,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                                     }
                             }
                         }
-                        if (rem == blobs_per_chunk - 1) tc_commit(A_EMPTY(aslot));     // chunk consumed -> slot may be overwritten
+                        if (rem == blobs_per_chunk - 1 && !(a.dbg & 2)) tc_commit(A_EMPTY(aslot));     // chunk consumed -> slot may be overwritten
                     }
                     __syncwarp();
                     if (rem == blobs_per_chunk - 1) ++ia;
                 }
-                if (elect_one()) tc_commit(W_EMPTY(slot));
+                if (!(a.dbg & 1) && elect_one()) tc_commit(W_EMPTY(slot));
                 __syncwarp();
             }
             if (elect_one()) tc_commit(ACC_FULL(accb));
@@ -368,7 +370,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             for (int ms = 0; ms < a.msub; ++ms) {
                 const int q = q0 + ms * 128 + quad * 32 + lane;
                 const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT);
-                for (int cg = c_begin; cg < c_end; cg += gc) {
+                for (int cg = c_begin; cg < c_end && !(a.dbg & 4); cg += gc) {
                     const int ncol = min(gc, c_end - cg);
                     const long eg = (long)q * a.orow + a.ooff + n0 + cg;
                     const bool rowok = q < a.Q;
@@ -554,6 +556,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.Y = io.Y; a.Y16 = io.Y16; a.y_bs = io.y_bs; a.y_limit = io.y_limit; a.orow = d.orow ? d.orow : d.N; a.ooff = d.ooff; a.Q = io.Q;
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale;
+    { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
     MASG_CHECK(a.orow % 16 == 0 && a.ooff % 16 == 0 && a.y_bs % 16 == 0 && a.bias_mod % 16 == 0,
                "conv_tc: output row stride/offset/bias period must be multiples of 16");
     const size_t smem = SMEM_HDR + BIAS_MAX * 4 + 2 * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
