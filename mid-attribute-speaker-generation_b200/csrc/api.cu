@@ -309,7 +309,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         const int u = stride_transposed;
         MASG_CHECK(k == 2 * u, "transposed conv needs k = 2*stride");
         d.Cin = Cin; d.N = u * Cout; d.taps = 2; d.off0 = 0; d.tstep = -1; d.bias_mod = Cout;
-        d.orow = (long)u * Cout; d.ooff = -(long)((k - u) / 2) * Cout;
+        d.orow = (long)u * Cout; d.ooff = -(long)((k - u) / 2) * Cout; d.up = u; d.up_pad = (k - u) / 2;
         float* w32 = nullptr; CUDA_OK(cudaMalloc(&w32, (size_t)2 * Cin * u * Cout * 4)); c->owned.push_back(w32);
         launch_repack_convT_w(c, s, w, Cin, Cout, k, u, w32);
         d.w32 = w32; d.bias = bias;
@@ -325,8 +325,8 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     if (act_bf16) {                                           // HiFi-GAN style: bf16 activations in HBM
         CUDA_OK(cudaMalloc(&x16, (size_t)B * T * Cin * 2)); c->owned.push_back(x16);
         CUDA_OK(cudaMalloc(&y16, (size_t)B * So * Cout * 2)); c->owned.push_back(y16);
-        launch_f32_to_bf16(c, s, x, x16, (long)B * T * Cin);
-        io.X = x16; io.x_bf16 = 1; io.Y = nullptr; io.Y16 = y16;
+        launch_to_planar(c, s, x, x16, B, T, Cin);                  // planar [B][C/8][T][8], moved by TMA
+        io.X = x16; io.x_bf16 = 1; io.x_planar = 1; io.Y = nullptr; io.Y16 = y16; io.y_planar = 1; io.y_T = (int)So;
     }
     if (residual) { io.R1 = io.X; io.r_bf16 = act_bf16; }
     if (in_lrelu_slope != 0.f) { io.in_act = ACT_LRELU; io.in_slope = in_lrelu_slope; }
@@ -339,7 +339,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
     if (ms_out) *ms_out = ms / reps;
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    if (act_bf16) { launch_bf16_to_f32(c, s, y16, y, (long)B * So * Cout); CUDA_OK(cudaStreamSynchronize(s)); }
+    if (act_bf16) { launch_from_planar(c, s, y16, y, B, (int)So, Cout); CUDA_OK(cudaStreamSynchronize(s)); }
     while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }
     API_END(c)
 }

@@ -48,6 +48,7 @@ struct ConvDesc {
     int Cin = 0, N = 0, taps = 1, off0 = 0, tstep = 1;
     int bias_mod = 0;                 // 0 → N
     long orow = 0, ooff = 0;          // output row stride / offset in elements (0 → N / 0)
+    int up = 0, up_pad = 0;           // phase-decomposed ConvTranspose1d: column n = r*Cout + co lands at time q*up + r - up_pad (planar output)
     const float* w32 = nullptr;       // [taps*Cin][N] fp32 (SIMT path)
     const float* bias = nullptr;      // [bias_mod]
     // tcgen05 path (conv_tc.cu): bf16 weights pre-tiled into UMMA no-swizzle K-major blobs
@@ -107,7 +108,10 @@ struct masg_ctx {
 // kernel launchers (each increments ctx->launches)
 // ------------------------------------------------------------------------------------------------
 struct ConvIO {
-    const void* X = nullptr; int x_bf16 = 0; long x_bs = 0; int x_ld = 0; int Tin = 0;   // input rows [B][Tin][x_ld] (fp32 or bf16)
+    const void* X = nullptr; int x_bf16 = 0; long x_bs = 0; int x_ld = 0; int Tin = 0;   // input rows [B][Tin][x_ld] fp32, or
+    int x_planar = 0;                                                        // bf16 planar [B][x_ld/8][Tin][8] (tcgen05 path only)
+    int y_planar = 0, y_T = 0;                                               // Y16 is planar [B][Cout/8][y_T][8] (residuals too)
+    float post_slope = 1.f;                                                  // trailing leaky-relu after residuals and scale (1 = none)
     float* Y = nullptr; bf16* Y16 = nullptr; long y_bs = 0; long y_limit = 0;  // fp32 and/or bf16 output, valid elements per batch
     int B = 1, Q = 0;                                                        // rows computed per batch
     int in_act = ACT_NONE; float in_slope = 0.f;
@@ -155,6 +159,9 @@ void launch_gmm_bary(masg_ctx* c, cudaStream_t s, const float* mu, const float* 
 void launch_gmm_bary_assign(masg_ctx* c, cudaStream_t s, const float* mu, const float* sigma, const float* bmean,
                             const float* bstd, int A, int K, int D, int nb, int32_t* assign);
 
+// row-major fp32 [B][T][C] <-> planar bf16 [B][C/8][T][8] (conv_tc.cu)
+void launch_to_planar(masg_ctx* c, cudaStream_t s, const float* x, bf16* out, int B, int T, int C);
+void launch_from_planar(masg_ctx* c, cudaStream_t s, const bf16* x, float* out, int B, int T, int C);
 void launch_f32_to_bf16(masg_ctx* c, cudaStream_t s, const float* in, bf16* out, long n);
 void launch_bf16_to_f32(masg_ctx* c, cudaStream_t s, const bf16* in, float* out, long n);
 // repack helpers (device side)

@@ -1,65 +1,74 @@
 // tcgen05 implicit-GEMM conv1d / linear / transposed-conv kernel for sm_100a (MASG_PREC_BF16 path).
 //
 // Same row-GEMM contract as conv_simt.cu (ConvDesc / ConvIO in common.cuh):
-//   out[b, q*orow + ooff + n] = (act(sum_{j<taps, c<Cin} in_act(X[b, q + off0 + j*tstep, c]) * W[j*Cin + c, n] + bias[n % bias_mod])
-//                                + R1 + R2) * out_scale
+//   out[b, q, n] = post( (act(sum_{j<taps, c<Cin} in_act(X[b, q + off0 + j*tstep, c]) * W[j*Cin + c, n] + bias[n % bias_mod])
+//                         + R1 + R2) * out_scale )
 // It stands behind every dense contraction of the hot path: the FFT-block QKV / fc projections
 // (transformer/SubLayers.py:39-41,54), the k=9 / k=1 position-wise FFN convs (SubLayers.py:88), the variance-
 // predictor convs (model/modules.py:209-240), mel_linear (model/fastspeech2.py:242), PostNet (transformer/
 // Layers.py:129-137) and every Conv1d / ConvTranspose1d of the HiFi-GAN generator (hifigan/models.py:149-165).
 //
 // Persistent, warp-specialised kernel: one CTA per SM walks a list of (128*msub rows) x (NT columns) output tiles
-// (tile = one utterance's row range x one column tile).  Activation staging, weight streaming, MMA issue and the
-// epilogue run as four concurrent roles connected by mbarrier rings, and the TMEM accumulators are double-buffered,
-// so the epilogue of tile i overlaps the loads and MMAs of tile i+1:
-//   * A operand (activations): the tile's rows PLUS the conv halo are staged ONCE per channel chunk in shared memory
-//     in the UMMA no-swizzle K-major layout [KC/8][Rp rows][8 ch] (16-byte pieces).  In that layout a conv tap is a
-//     16-byte-granular shift of the descriptor start address, so all taps (and dilations, and the two taps of a
-//     phase-decomposed ConvTranspose1d) reuse the same resident tile — no im2col, no per-tap re-read from L2.
-//     8 producer warps do the staging with 128-bit loads, converting fp32 -> bf16 and applying the input
-//     leaky-relu on the way (hifigan/models.py:98,100,152), zero-filling rows outside [0, Tin) (= conv padding).
+// (tile = one utterance's row range x one column tile).  Five roles run concurrently, connected by mbarrier rings;
+// the TMEM accumulators are double-buffered so the epilogue of tile i overlaps the loads and MMAs of tile i+1:
+//   * A operand (activations), UMMA no-swizzle K-major layout (8-row x 16-byte core matrices), so that a conv tap is
+//     a 16-byte-granular shift of the descriptor start address: all taps (and dilations, and the two taps of a
+//     phase-decomposed ConvTranspose1d) reuse one resident tile — no im2col, no per-tap re-read.
+//       - planar input (HiFi-GAN): activations live in HBM as bf16 [B][C/8][T][8] — the operand layout itself —
+//         and ONE thread moves each (128 + halo)-row block with a 4-D TMA tile copy (cp.async.bulk.tensor); rows
+//         outside [0, T) are zero-filled by the TMA unit (= conv padding).  When the conv takes leaky_relu(x)
+//         (hifigan/models.py:98,152) 8 worker warps apply it in place in shared memory before the tile is released.
+//       - row-major fp32 input (FastSpeech2): 8 worker warps stage the tile with 128-bit loads, converting to bf16
+//         (hi + lo halves in split mode).
 //   * B operand (weights): pre-tiled at commit (k_tile_w) into contiguous blobs already in UMMA layout, streamed by
 //     one thread with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx) through a 4-stage ring.
-//   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators of the
-//     current accumulator set; tcgen05.commit releases weight stages / activation slots and signals the epilogue.
+//   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators; the issue
+//     loop is specialised on msub and keeps every descriptor a running add (a single thread issues one instruction
+//     every few cycles, and an N=32 MMA only lasts 16); tcgen05.commit releases weight stages / activation slots.
 //   * split mode (FastSpeech2 layers): both operands are carried as bf16 hi + bf16 lo (x = hi + lo to 16 mantissa
 //     bits) and each K step issues three MMAs, hi*hi + lo*hi + hi*lo, into the same fp32 accumulator.  That keeps
 //     the bucketize / duration-rounding decisions and the mel within 1e-4 of the fp32 oracle while still running
-//     on the bf16 tensor pipe (plain bf16 operands give a 0.45 max-abs mel error on random-init weights because
-//     pitch/energy bucket indices flip).  HiFi-GAN layers use plain bf16.
-//   * 8 epilogue warps (two per TMEM lane quadrant, half the columns each) prefetch the residual rows, read TMEM
-//     (tcgen05.ld 32x32b), add the smem-staged bias, apply the activation, residuals and scale, store fp32 and/or bf16
-//     rows and hand the accumulator set back to the MMA thread.
+//     on the bf16 tensor pipe.  HiFi-GAN layers use plain bf16.
+//   * 8 epilogue warps (two per TMEM lane quadrant, half the columns each) read TMEM (tcgen05.ld 32x32b), add the
+//     smem-staged bias, apply activation, residuals, scale and the optional trailing leaky-relu, and store fp32
+//     row-major rows or planar bf16 (lane = time row, so each store instruction writes 512 contiguous bytes).
 #include "common.cuh"
 #include "tc.cuh"
+#include <cuda.h>
 
 namespace {
 
-// warp roles of the persistent CTA (576 threads, one CTA per SM)
+// warp roles of the persistent CTA (608 threads, one CTA per SM)
 constexpr int EPI_WARPS = 8;            // warps 0-7: epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column half)
 constexpr int MMA_WARP = 8;
-constexpr int W_WARP = 9;
-constexpr int A_WARP0 = 10;
+constexpr int W_WARP = 9;               // weight stream
+constexpr int T_WARP = 10;              // TMA issuer for planar activations
+constexpr int A_WARP0 = 11;             // activation workers
 constexpr int A_WARPS = 8;
 constexpr int A_THREADS = A_WARPS * 32;
-constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 576
+constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 608
 constexpr int W_STAGES = 4;
 constexpr int W_STAGE_BYTES = 16384;
+constexpr int A_SLOTS = 3;
+constexpr int A_SLOT_BYTES = 48 * 1024;
 constexpr int SMEM_HDR = 1024;
 constexpr int BIAS_MAX = 2048;                          // floats staged per CTA (N <= 2048)
-constexpr int A_SLOT_BUDGET = 72 * 1024;                // two activation slots
 constexpr int MAX_SMEM = 227 * 1024;
 
 struct TcArgs {
-    const void* X; long x_bs; int x_ld; int Tin;
+    // input
+    const void* X; long x_bs; int x_ld; int Tin;       // row-major fp32 input (worker-staged); unused with TMA
     const bf16* Wt; const float* bias; int bias_mod;
     int Cin, N, taps, off0, tstep;
     int KW, KC, G, a_bytes, stage_bytes, blob_bytes, n_blobs;
     int msub, rows, Rp, off_lo, tmem_cols, split, a_half;
+    int a_lbo16, a_ms16, a_tx, a_blk_bytes;            // operand strides in 16-byte units; TMA bytes per chunk; bytes per ms block
     int B, row_tiles, n_ntiles, total_tiles;
+    // output
     float* Y; bf16* Y16; long y_bs; long y_limit; long orow; long ooff; int Q;
+    int y_planar, y_T, up, up_pad, cout_shift;         // planar bf16 output [B][Cout/8][y_T][8]; t = q*up + n/Cout - up_pad
     int in_act; float in_slope; int out_act; float out_slope;
-    const void* R1; const void* R2; int r_bf16; float out_scale;
+    const void* R1; const void* R2; int r_bf16; float out_scale; float post_slope;
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
 
@@ -87,11 +96,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
-// one lane of the (converged) warp; the same lane every time, so MMAs and their commits come from one thread
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
+// 4-D TMA tile copy global -> shared (coordinates innermost first); out-of-range elements are zero-filled
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -99,10 +107,12 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]; both operands K-major
-__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+// D[tmem] (+)= A[smem] * B[smem]; both operands K-major.  Descriptors are passed as (lo, hi) halves so that
+// advancing an operand is one 32-bit add.
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+                 ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 // 32 lanes x 16 consecutive fp32 columns; the wait is part of the same statement so the registers are defined after it
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
@@ -115,12 +125,6 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
         : "r"(taddr) : "memory");
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-// UMMA shared-memory descriptor, SWIZZLE_NONE, K-major: 8-row x 16-byte core matrices; SBO = stride between 8-row
-// groups, LBO = stride between the two 8-element K chunks of one K=16 MMA.  version = 1 (Blackwell).
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
-           ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | ((uint64_t)1 << 46);
 }
 // streaming 128-bit global load (read-only path, no L1 allocation: every activation byte is used once per tile)
 __device__ __forceinline__ uint4 ld_nc(const uint4* p) {
@@ -141,38 +145,29 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
-    __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&u);
-    return __bfloat1622float2(h);
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+}
+// leaky-relu on two packed bf16 values (fp32 arithmetic, one rounding)
+__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t u, float slope) {
+    const float2 f = unpack_bf16(u);
+    return pack_bf16(f.x > 0.f ? f.x : f.x * slope, f.y > 0.f ? f.y : f.y * slope);
 }
 
 // ---------------------------------------------------------------------------------------------
-// A staging: one 16-byte piece = 8 consecutive channels of one row.  Loads and transforms are separate so the
-// producer loop can put U independent 128-bit loads in flight before the first use.
+// Worker staging of row-major fp32 activations: one 16-byte piece = 8 consecutive channels of one row.
 // ---------------------------------------------------------------------------------------------
-template <bool XF32>
-__device__ __forceinline__ uint4 transform_piece(const TcArgs& a, const uint4 (&raw)[XF32 ? 2 : 1], bool ok, uint4& lo) {
+__device__ __forceinline__ uint4 convert_piece(const TcArgs& a, const uint4 r0, const uint4 r1, bool ok, uint4& lo) {
     uint4 o = make_uint4(0u, 0u, 0u, 0u);
     lo = o;
     if (!ok) return o;                                   // row outside [0, Tin): conv zero padding
-    float f[8];
-    if (XF32) {
-        f[0] = __uint_as_float(raw[0].x); f[1] = __uint_as_float(raw[0].y); f[2] = __uint_as_float(raw[0].z); f[3] = __uint_as_float(raw[0].w);
-        f[4] = __uint_as_float(raw[XF32 ? 1 : 0].x); f[5] = __uint_as_float(raw[XF32 ? 1 : 0].y);
-        f[6] = __uint_as_float(raw[XF32 ? 1 : 0].z); f[7] = __uint_as_float(raw[XF32 ? 1 : 0].w);
-    } else {
-        if (a.in_act == ACT_NONE) return raw[0];
-        float2 t0 = unpack_bf16(raw[0].x), t1 = unpack_bf16(raw[0].y), t2 = unpack_bf16(raw[0].z), t3 = unpack_bf16(raw[0].w);
-        f[0] = t0.x; f[1] = t0.y; f[2] = t1.x; f[3] = t1.y; f[4] = t2.x; f[5] = t2.y; f[6] = t3.x; f[7] = t3.y;
-    }
-    if (a.in_act == ACT_LRELU) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * a.in_slope;
-    } else if (a.in_act != ACT_NONE) {
+    float f[8] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w),
+                  __uint_as_float(r1.x), __uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r1.w)};
+    if (a.in_act != ACT_NONE) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = act_apply(f[i], a.in_act, a.in_slope);
     }
     o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
-    if (XF32 && a.split) {                                  // residual of the bf16 rounding, itself rounded to bf16
+    if (a.split) {                                       // residual of the bf16 rounding, itself rounded to bf16
         float2 h0 = unpack_bf16(o.x), h1 = unpack_bf16(o.y), h2 = unpack_bf16(o.z), h3 = unpack_bf16(o.w);
         lo.x = pack_bf16(f[0] - h0.x, f[1] - h0.y); lo.y = pack_bf16(f[2] - h1.x, f[3] - h1.y);
         lo.z = pack_bf16(f[4] - h2.x, f[5] - h2.y); lo.w = pack_bf16(f[6] - h3.x, f[7] - h3.y);
@@ -180,35 +175,153 @@ __device__ __forceinline__ uint4 transform_piece(const TcArgs& a, const uint4 (&
     return o;
 }
 
-template <int NT, bool XF32>
-__global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
+struct Bars {                                            // mbarrier addresses (shared window), 8 bytes each
+    uint32_t base;
+    __device__ uint32_t a_full(int i) const { return base + 8u * i; }
+    __device__ uint32_t a_empty(int i) const { return base + 8u * (A_SLOTS + i); }
+    __device__ uint32_t a_raw(int i) const { return base + 8u * (2 * A_SLOTS + i); }
+    __device__ uint32_t w_full(int i) const { return base + 8u * (3 * A_SLOTS + i); }
+    __device__ uint32_t w_empty(int i) const { return base + 8u * (3 * A_SLOTS + W_STAGES + i); }
+    __device__ uint32_t acc_full(int i) const { return base + 8u * (3 * A_SLOTS + 2 * W_STAGES + i); }
+    __device__ uint32_t acc_empty(int i) const { return base + 8u * (3 * A_SLOTS + 2 * W_STAGES + 2 + i); }
+};
+
+// ---------------------------------------------------------------------------------------------
+// MMA issue loop (one thread).  Everything that changes per MMA is a running 32-bit add on the low descriptor word.
+// ---------------------------------------------------------------------------------------------
+template <int NT, int MS, bool SPLIT>
+__device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base) {
+    // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t desc_hi = (128u >> 4) | (1u << 14);                     // SBO = 128 B, descriptor version 1
+    const uint32_t a_fixed = (uint32_t)a.a_lbo16 << 16, w_fixed = (uint32_t)NT << 16;     // LBO fields (16-byte units)
+    const uint32_t a_ks = 2u * (uint32_t)a.a_lbo16, w_ks = 2u * (uint32_t)NT;              // one K=16 step = two 8-channel groups
+    const uint32_t a_sub = (uint32_t)(a.KW >> 3) * (uint32_t)a.a_lbo16;
+    const uint32_t a_ms = (uint32_t)a.a_ms16;
+    const uint32_t blob16 = (uint32_t)a.blob_bytes >> 4, a_half16 = (uint32_t)a.a_half >> 4, w_half16 = blob16 >> 1;
+    const int n_chunks = a.Cin / a.KC, subs = a.KC / a.KW, ksteps = a.KW >> 4;
+    const bool no_w = a.dbg & 1, no_a = a.dbg & 2, no_mma = a.dbg & 8;
+    int wslot = 0, aslot = 0, it = 0;
+    uint32_t wphase = 0, aphase = 0;
+    for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+        const int accb = it & 1;
+        mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1);             // epilogue has drained this accumulator set
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + (uint32_t)(accb * MS * NT);
+        uint32_t accum = 0;
+        int g = a.G;                                                       // forces a stage fetch before the first blob
+        bool have_stage = false;
+        uint32_t wbase16 = 0;
+        for (int kc = 0; kc < n_chunks; ++kc) {
+            if (!no_a) { mbar_wait(bars.a_full(aslot), aphase); tc_fence_after(); }
+            const uint32_t abase16 = (a_smem + (uint32_t)aslot * (uint32_t)a.a_bytes) >> 4;
+            for (int sub = 0; sub < subs; ++sub) {
+                uint32_t a_tap = abase16 + (uint32_t)sub * a_sub + (uint32_t)(a.off0 - a.off_lo);
+                for (int j = 0; j < a.taps; ++j, a_tap += (uint32_t)a.tstep) {
+                    if (g == a.G) {                                        // next weight stage
+                        if (have_stage) {
+                            if (!no_w) tc_commit(bars.w_empty(wslot));
+                            if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
+                        }
+                        if (!no_w) { mbar_wait(bars.w_full(wslot), wphase); tc_fence_after(); }
+                        wbase16 = (w_smem + (uint32_t)wslot * (uint32_t)a.stage_bytes) >> 4;
+                        g = 0; have_stage = true;
+                    }
+                    uint32_t a_lo = a_fixed | a_tap, w_lo = w_fixed | (wbase16 + (uint32_t)g * blob16);
+                    ++g;
+                    if (no_mma) continue;
+                    for (int ks = 0; ks < ksteps; ++ks, a_lo += a_ks, w_lo += w_ks) {
+#pragma unroll
+                        for (int ms = 0; ms < MS; ++ms) {
+                            const uint32_t d = tacc + (uint32_t)(ms * NT), al = a_lo + (uint32_t)ms * a_ms;
+                            tc_mma(d, al, w_lo, desc_hi, idesc, accum);
+                            if (SPLIT) {
+                                tc_mma(d, al + a_half16, w_lo, desc_hi, idesc, 1u);
+                                tc_mma(d, al, w_lo + w_half16, desc_hi, idesc, 1u);
+                            }
+                        }
+                        accum = 1u;
+                    }
+                }
+            }
+            if (!no_a) tc_commit(bars.a_empty(aslot));                     // chunk consumed -> slot may be overwritten
+            if (++aslot == A_SLOTS) { aslot = 0; aphase ^= 1; }
+        }
+        if (!no_w) tc_commit(bars.w_empty(wslot));                         // the weight stream restarts on a stage boundary per tile
+        if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
+        tc_commit(bars.acc_full(accb));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Epilogue helpers
+// ---------------------------------------------------------------------------------------------
+// bias + activation on 16 accumulator columns
+__device__ __forceinline__ void epi_bias_act(const TcArgs& a, float (&v)[16], const float* bp) {
+    const float4* b4 = reinterpret_cast<const float4*>(bp);
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+        const float4 bb = b4[h];
+        v[h * 4 + 0] += bb.x; v[h * 4 + 1] += bb.y; v[h * 4 + 2] += bb.z; v[h * 4 + 3] += bb.w;
+    }
+    if (a.out_act == ACT_LRELU) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * a.out_slope;
+    } else if (a.out_act != ACT_NONE) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i], a.out_act, a.out_slope);
+    }
+}
+__device__ __forceinline__ void add_bf16x8(float* v, const uint4 u) {
+    const float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
+    v[0] += t0.x; v[1] += t0.y; v[2] += t1.x; v[3] += t1.y; v[4] += t2.x; v[5] += t2.y; v[6] += t3.x; v[7] += t3.y;
+}
+__device__ __forceinline__ void epi_scale_post(const TcArgs& a, float (&v)[16]) {
+    if (a.out_scale != 1.f) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] *= a.out_scale;
+    }
+    if (a.post_slope != 1.f) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * a.post_slope;
+    }
+}
+__device__ __forceinline__ uint4 pack8(const float* v) {
+    return make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+
+// planar bf16 output: element offset (within the batch) of the 8-channel group holding column n at row q, or -1
+__device__ __forceinline__ long planar_off(const TcArgs& a, int q, int n) {
+    const int co = n & ((1 << a.cout_shift) - 1), r = n >> a.cout_shift;
+    const int t = q * a.up + r - a.up_pad;
+    if (q >= a.Q || t < 0 || t >= a.y_T) return -1;
+    return ((long)(co >> 3) * a.y_T + t) * 8;
+}
+
+template <int NT, bool TMA_IN>
+__global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    // header: mbarriers + TMEM base; then the bias row, the two activation slots and the weight ring
-    const uint32_t bar0 = smem_u32(smem);
-    auto A_FULL = [&](int i) { return bar0 + 8u * i; };                       // 2
-    auto A_EMPTY = [&](int i) { return bar0 + 8u * (2 + i); };                // 2
-    auto W_FULL = [&](int i) { return bar0 + 8u * (4 + i); };                 // W_STAGES
-    auto W_EMPTY = [&](int i) { return bar0 + 8u * (4 + W_STAGES + i); };     // W_STAGES
-    auto ACC_FULL = [&](int i) { return bar0 + 8u * (4 + 2 * W_STAGES + i); };        // 2
-    auto ACC_EMPTY = [&](int i) { return bar0 + 8u * (6 + 2 * W_STAGES + i); };       // 2
+    // header: mbarriers + TMEM base; then the bias row, the activation slots and the weight ring
+    const Bars bars{smem_u32(smem)};
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + 512);
     float* bias_s = reinterpret_cast<float*>(smem + SMEM_HDR);
     uint8_t* A_smem = smem + SMEM_HDR + BIAS_MAX * 4;
-    uint8_t* W_smem = A_smem + 2 * (size_t)a.a_bytes;
+    uint8_t* W_smem = A_smem + A_SLOTS * (size_t)a.a_bytes;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_chunks = a.Cin / a.KC;
-    const int blobs_per_chunk = (a.KC / a.KW) * a.taps;
     const int n_stages = (a.n_blobs + a.G - 1) / a.G;
     const int acc_cols = a.msub * NT;                      // TMEM columns of one accumulator set (two sets)
+    const bool a_workers = !TMA_IN || a.in_act != ACT_NONE;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(A_FULL(i), A_THREADS); mbar_init(A_EMPTY(i), 1);
-            mbar_init(ACC_FULL(i), 1); mbar_init(ACC_EMPTY(i), EPI_WARPS);
+        for (int i = 0; i < A_SLOTS; ++i) {
+            mbar_init(bars.a_full(i), a_workers ? A_THREADS : 1); mbar_init(bars.a_empty(i), 1); mbar_init(bars.a_raw(i), 1);
         }
-        for (int i = 0; i < W_STAGES; ++i) { mbar_init(W_FULL(i), 1); mbar_init(W_EMPTY(i), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), 1); mbar_init(bars.acc_empty(i), EPI_WARPS); }
+        for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (TMA_IN) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     }
     for (int i = threadIdx.x; i < a.N; i += NTHREADS) bias_s[i] = a.bias ? a.bias[i % a.bias_mod] : 0.f;
     if (warp == MMA_WARP) {
@@ -222,135 +335,134 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
 
     // tile id -> (batch b, row tile rt, column tile nt); a CTA walks ids blockIdx.x, blockIdx.x + gridDim.x, ...
     if (warp >= A_WARP0) {
-        // ===== activation producers: stage rows [q0 + off_lo, q0 + off_lo + rows) x KC channels per chunk =====
         const int tid = threadIdx.x - A_WARP0 * 32;
-        const int cpr = a.KC >> 3;                       // 16-byte pieces per row
-        const int total = cpr * a.rows;
-        const int dr = A_THREADS / cpr, dc = A_THREADS % cpr;
-        int ia = 0;                                      // running chunk counter -> slot / parity
-        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
-            const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
-            const uint8_t* Xb = reinterpret_cast<const uint8_t*>(a.X) + (size_t)b * a.x_bs * (XF32 ? 4 : 2);
-            const int q_lo = rt * a.msub * 128 + a.off_lo;
-            for (int kc = 0; kc < n_chunks; ++kc, ++ia) {
-                const int slot = ia & 1;
-                if (a.dbg & 2) continue;
-                mbar_wait(A_EMPTY(slot), ((ia >> 1) & 1) ^ 1);
-                uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
-                const int ch0 = kc * a.KC;
-                int r = tid / cpr, cc = tid % cpr;
-                constexpr int U = XF32 ? 4 : 8;            // independent 128-bit loads in flight per thread (x2 for fp32 pieces)
-                constexpr int RW = XF32 ? 2 : 1;
-                const int tmax = a.Tin - 1;
-                for (int i = tid; i < total; i += U * A_THREADS) {
-                    uint4 raw[U][RW]; int rr[U], cs[U]; bool ok[U];
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        rr[u] = r; cs[u] = cc;
-                        const int t = q_lo + r;
-                        ok[u] = t >= 0 && t <= tmax;
-                        const int tcl = min(max(t, 0), tmax);          // clamped: the load is always legal, the value is dropped when !ok
-                        const uint4* p = reinterpret_cast<const uint4*>(Xb + ((size_t)tcl * a.x_ld + ch0 + cc * 8) * (XF32 ? 4 : 2));
-                        raw[u][0] = ld_nc(p);
-                        if (XF32) raw[u][RW - 1] = ld_nc(p + 1);
-                        r += dr; cc += dc;
-                        if (cc >= cpr) { cc -= cpr; ++r; }
-                    }
-#pragma unroll
-                    for (int u = 0; u < U; ++u)
-                        if (i + u * A_THREADS < total) {
-                            uint4 vl;
-                            const uint4 v = transform_piece<XF32>(a, raw[u], ok[u], vl);
-                            const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
-                            *reinterpret_cast<uint4*>(dst + o) = v;
-                            if (XF32 && a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl;
+        if (a.dbg & 2) {
+            // what-if: no activation staging
+        } else if (TMA_IN) {
+            // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled =====
+            if (a.in_act != ACT_NONE) {
+                const int pieces = (a.msub * a.a_blk_bytes) >> 4;
+                int slot = 0; uint32_t phase = 0;
+                for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+                    for (int kc = 0; kc < n_chunks; ++kc) {
+                        mbar_wait(bars.a_raw(slot), phase);
+                        uint4* p = reinterpret_cast<uint4*>(A_smem + (size_t)slot * a.a_bytes);
+                        for (int i = tid; i < pieces; i += A_THREADS) {
+                            uint4 v = p[i];
+                            v.x = lrelu_bf16x2(v.x, a.in_slope); v.y = lrelu_bf16x2(v.y, a.in_slope);
+                            v.z = lrelu_bf16x2(v.z, a.in_slope); v.w = lrelu_bf16x2(v.w, a.in_slope);
+                            p[i] = v;
                         }
+                        fence_proxy_async();                  // generic-proxy stores -> visible to the tensor core (async proxy)
+                        mbar_arrive(bars.a_full(slot));
+                        if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
+                    }
                 }
-                fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core (async proxy)
-                mbar_arrive(A_FULL(slot));
+            }
+        } else {
+            // ===== workers, row-major fp32 input: stage rows [q0 + off_lo, q0 + off_lo + rows) x KC channels per chunk =====
+            const int cpr = a.KC >> 3;                       // 16-byte pieces per row
+            const int total = cpr * a.rows;
+            const int dr = A_THREADS / cpr, dc = A_THREADS % cpr;
+            int slot = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+                const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+                const uint8_t* Xb = reinterpret_cast<const uint8_t*>(a.X) + (size_t)b * a.x_bs * 4;
+                const int q_lo = rt * a.msub * 128 + a.off_lo;
+                for (int kc = 0; kc < n_chunks; ++kc) {
+                    mbar_wait(bars.a_empty(slot), phase ^ 1);
+                    uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
+                    const int ch0 = kc * a.KC;
+                    int r = tid / cpr, cc = tid % cpr;
+                    constexpr int U = 4;                       // rows in flight per thread (two 128-bit loads each)
+                    const int tmax = a.Tin - 1;
+                    for (int i = tid; i < total; i += U * A_THREADS) {
+                        uint4 raw[U][2]; int rr[U], cs[U]; bool ok[U];
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            rr[u] = r; cs[u] = cc;
+                            const int t = q_lo + r;
+                            ok[u] = t >= 0 && t <= tmax;
+                            const int tcl = min(max(t, 0), tmax);          // clamped: the load is always legal, the value is dropped when !ok
+                            const uint4* p = reinterpret_cast<const uint4*>(Xb + ((size_t)tcl * a.x_ld + ch0 + cc * 8) * 4);
+                            raw[u][0] = ld_nc(p);
+                            raw[u][1] = ld_nc(p + 1);
+                            r += dr; cc += dc;
+                            if (cc >= cpr) { cc -= cpr; ++r; }
+                        }
+#pragma unroll
+                        for (int u = 0; u < U; ++u)
+                            if (i + u * A_THREADS < total) {
+                                uint4 vl;
+                                const uint4 v = convert_piece(a, raw[u][0], raw[u][1], ok[u], vl);
+                                const size_t o = ((size_t)cs[u] * a.Rp + rr[u]) * 16;
+                                *reinterpret_cast<uint4*>(dst + o) = v;
+                                if (a.split) *reinterpret_cast<uint4*>(dst + a.a_half + o) = vl;
+                            }
+                    }
+                    fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core (async proxy)
+                    mbar_arrive(bars.a_full(slot));
+                    if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == T_WARP) {
+        // ===== TMA issuer (planar input): one (128 + halo)-row block per accumulator sub-tile and channel chunk =====
+        if (TMA_IN && lane == 0 && !(a.dbg & 2)) {
+            int slot = 0; uint32_t phase = 0;
+            const int cg_per_chunk = a.KC >> 3;
+            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+                const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+                const int q_lo = rt * a.msub * 128 + a.off_lo;
+                for (int kc = 0; kc < n_chunks; ++kc) {
+                    mbar_wait(bars.a_empty(slot), phase ^ 1);
+                    const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
+                    mbar_expect_tx(bar, (uint32_t)a.a_tx);
+                    const uint32_t dst = smem_u32(A_smem + (size_t)slot * a.a_bytes);
+                    for (int ms = 0; ms < a.msub; ++ms)
+                        tma_load_4d(dst + (uint32_t)(ms * a.a_blk_bytes), &tmap, 0, q_lo + ms * 128, kc * cg_per_chunk, b, bar);
+                    if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
+                }
             }
         }
     } else if (warp == W_WARP) {
         // ===== weight producer: 1-D bulk copies of pre-tiled blobs =====
         if (lane == 0 && !(a.dbg & 1)) {
-            int iw = 0;
+            int slot = 0; uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                 const int nt = tile % a.n_ntiles;
                 const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
-                for (int st = 0; st < n_stages; ++st, ++iw) {
-                    const int slot = iw % W_STAGES;
-                    mbar_wait(W_EMPTY(slot), ((iw / W_STAGES) & 1) ^ 1);
+                for (int st = 0; st < n_stages; ++st) {
+                    mbar_wait(bars.w_empty(slot), phase ^ 1);
                     const int nb = min(a.G, a.n_blobs - st * a.G);
                     const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
-                    mbar_expect_tx(W_FULL(slot), bytes);
-                    bulk_g2s(smem_u32(W_smem + (size_t)slot * a.stage_bytes), src + (size_t)st * a.G * a.blob_bytes, bytes, W_FULL(slot));
+                    mbar_expect_tx(bars.w_full(slot), bytes);
+                    bulk_g2s(smem_u32(W_smem + (size_t)slot * a.stage_bytes), src + (size_t)st * a.G * a.blob_bytes, bytes, bars.w_full(slot));
+                    if (++slot == W_STAGES) { slot = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == MMA_WARP) {
-        // ===== MMA issuer: the whole warp walks the (warp-uniform) loops, one elected lane issues tcgen05.mma / commit =====
-        // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
-        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t w_lbo = (uint32_t)NT * 16u;
-        // descriptor halves: hi = SBO (128 B) | version 1; lo = start address | LBO — advancing an operand = adding to lo
-        const uint32_t desc_hi = (128u >> 4) | (1u << 14);
-        const uint32_t a_lo_base = (((uint32_t)a.Rp * 16u) >> 4) << 16, w_lo_base = (w_lbo >> 4) << 16;
-        int iw = 0, ia = 0, it = 0;
-        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-            const int accb = it & 1;
-            mbar_wait(ACC_EMPTY(accb), ((it >> 1) & 1) ^ 1);          // epilogue has drained this accumulator set
-            tc_fence_after();
-            const uint32_t tacc = tmem_base + (uint32_t)(accb * acc_cols);
-            int blob = 0;
-            for (int st = 0; st < n_stages; ++st, ++iw) {
-                const int slot = iw % W_STAGES;
-                if (!(a.dbg & 1)) mbar_wait(W_FULL(slot), (iw / W_STAGES) & 1);
-                tc_fence_after();
-                const uint32_t wbase = smem_u32(W_smem + (size_t)slot * a.stage_bytes);
-                for (int g = 0; g < a.G && blob < a.n_blobs; ++g, ++blob) {
-                    const int rem = blob % blobs_per_chunk;
-                    const int sub = rem / a.taps, j = rem % a.taps;
-                    const int aslot = ia & 1;
-                    if (rem == 0 && !(a.dbg & 2)) { mbar_wait(A_FULL(aslot), (ia >> 1) & 1); tc_fence_after(); }
-                    const uint32_t abase = smem_u32(A_smem + (size_t)aslot * a.a_bytes);
-                    const int rowoff = a.off0 + j * a.tstep - a.off_lo;
-                    if (elect_one()) {
-                        for (int ks = 0; ks < a.KW / 16 && !(a.dbg & 8); ++ks) {
-                            const uint32_t aaddr = abase + (uint32_t)((((sub * a.KW + ks * 16) >> 3) * a.Rp + rowoff) * 16);
-                            const uint32_t waddr = wbase + (uint32_t)g * a.blob_bytes + (uint32_t)ks * 2u * w_lbo;
-                            const uint32_t a_lo = a_lo_base | (aaddr >> 4), w_lo = w_lo_base | (waddr >> 4);
-                            const uint64_t bdesc = ((uint64_t)desc_hi << 32) | w_lo;
-                            const uint32_t acc = (blob > 0 || ks > 0) ? 1u : 0u;
-                            if (!a.split) {
-#pragma unroll
-                                for (int ms = 0; ms < 8; ++ms)
-                                    if (ms < a.msub)
-                                        tc_mma(tacc + (uint32_t)(ms * NT), ((uint64_t)desc_hi << 32) | (a_lo + (uint32_t)ms * 128u), bdesc, idesc, acc);
-                            } else {
-                                const uint64_t bdesc_lo = ((uint64_t)desc_hi << 32) | (w_lo + (uint32_t)(a.blob_bytes >> 5));
-                                const uint32_t a_lo2 = a_lo + (uint32_t)(a.a_half >> 4);
-#pragma unroll
-                                for (int ms = 0; ms < 8; ++ms)
-                                    if (ms < a.msub) {
-                                        const uint64_t ad_hi = ((uint64_t)desc_hi << 32) | (a_lo + (uint32_t)ms * 128u);
-                                        const uint64_t ad_lo = ((uint64_t)desc_hi << 32) | (a_lo2 + (uint32_t)ms * 128u);
-                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc, idesc, acc);
-                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_lo, bdesc, idesc, 1u);
-                                        tc_mma(tacc + (uint32_t)(ms * NT), ad_hi, bdesc_lo, idesc, 1u);
-                                    }
-                            }
-                        }
-                        if (rem == blobs_per_chunk - 1 && !(a.dbg & 2)) tc_commit(A_EMPTY(aslot));     // chunk consumed -> slot may be overwritten
-                    }
-                    __syncwarp();
-                    if (rem == blobs_per_chunk - 1) ++ia;
+        // ===== MMA issuer: one thread; specialised on the number of accumulator sub-tiles =====
+        if (lane == 0) {
+            const uint32_t as = smem_u32(A_smem), ws = smem_u32(W_smem);
+            if (a.split) {
+                switch (a.msub) {
+                    case 1: mma_role<NT, 1, true>(a, bars, as, ws, tmem_base); break;
+                    case 2: mma_role<NT, 2, true>(a, bars, as, ws, tmem_base); break;
+                    default: break;
                 }
-                if (!(a.dbg & 1) && elect_one()) tc_commit(W_EMPTY(slot));
-                __syncwarp();
+            } else {
+                switch (a.msub) {
+                    case 1: mma_role<NT, 1, false>(a, bars, as, ws, tmem_base); break;
+                    case 2: if (NT <= 128) mma_role<NT, 2, false>(a, bars, as, ws, tmem_base); break;
+                    case 4: if (NT <= 64) mma_role<NT, 4, false>(a, bars, as, ws, tmem_base); break;
+                    case 8: if (NT <= 32) mma_role<NT, 8, false>(a, bars, as, ws, tmem_base); break;
+                    default: break;
+                }
             }
-            if (elect_one()) tc_commit(ACC_FULL(accb));
-            __syncwarp();
         }
+        __syncwarp();
     } else {
         // ===== epilogue (8 warps): TMEM -> registers -> bias / activation / residual / scale -> global =====
         const int quad = warp & 3, half = warp >> 2;
@@ -358,80 +470,105 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         const int c_begin = half ? c_split : 0, c_end = half ? NT : c_split;
         const float* R1f = reinterpret_cast<const float*>(a.R1); const bf16* R1h = reinterpret_cast<const bf16*>(a.R1);
         const float* R2f = reinterpret_cast<const float*>(a.R2); const bf16* R2h = reinterpret_cast<const bf16*>(a.R2);
-        const int gc = ((a.R1 || a.R2) && !a.r_bf16) ? 16 : 32;     // columns per residual prefetch group (4 x 16 bytes)
         int it = 0;
         for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
             const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
             const int n0 = nt * NT, q0 = rt * a.msub * 128;
             const int accb = it & 1;
-            mbar_wait(ACC_FULL(accb), (it >> 1) & 1);
+            mbar_wait(bars.acc_full(accb), (it >> 1) & 1);
             tc_fence_after();
             const long boff = (long)b * a.y_bs;
-            for (int ms = 0; ms < a.msub; ++ms) {
-                const int q = q0 + ms * 128 + quad * 32 + lane;
-                const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT);
-                for (int cg = c_begin; cg < c_end && !(a.dbg & 4); cg += gc) {
-                    const int ncol = min(gc, c_end - cg);
-                    const long eg = (long)q * a.orow + a.ooff + n0 + cg;
-                    const bool rowok = q < a.Q;
-                    // prefetch the residual values of this column group (up to 4 x 16 bytes each) before touching TMEM
-                    uint4 r1[4], r2[4];
+            if (a.dbg & 4) {
+                // what-if: no epilogue work
+            } else if (a.y_planar) {
+                // ---- planar bf16 output [Cout/8][y_T][8]: lane = row, one 16-byte store per 8 columns; the residuals of
+                //      the next 16-column unit are fetched before the current one is read from TMEM ----
+                const int ncg = (c_end - c_begin) >> 4;
+                const int units = a.msub * ncg;
+                long o0 = -1, o1 = -1;
+                uint4 r1a = make_uint4(0u, 0u, 0u, 0u), r1b = r1a, r2a = r1a, r2b = r1a;
+                auto fetch = [&](int ms, int cgi, long& p0, long& p1, uint4& x1a, uint4& x1b, uint4& x2a, uint4& x2b) {
+                    const int q = q0 + ms * 128 + quad * 32 + lane, n = n0 + c_begin + cgi * 16;
+                    p0 = planar_off(a, q, n); p1 = planar_off(a, q, n + 8);
+                    x1a = x1b = x2a = x2b = make_uint4(0u, 0u, 0u, 0u);
+                    if (a.R1) { if (p0 >= 0) x1a = *reinterpret_cast<const uint4*>(R1h + boff + p0); if (p1 >= 0) x1b = *reinterpret_cast<const uint4*>(R1h + boff + p1); }
+                    if (a.R2) { if (p0 >= 0) x2a = *reinterpret_cast<const uint4*>(R2h + boff + p0); if (p1 >= 0) x2b = *reinterpret_cast<const uint4*>(R2h + boff + p1); }
+                };
+                if (units > 0) fetch(0, 0, o0, o1, r1a, r1b, r2a, r2b);
+                int ms = 0, cgi = 0;
+                for (int u = 0; u < units; ++u) {
+                    int ms_n = ms, cgi_n = cgi + 1;
+                    if (cgi_n == ncg) { cgi_n = 0; ++ms_n; }
+                    long p0 = -1, p1 = -1; uint4 x1a, x1b, x2a, x2b;
+                    x1a = x1b = x2a = x2b = make_uint4(0u, 0u, 0u, 0u);
+                    if (u + 1 < units) fetch(ms_n, cgi_n, p0, p1, x1a, x1b, x2a, x2b);
+                    float v[16];
+                    const int cc = c_begin + cgi * 16;
+                    tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT + cc), v);
+                    epi_bias_act(a, v, bias_s + n0 + cc);
+                    if (a.R1) { add_bf16x8(v, r1a); add_bf16x8(v + 8, r1b); }
+                    if (a.R2) { add_bf16x8(v, r2a); add_bf16x8(v + 8, r2b); }
+                    epi_scale_post(a, v);
+                    if (o0 >= 0) *reinterpret_cast<uint4*>(a.Y16 + boff + o0) = pack8(v);
+                    if (o1 >= 0) *reinterpret_cast<uint4*>(a.Y16 + boff + o1) = pack8(v + 8);
+                    o0 = p0; o1 = p1; r1a = x1a; r1b = x1b; r2a = x2a; r2b = x2b;
+                    ms = ms_n; cgi = cgi_n;
+                }
+            } else {
+                // ---- row-major output (fp32 and/or bf16): lane = row, 16 consecutive columns per store group ----
+                const int gc = ((a.R1 || a.R2) && !a.r_bf16) ? 16 : 32;     // columns per residual prefetch group (4 x 16 bytes)
+                for (int ms = 0; ms < a.msub; ++ms) {
+                    const int q = q0 + ms * 128 + quad * 32 + lane;
+                    const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT);
+                    for (int cg = c_begin; cg < c_end; cg += gc) {
+                        const int ncol = min(gc, c_end - cg);
+                        const long eg = (long)q * a.orow + a.ooff + n0 + cg;
+                        const bool rowok = q < a.Q;
+                        // prefetch the residual values of this column group (up to 4 x 16 bytes each) before touching TMEM
+                        uint4 r1[4], r2[4];
 #pragma unroll
-                    for (int h = 0; h < 4; ++h) {
-                        r1[h] = make_uint4(0u, 0u, 0u, 0u); r2[h] = r1[h];
-                        const int col = a.r_bf16 ? h * 8 : h * 4;                       // first column covered by piece h
-                        const long e = eg + (col & ~15);
-                        const bool ok = rowok && col < ncol && e >= 0 && e + 16 <= a.y_limit;
-                        if (ok && a.R1) r1[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R1h + boff + eg + col)
-                                                        : *reinterpret_cast<const uint4*>(R1f + boff + eg + col);
-                        if (ok && a.R2) r2[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R2h + boff + eg + col)
-                                                        : *reinterpret_cast<const uint4*>(R2f + boff + eg + col);
-                    }
+                        for (int h = 0; h < 4; ++h) {
+                            r1[h] = make_uint4(0u, 0u, 0u, 0u); r2[h] = r1[h];
+                            const int col = a.r_bf16 ? h * 8 : h * 4;                       // first column covered by piece h
+                            const long e = eg + (col & ~15);
+                            const bool ok = rowok && col < ncol && e >= 0 && e + 16 <= a.y_limit;
+                            if (ok && a.R1) r1[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R1h + boff + eg + col)
+                                                            : *reinterpret_cast<const uint4*>(R1f + boff + eg + col);
+                            if (ok && a.R2) r2[h] = a.r_bf16 ? *reinterpret_cast<const uint4*>(R2h + boff + eg + col)
+                                                            : *reinterpret_cast<const uint4*>(R2f + boff + eg + col);
+                        }
 #pragma unroll
-                    for (int k16 = 0; k16 < 2; ++k16) {
-                        const int cc = k16 * 16;
-                        if (cc < ncol) {                                   // warp-uniform
-                            float v[16];
-                            tmem_ld16(trow + (uint32_t)(cg + cc), v);
-                            const long e = eg + cc;
-                            if (rowok && e >= 0 && e + 16 <= a.y_limit) {
-                                const float* bp = bias_s + n0 + cg + cc;
+                        for (int k16 = 0; k16 < 2; ++k16) {
+                            const int cc = k16 * 16;
+                            if (cc < ncol) {                                   // warp-uniform
+                                float v[16];
+                                tmem_ld16(trow + (uint32_t)(cg + cc), v);
+                                const long e = eg + cc;
+                                if (rowok && e >= 0 && e + 16 <= a.y_limit) {
+                                    epi_bias_act(a, v, bias_s + n0 + cg + cc);
+                                    if (a.R1 || a.R2) {
+                                        if (a.r_bf16) {
 #pragma unroll
-                                for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i] + bp[i], a.out_act, a.out_slope);
-                                if (a.R1 || a.R2) {
-                                    if (a.r_bf16) {
+                                            for (int h = 0; h < 2; ++h) { add_bf16x8(v + h * 8, r1[(k16 * 2 + h) & 3]); add_bf16x8(v + h * 8, r2[(k16 * 2 + h) & 3]); }
+                                        } else {
 #pragma unroll
-                                        for (int h = 0; h < 2; ++h) {
-                                            const uint4 u = r1[(k16 * 2 + h) & 3], w = r2[(k16 * 2 + h) & 3];
-                                            float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
-                                            float2 s0 = unpack_bf16(w.x), s1 = unpack_bf16(w.y), s2 = unpack_bf16(w.z), s3 = unpack_bf16(w.w);
-                                            v[h * 8 + 0] += t0.x + s0.x; v[h * 8 + 1] += t0.y + s0.y; v[h * 8 + 2] += t1.x + s1.x; v[h * 8 + 3] += t1.y + s1.y;
-                                            v[h * 8 + 4] += t2.x + s2.x; v[h * 8 + 5] += t2.y + s2.y; v[h * 8 + 6] += t3.x + s3.x; v[h * 8 + 7] += t3.y + s3.y;
-                                        }
-                                    } else {
-#pragma unroll
-                                        for (int h = 0; h < 4; ++h) {
-                                            const uint4 u = r1[(k16 * 4 + h) & 3], w = r2[(k16 * 4 + h) & 3];
-                                            v[h * 4 + 0] += __uint_as_float(u.x) + __uint_as_float(w.x); v[h * 4 + 1] += __uint_as_float(u.y) + __uint_as_float(w.y);
-                                            v[h * 4 + 2] += __uint_as_float(u.z) + __uint_as_float(w.z); v[h * 4 + 3] += __uint_as_float(u.w) + __uint_as_float(w.w);
+                                            for (int h = 0; h < 4; ++h) {
+                                                const uint4 u = r1[(k16 * 4 + h) & 3], w = r2[(k16 * 4 + h) & 3];
+                                                v[h * 4 + 0] += __uint_as_float(u.x) + __uint_as_float(w.x); v[h * 4 + 1] += __uint_as_float(u.y) + __uint_as_float(w.y);
+                                                v[h * 4 + 2] += __uint_as_float(u.z) + __uint_as_float(w.z); v[h * 4 + 3] += __uint_as_float(u.w) + __uint_as_float(w.w);
+                                            }
                                         }
                                     }
-                                }
-                                if (a.out_scale != 1.f) {
+                                    epi_scale_post(a, v);
+                                    if (a.Y) {
+                                        float4* p = reinterpret_cast<float4*>(a.Y + boff + e);
 #pragma unroll
-                                    for (int i = 0; i < 16; ++i) v[i] *= a.out_scale;
-                                }
-                                if (a.Y) {
-                                    float4* p = reinterpret_cast<float4*>(a.Y + boff + e);
-#pragma unroll
-                                    for (int h = 0; h < 4; ++h) p[h] = make_float4(v[h * 4], v[h * 4 + 1], v[h * 4 + 2], v[h * 4 + 3]);
-                                }
-                                if (a.Y16) {
-                                    uint4* p = reinterpret_cast<uint4*>(a.Y16 + boff + e);
-#pragma unroll
-                                    for (int h = 0; h < 2; ++h)
-                                        p[h] = make_uint4(pack_bf16(v[h * 8], v[h * 8 + 1]), pack_bf16(v[h * 8 + 2], v[h * 8 + 3]),
-                                                          pack_bf16(v[h * 8 + 4], v[h * 8 + 5]), pack_bf16(v[h * 8 + 6], v[h * 8 + 7]));
+                                        for (int h = 0; h < 4; ++h) p[h] = make_float4(v[h * 4], v[h * 4 + 1], v[h * 4 + 2], v[h * 4 + 3]);
+                                    }
+                                    if (a.Y16) {
+                                        uint4* p = reinterpret_cast<uint4*>(a.Y16 + boff + e);
+                                        p[0] = pack8(v); p[1] = pack8(v + 8);
+                                    }
                                 }
                             }
                         }
@@ -440,7 +577,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             }
             tc_fence_before();                              // order this warp's tcgen05.ld before the release below
             __syncwarp();
-            if (lane == 0) mbar_arrive(ACC_EMPTY(accb));
+            if (lane == 0) mbar_arrive(bars.acc_empty(accb));
         }
     }
     tc_fence_before();
@@ -470,14 +607,62 @@ __global__ void k_tile_w(const float* __restrict__ w32, bf16* __restrict__ out, 
     out[blob * 2 * KW * NT + (long)KW * NT + within] = __float2bfloat16_rn(w - __bfloat162float(hi));
 }
 
-template <int NT, bool XF32>
-void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
+// row-major fp32 [B][T][C] <-> planar bf16 [B][C/8][T][8] (the HiFi-GAN activation layout); one 16-byte piece per thread
+__global__ void k_to_planar(const float* __restrict__ x, bf16* __restrict__ out, int T, int C, long total_pieces) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total_pieces) return;
+    const int cg = C >> 3;
+    long t = i % T; long r = i / T; int g = (int)(r % cg); long b = r / cg;
+    const float4* p = reinterpret_cast<const float4*>(x + ((b * T + t) * C + g * 8));
+    const float4 a = p[0], c = p[1];
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(c.x, c.y), pack_bf16(c.z, c.w));
+}
+__global__ void k_from_planar(const bf16* __restrict__ x, float* __restrict__ out, int T, int C, long total_pieces) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total_pieces) return;
+    const int cg = C >> 3;
+    long t = i % T; long r = i / T; int g = (int)(r % cg); long b = r / cg;
+    const uint4 u = reinterpret_cast<const uint4*>(x)[i];
+    const float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
+    float4* p = reinterpret_cast<float4*>(out + ((b * T + t) * C + g * 8));
+    p[0] = make_float4(f0.x, f0.y, f1.x, f1.y); p[1] = make_float4(f2.x, f2.y, f3.x, f3.y);
+}
+
+template <int NT, bool TMA_IN>
+void launch_inst(const TcArgs& a, const CUtensorMap& tm, dim3 grid, size_t smem, cudaStream_t s) {
     static bool attr = false;
-    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, XF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
-    k_conv_tc<NT, XF32><<<grid, NTHREADS, smem, s>>>(a);
+    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
+    k_conv_tc<NT, TMA_IN><<<grid, NTHREADS, smem, s>>>(a, tm);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        MASG_CHECK(p != nullptr && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
 }
 
 }  // namespace
+
+void launch_to_planar(masg_ctx* c, cudaStream_t s, const float* x, bf16* out, int B, int T, int C) {
+    MASG_CHECK(C % 8 == 0, "planar layout needs C %% 8 == 0 (C=%d)", C);
+    const long n = (long)B * T * (C / 8);
+    k_to_planar<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, out, T, C, n);
+    c->launches++;
+}
+void launch_from_planar(masg_ctx* c, cudaStream_t s, const bf16* x, float* out, int B, int T, int C) {
+    const long n = (long)B * T * (C / 8);
+    k_from_planar<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, out, T, C, n);
+    c->launches++;
+}
 
 void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
     MASG_CHECK(d.w32 != nullptr, "tc_prepare_weights: fp32 GEMM weights missing");
@@ -500,50 +685,78 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
 
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
     MASG_CHECK(d.w16 != nullptr && d.NT > 0, "conv_tc: bf16 weights not committed");
-    MASG_CHECK(io.x_ld % 8 == 0 && io.x_bs % 8 == 0, "conv_tc: x_ld=%d / batch stride must be multiples of 8", io.x_ld);
     MASG_CHECK(io.Y != nullptr || io.Y16 != nullptr, "conv_tc: no output tensor");
     MASG_CHECK(d.N <= BIAS_MAX, "conv_tc: N=%d exceeds the staged bias row (%d)", d.N, BIAS_MAX);
+    MASG_CHECK(!io.x_bf16 || io.x_planar, "conv_tc: bf16 activations must be planar [B][C/8][T][8]");
+    MASG_CHECK(!d.split || !io.x_planar, "conv_tc: split-bf16 layers take row-major fp32 activations");
     if (io.Q <= 0 || io.B <= 0) return;
+    const bool tma_in = io.x_planar != 0;
     TcArgs a;
+    memset(&a, 0, sizeof(a));
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
     a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
     a.KW = d.KW; a.split = d.split;
-    MASG_CHECK(!d.split || !io.x_bf16, "conv_tc: split-bf16 layers take fp32 activations");
     const int NT = d.NT;
     const size_t a_mul = d.split ? 2 : 1;
     int off_lo = d.off0, off_hi = d.off0;
     for (int j = 0; j < d.taps; ++j) { int o = d.off0 + j * d.tstep; off_lo = std::min(off_lo, o); off_hi = std::max(off_hi, o); }
     const int halo = off_hi - off_lo;
     a.off_lo = off_lo;
-    // rows per tile: two accumulator sets share the 512 TMEM columns (2 * msub * NT <= 512); fewer sub-tiles when that
-    // would leave SMs without a tile
-    int msub = std::min(std::max(256 / NT, 1), (io.Q + 127) / 128);
+    // rows per tile: two accumulator sets share the 512 TMEM columns (2 * msub * NT <= 512), msub a power of two;
+    // fewer sub-tiles when that would leave SMs without a tile
+    int msub = 1;
+    while (msub * 2 * NT <= 256 && msub * 128 < io.Q) msub *= 2;
+    if (d.split) msub = std::min(msub, 2);
     const int ntiles_n = d.N / NT;
-    while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub = (msub + 1) / 2;
-    // channel chunk: the largest multiple of KW dividing Cin whose staged tile (rows + halo) fits one activation slot
-    int KC = 0, Rp = 0;
-    for (;;) {
-        const int rows = msub * 128 + halo;
-        auto pad_rows = [&](int kc) {
-            const int cpr = kc / 8;
-            const int want = cpr >= 8 ? 1 : (8 / std::max(cpr, 1)) % 8;    // bank-conflict-free staging stores
-            int rp = rows;
-            while ((rp % 8) != want && !(cpr >= 8 && (rp & 1))) ++rp;
-            return rp;
-        };
-        for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
-            if ((d.Cin / d.KW) % m) continue;
-            const int kc = m * d.KW;
-            if ((size_t)pad_rows(kc) * kc * 2 * a_mul <= (size_t)A_SLOT_BUDGET) { KC = kc; Rp = pad_rows(kc); }
+    while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub /= 2;
+    int KC = 0;
+    if (tma_in) {
+        // one [KC/8][Rb][8] block per accumulator sub-tile (its 128 rows + the halo), filled by one TMA tile copy
+        MASG_CHECK(io.x_ld == d.Cin, "conv_tc: planar input must have exactly Cin=%d channels", d.Cin);
+        const int Rb = (128 + halo + 7) & ~7;
+        MASG_CHECK(Rb <= 256, "conv_tc: conv halo %d exceeds the TMA box (Cin=%d taps=%d tstep=%d)", halo, d.Cin, d.taps, d.tstep);
+        for (;;) {
+            for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
+                if ((d.Cin / d.KW) % m) continue;
+                const int kc = m * d.KW;
+                if ((size_t)msub * Rb * kc * 2 <= (size_t)A_SLOT_BYTES && kc / 8 <= 256) KC = kc;
+            }
+            if (KC || msub == 1) break;
+            msub /= 2;
         }
-        if (KC || msub == 1) break;
-        msub = (msub + 1) / 2;
+        MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
+        a.Rp = Rb; a.rows = Rb; a.a_blk_bytes = Rb * KC * 2; a.a_tx = msub * a.a_blk_bytes;
+        a.a_bytes = (a.a_tx + 1023) & ~1023; a.a_half = 0;
+        a.a_lbo16 = Rb; a.a_ms16 = a.a_blk_bytes >> 4;
+    } else {
+        // one shared [KC/8][Rp][8] tile (rows + halo) staged by the worker warps; sub-tile ms starts 128 rows further down
+        MASG_CHECK(io.x_ld % 8 == 0 && io.x_bs % 8 == 0, "conv_tc: x_ld=%d / batch stride must be multiples of 8", io.x_ld);
+        int Rp = 0;
+        for (;;) {
+            const int rows = msub * 128 + halo;
+            auto pad_rows = [&](int kc) {
+                const int cpr = kc / 8;
+                const int want = cpr >= 8 ? 1 : (8 / std::max(cpr, 1)) % 8;    // bank-conflict-free staging stores
+                int rp = rows;
+                while ((rp % 8) != want && !(cpr >= 8 && (rp & 1))) ++rp;
+                return rp;
+            };
+            for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
+                if ((d.Cin / d.KW) % m) continue;
+                const int kc = m * d.KW;
+                if ((size_t)pad_rows(kc) * kc * 2 * a_mul + 256 <= (size_t)A_SLOT_BYTES) { KC = kc; Rp = pad_rows(kc); }
+            }
+            if (KC || msub == 1) break;
+            msub /= 2;
+        }
+        MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
+        a.rows = msub * 128 + halo; a.Rp = Rp;
+        a.a_half = (((KC / 8) * Rp * 16) + 127) & ~127;
+        a.a_bytes = a.a_half * (int)a_mul;
+        a.a_lbo16 = Rp; a.a_ms16 = 128;
     }
-    MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
-    a.msub = msub; a.rows = msub * 128 + halo; a.Rp = Rp; a.KC = KC;
-    a.a_half = (((KC / 8) * Rp * 16) + 127) & ~127;
-    a.a_bytes = a.a_half * (int)a_mul;
+    a.msub = msub; a.KC = KC;
     a.blob_bytes = d.KW * NT * 2 * (int)a_mul;
     a.G = std::max(1, W_STAGE_BYTES / a.blob_bytes);
     a.stage_bytes = a.G * a.blob_bytes;
@@ -555,18 +768,41 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.total_tiles = io.B * a.row_tiles * ntiles_n;
     a.Y = io.Y; a.Y16 = io.Y16; a.y_bs = io.y_bs; a.y_limit = io.y_limit; a.orow = d.orow ? d.orow : d.N; a.ooff = d.ooff; a.Q = io.Q;
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
-    a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale;
+    a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale; a.post_slope = io.post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
-    MASG_CHECK(a.orow % 16 == 0 && a.ooff % 16 == 0 && a.y_bs % 16 == 0 && a.bias_mod % 16 == 0,
-               "conv_tc: output row stride/offset/bias period must be multiples of 16");
-    const size_t smem = SMEM_HDR + BIAS_MAX * 4 + 2 * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
+    a.y_planar = io.y_planar;
+    if (io.y_planar) {
+        MASG_CHECK(io.Y16 != nullptr && io.Y == nullptr && io.y_T > 0, "conv_tc: planar output is bf16 only and needs y_T");
+        MASG_CHECK((a.bias_mod & (a.bias_mod - 1)) == 0 && a.bias_mod >= 8, "conv_tc: planar output needs a power-of-two channel count (%d)", a.bias_mod);
+        MASG_CHECK((io.R1 == nullptr && io.R2 == nullptr) || io.r_bf16, "conv_tc: planar residuals must be bf16");
+        int sh = 0; while ((1 << sh) < a.bias_mod) ++sh;
+        a.cout_shift = sh; a.y_T = io.y_T; a.up = d.up > 0 ? d.up : 1; a.up_pad = d.up_pad;
+        MASG_CHECK(d.N == a.bias_mod * a.up || d.up == 0, "conv_tc: transposed-conv column count mismatch");
+    } else {
+        MASG_CHECK(a.orow % 16 == 0 && a.ooff % 16 == 0 && a.y_bs % 16 == 0 && a.bias_mod % 16 == 0,
+                   "conv_tc: output row stride/offset/bias period must be multiples of 16");
+    }
+    MASG_CHECK(a.in_act == ACT_NONE || a.in_act == ACT_LRELU || !tma_in, "conv_tc: planar input supports leaky-relu only");
+    const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
+    CUtensorMap tm;
+    memset(&tm, 0, sizeof(tm));
+    if (tma_in) {
+        const cuuint64_t dims[4] = {8, (cuuint64_t)io.Tin, (cuuint64_t)(d.Cin / 8), (cuuint64_t)io.B};
+        const cuuint64_t strides[3] = {16, (cuuint64_t)io.Tin * 16, (cuuint64_t)io.Tin * d.Cin * 2};
+        const cuuint32_t box[4] = {8, (cuuint32_t)a.Rp, (cuuint32_t)(KC / 8), 1};
+        const cuuint32_t estr[4] = {1, 1, 1, 1};
+        MASG_CHECK(((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
+        CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(io.X), dims, strides, box, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        MASG_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) for T=%d C=%d B=%d box rows %d", (int)r, io.Tin, d.Cin, io.B, a.Rp);
+    }
     static int n_sm = 0;
     if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
     dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
-    const bool xf32 = !io.x_bf16;
 #define MASG_TC_CASE(NTV)                                                                       \
-    case NTV: if (xf32) launch_inst<NTV, true>(a, grid, smem, s); else launch_inst<NTV, false>(a, grid, smem, s); break;
+    case NTV: if (tma_in) launch_inst<NTV, true>(a, tm, grid, smem, s); else launch_inst<NTV, false>(a, tm, grid, smem, s); break;
     switch (NT) {
         MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128) MASG_TC_CASE(256)
         default: MASG_CHECK(false, "conv_tc: unsupported N tile %d", NT);

@@ -48,7 +48,7 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
         MASG_CHECK(sh[0] == cin && sh[1] == cout && sh[2] == k && k == 2 * u, "%s must be (%d,%d,%d) with k = 2*stride", name.c_str(), cin, cout, k);
         ConvDesc d;
         d.Cin = cin; d.N = u * cout; d.taps = 2; d.off0 = 0; d.tstep = -1; d.bias_mod = cout;
-        d.orow = (long)u * cout; d.ooff = -(long)((k - u) / 2) * cout;
+        d.orow = (long)u * cout; d.ooff = -(long)((k - u) / 2) * cout; d.up = u; d.up_pad = (k - u) / 2;
         float* w32 = dev_alloc<float>(c, (size_t)2 * cin * u * cout);
         launch_repack_convT_w(c, s, w, cin, cout, k, u, w32);
         d.w32 = w32; d.bias = bias_of(c, name, cout);
@@ -93,6 +93,58 @@ static void convS(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const void* X,
     launch_conv(c, s, d, io);
 }
 
+// MASG_PREC_BF16 graph: activations are planar bf16 [B][C/8][S][8] (the tcgen05 operand layout, moved by TMA).  Where a
+// tensor is only ever consumed through a leaky-relu (conv_pre output, convs1 outputs, the MRF mean) the producer's
+// epilogue applies it; where the raw tensor is also a residual (ups / convs2 outputs) the consumer applies it in
+// shared memory.
+static void convP(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const void* X, bool x_planar, int B, long Sin, bf16* Y, long Sout,
+                  int in_act, int out_act, const bf16* R1, const bf16* R2, float out_scale, float post_slope, int Q) {
+    ConvIO io;
+    io.X = X; io.x_bf16 = x_planar; io.x_planar = x_planar; io.x_ld = d.Cin; io.x_bs = Sin * d.Cin; io.Tin = (int)Sin;
+    io.Y16 = Y; io.y_planar = 1; io.y_T = (int)Sout; io.y_bs = Sout * (d.bias_mod ? d.bias_mod : d.N); io.y_limit = io.y_bs;
+    io.B = B; io.Q = Q;
+    io.in_act = in_act; io.in_slope = 0.1f; io.out_act = out_act; io.out_slope = 0.1f;
+    io.R1 = R1; io.R2 = R2; io.r_bf16 = 1; io.out_scale = out_scale; io.post_slope = post_slope;
+    launch_conv(c, s, d, io);
+}
+
+static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT, int B, int T, float* wav, int16_t* w16) {
+    Arena& ar = c->arena_b;
+    long S = T;
+    bf16* x = ar.get<bf16>((size_t)B * S * 512);
+    // conv_pre (models.py:151); its output only feeds leaky_relu -> ups[0] (models.py:152-153)
+    convP(c, s, c->hg_pre, melT, false, B, S, x, S, ACT_NONE, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)S);
+    for (int i = 0; i < 4; ++i) {
+        const int u = c->hg_up_rate[i], C = c->hg_ch[i + 1];
+        const long So = S * u;
+        const size_t n = (size_t)B * So * C;
+        bf16* xu = ar.get<bf16>(n); bf16* xs = ar.get<bf16>(n); bf16* h = ar.get<bf16>(n);
+        bf16* ya = ar.get<bf16>(n); bf16* yb = ar.get<bf16>(n);
+        convP(c, s, c->hg_ups[i], x, true, B, S, xu, So, ACT_NONE, ACT_NONE, nullptr, nullptr, 1.f, 1.f, (int)S + 1);
+        for (int j = 0; j < 3; ++j) {
+            const int rb = i * 3 + j;
+            const bf16* y = xu;
+            for (int m = 0; m < 3; ++m) {
+                // h = lrelu(c1(lrelu(y))); y' = c2(h) + y   (models.py:96-103)
+                convP(c, s, c->hg_c1[rb][m], y, true, B, So, h, So, ACT_LRELU, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)So);
+                if (m < 2) {
+                    bf16* yn = (y == ya) ? yb : ya;
+                    convP(c, s, c->hg_c2[rb][m], h, true, B, So, yn, So, ACT_NONE, ACT_NONE, y, nullptr, 1.f, 1.f, (int)So);
+                    y = yn;
+                } else {
+                    // last pair of the block: fold the MRF sum, the /3 and the leaky-relu that follows it (models.py:155-161:
+                    // slope 0.1 before the next upsampler, F.leaky_relu's default 0.01 before conv_post)
+                    const float post = j == 2 ? (i < 3 ? 0.1f : 0.01f) : 1.f;
+                    convP(c, s, c->hg_c2[rb][m], h, true, B, So, xs, So, ACT_NONE, ACT_NONE, y, j > 0 ? xs : nullptr,
+                          j == 2 ? (1.0f / 3.0f) : 1.f, post, (int)So);
+                }
+            }
+        }
+        x = xs; S = So;
+    }
+    launch_conv_post(c, s, x, 1, c->hg_post_w, c->hg_post_b, B, S, 1.0f, wav, w16);   // the leaky-relu is already applied
+}
+
 void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16) {
     MASG_CHECK(c->hg_ready, "HiFi-GAN weights not committed (call masg_hifigan_commit)");
     MASG_CHECK(B > 0 && T > 0, "empty vocoder input B=%d T=%d", B, T);
@@ -106,6 +158,7 @@ void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int 
         launch_transpose_mel(c, s, mel, B, 80, T, t);
         melT = t;
     }
+    if (bf) { hifigan_forward_bf16(c, s, melT, B, T, wav, w16); return; }
     long S = T;
     char* x = (char*)ar.alloc((size_t)B * S * 512 * esz);
     convS(c, s, c->hg_pre, melT, false, B, S, x, S, 512, ACT_NONE, 0.f, nullptr, nullptr, 1.f, (int)S);

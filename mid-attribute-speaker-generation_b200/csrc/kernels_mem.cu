@@ -441,23 +441,33 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
     int b = blockIdx.y; long s0 = (long)blockIdx.x * 256;
     int tid = threadIdx.x;
     if (tid < 224) ws[tid] = w[tid];
-    for (int i = tid; i < 262 * 8; i += 256) {
-        int r = i >> 3, c4 = i & 7;
-        long srow = s0 + r - 3;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (srow >= 0 && srow < S) {
-            if (XBF) {
-                uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(xv) + ((long)b * S + srow) * 32 + c4 * 4);
-                float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.x)), b2 = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u.y));
-                v = make_float4(a.x, a.y, b2.x, b2.y);
-            } else {
-                v = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xv) + ((long)b * S + srow) * 32)[c4];
+    if (XBF) {
+        // planar bf16 input [B][4][S][8]: one 16-byte piece = 8 channels of one sample
+        for (int i = tid; i < 262 * 4; i += 256) {
+            int g = i / 262, r = i % 262;
+            long srow = s0 + r - 3;
+            float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (srow >= 0 && srow < S) {
+                uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(xv) + (((long)b * 4 + g) * S + srow) * 8);
+                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { f[2 * k] = __uint_as_float(w4[k] << 16); f[2 * k + 1] = __uint_as_float(w4[k] & 0xffff0000u); }
             }
+            float* dst = &xs[r * 33 + g * 8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dst[k] = f[k] > 0.f ? f[k] : f[k] * slope;
         }
-        v.x = v.x > 0.f ? v.x : v.x * slope; v.y = v.y > 0.f ? v.y : v.y * slope;
-        v.z = v.z > 0.f ? v.z : v.z * slope; v.w = v.w > 0.f ? v.w : v.w * slope;
-        float* dst = &xs[r * 33 + c4 * 4];
-        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+    } else {
+        for (int i = tid; i < 262 * 8; i += 256) {
+            int r = i >> 3, c4 = i & 7;
+            long srow = s0 + r - 3;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (srow >= 0 && srow < S) v = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xv) + ((long)b * S + srow) * 32)[c4];
+            v.x = v.x > 0.f ? v.x : v.x * slope; v.y = v.y > 0.f ? v.y : v.y * slope;
+            v.z = v.z > 0.f ? v.z : v.z * slope; v.w = v.w > 0.f ? v.w : v.w * slope;
+            float* dst = &xs[r * 33 + c4 * 4];
+            dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+        }
     }
     __syncthreads();
     long sidx = s0 + tid;

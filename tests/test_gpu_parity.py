@@ -380,6 +380,8 @@ def test_conv_kernel_matches_torch(precision, case):
     from masg_b200 import _lib
     B, T, Cin, Cout, k, dil, ups, slope, act = case
     split = precision == "bf16-split"
+    if precision == "bf16-act" and (Cout & (Cout - 1)):
+        pytest.skip("planar bf16 activations (HiFi-GAN layout) need a power-of-two channel count")
     residual = precision == "bf16-act" and Cin == Cout and not ups       # bf16 activations in HBM + residual add (HiFi-GAN style)
     flags = (1 if split else 0) | (2 if precision == "bf16-act" else 0) | (4 if residual else 0)
     cx = _lib.default_context(DEV, "bf16" if precision.startswith("bf16") else precision)
