@@ -38,15 +38,16 @@
 
 namespace {
 
-// warp roles of the persistent CTA (608 threads, one CTA per SM)
+// warp roles of the persistent CTA (704 threads, one CTA per SM)
 constexpr int EPI_WARPS = 8;            // warps 0-7: epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column half)
-constexpr int MMA_WARP = 8;
-constexpr int W_WARP = 9;               // weight stream
-constexpr int T_WARP = 10;              // TMA issuer for planar activations
-constexpr int A_WARP0 = 11;             // activation workers
+constexpr int MMA_WARP = 8;             // warps 8-11: MMA issuers (one thread each, on the four different warp schedulers)
+constexpr int MMA_WARPS = 4;
+constexpr int W_WARP = 12;              // weight stream
+constexpr int T_WARP = 13;              // TMA issuer for planar activations
+constexpr int A_WARP0 = 14;             // activation workers
 constexpr int A_WARPS = 8;
 constexpr int A_THREADS = A_WARPS * 32;
-constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 608
+constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 704
 constexpr int W_STAGES = 4;
 constexpr int W_STAGE_BYTES = 16384;
 constexpr int A_SLOTS = 3;
@@ -88,8 +89,17 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok = 0;
     while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(20000u) : "memory");
+    }
+}
+// same, for roles that can afford to sleep: the hardware parks the thread for up to the hinted time instead of
+// re-polling, which keeps 16+ waiting warps from competing with the MMA thread for the shared-memory pipe
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(1000000u) : "memory");
     }
 }
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -147,10 +157,31 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
     return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
 }
-// leaky-relu on two packed bf16 values (fp32 arithmetic, one rounding)
-__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t u, float slope) {
-    const float2 f = unpack_bf16(u);
-    return pack_bf16(f.x > 0.f ? f.x : f.x * slope, f.y > 0.f ? f.y : f.y * slope);
+// leaky-relu on two packed bf16 values in three packed instructions.  The slope is carried as c1 + c2 (c1 = bf16(slope),
+// c2 = bf16(slope - c1)) and y = fma(x, c1, x * c2) is rounded once, so y is the correctly rounded bf16 of slope * x
+// to within 2e-6 relative; lrelu(x) = max(x, y) for 0 < slope < 1.
+struct Slope2 { uint32_t c1, c2; };
+__device__ __forceinline__ Slope2 make_slope2(float slope) {
+    const bf16 h = __float2bfloat16_rn(slope);
+    const float l = slope - __bfloat162float(h);
+    Slope2 r; r.c1 = pack_bf16(__bfloat162float(h), __bfloat162float(h)); r.c2 = pack_bf16(l, l);
+    return r;
+}
+__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t x, const Slope2 s) {
+    uint32_t t, y, r;
+    asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(t) : "r"(x), "r"(s.c2));
+    asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(y) : "r"(x), "r"(s.c1), "r"(t));
+    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(y));
+    return r;
+}
+// packed fp32 pair arithmetic (sm_100 f32x2 pipe): halves the instruction count of the epilogue's elementwise passes
+__device__ __forceinline__ void add_f32x2(float& a0, float& a1, const float b0, const float b1) {
+    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void mul_f32x2(float& a0, float& a1, const float b0, const float b1) {
+    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tmul.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -189,8 +220,13 @@ struct Bars {                                            // mbarrier addresses (
 // ---------------------------------------------------------------------------------------------
 // MMA issue loop (one thread).  Everything that changes per MMA is a running 32-bit add on the low descriptor word.
 // ---------------------------------------------------------------------------------------------
-template <int NT, int MS, bool SPLIT>
-__device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base) {
+// NI threads (one per MMA warp) share the work: issuer w owns accumulators w, w + NI, ... of the MS sub-tiles and walks
+// the same barrier sequence as the others; every release barrier therefore expects NI commits.  (Measured: one
+// thread sustains ~56 cycles per MMA, the tensor core needs 40 at N=32 and 48 at N=64 — shared-memory operand reads,
+// (4096 + 32 N) bytes at 128 B/clk — so two to four issuers are needed to keep it busy.)
+template <int NT, int MS, int NI, bool SPLIT>
+__device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base, const int w) {
+    constexpr int MSL = MS / NI;
     // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);                     // SBO = 128 B, descriptor version 1
@@ -207,7 +243,7 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
         const int accb = it & 1;
         mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1);             // epilogue has drained this accumulator set
         tc_fence_after();
-        const uint32_t tacc = tmem_base + (uint32_t)(accb * MS * NT);
+        const uint32_t tacc_w = tmem_base + (uint32_t)(accb * MS * NT + w * NT);
         uint32_t accum = 0;
         int g = a.G;                                                       // forces a stage fetch before the first blob
         bool have_stage = false;
@@ -227,13 +263,13 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
                         wbase16 = (w_smem + (uint32_t)wslot * (uint32_t)a.stage_bytes) >> 4;
                         g = 0; have_stage = true;
                     }
-                    uint32_t a_lo = a_fixed | a_tap, w_lo = w_fixed | (wbase16 + (uint32_t)g * blob16);
+                    uint32_t a_lo = (a_fixed | a_tap) + (uint32_t)w * a_ms, w_lo = w_fixed | (wbase16 + (uint32_t)g * blob16);
                     ++g;
                     if (no_mma) continue;
                     for (int ks = 0; ks < ksteps; ++ks, a_lo += a_ks, w_lo += w_ks) {
 #pragma unroll
-                        for (int ms = 0; ms < MS; ++ms) {
-                            const uint32_t d = tacc + (uint32_t)(ms * NT), al = a_lo + (uint32_t)ms * a_ms;
+                        for (int i = 0; i < MSL; ++i) {
+                            const uint32_t d = tacc_w + (uint32_t)(i * NI * NT), al = a_lo + (uint32_t)(i * NI) * a_ms;
                             tc_mma(d, al, w_lo, desc_hi, idesc, accum);
                             if (SPLIT) {
                                 tc_mma(d, al + a_half16, w_lo, desc_hi, idesc, 1u);
@@ -313,13 +349,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
     const int n_stages = (a.n_blobs + a.G - 1) / a.G;
     const int acc_cols = a.msub * NT;                      // TMEM columns of one accumulator set (two sets)
     const bool a_workers = !TMA_IN || a.in_act != ACT_NONE;
+    const int n_issuers = min(a.msub, MMA_WARPS);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_SLOTS; ++i) {
-            mbar_init(bars.a_full(i), a_workers ? A_THREADS : 1); mbar_init(bars.a_empty(i), 1); mbar_init(bars.a_raw(i), 1);
+            mbar_init(bars.a_full(i), a_workers ? A_THREADS : 1); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), 1);
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), 1); mbar_init(bars.acc_empty(i), EPI_WARPS); }
-        for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), n_issuers); mbar_init(bars.acc_empty(i), EPI_WARPS); }
+        for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), n_issuers); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         if (TMA_IN) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     }
@@ -342,15 +379,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
             // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled =====
             if (a.in_act != ACT_NONE) {
                 const int pieces = (a.msub * a.a_blk_bytes) >> 4;
+                const Slope2 sl = make_slope2(a.in_slope);
                 int slot = 0; uint32_t phase = 0;
                 for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                     for (int kc = 0; kc < n_chunks; ++kc) {
-                        mbar_wait(bars.a_raw(slot), phase);
+                        mbar_wait_relaxed(bars.a_raw(slot), phase);
                         uint4* p = reinterpret_cast<uint4*>(A_smem + (size_t)slot * a.a_bytes);
                         for (int i = tid; i < pieces; i += A_THREADS) {
                             uint4 v = p[i];
-                            v.x = lrelu_bf16x2(v.x, a.in_slope); v.y = lrelu_bf16x2(v.y, a.in_slope);
-                            v.z = lrelu_bf16x2(v.z, a.in_slope); v.w = lrelu_bf16x2(v.w, a.in_slope);
+                            v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl);
+                            v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
                             p[i] = v;
                         }
                         fence_proxy_async();                  // generic-proxy stores -> visible to the tensor core (async proxy)
@@ -370,7 +408,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
                 const uint8_t* Xb = reinterpret_cast<const uint8_t*>(a.X) + (size_t)b * a.x_bs * 4;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
-                    mbar_wait(bars.a_empty(slot), phase ^ 1);
+                    mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1);
                     uint8_t* dst = A_smem + (size_t)slot * a.a_bytes;
                     const int ch0 = kc * a.KC;
                     int r = tid / cpr, cc = tid % cpr;
@@ -415,7 +453,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
-                    mbar_wait(bars.a_empty(slot), phase ^ 1);
+                    mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1);
                     const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
                     mbar_expect_tx(bar, (uint32_t)a.a_tx);
                     const uint32_t dst = smem_u32(A_smem + (size_t)slot * a.a_bytes);
@@ -433,7 +471,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
                 const int nt = tile % a.n_ntiles;
                 const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
                 for (int st = 0; st < n_stages; ++st) {
-                    mbar_wait(bars.w_empty(slot), phase ^ 1);
+                    mbar_wait_relaxed(bars.w_empty(slot), phase ^ 1);
                     const int nb = min(a.G, a.n_blobs - st * a.G);
                     const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
                     mbar_expect_tx(bars.w_full(slot), bytes);
@@ -442,22 +480,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
                 }
             }
         }
-    } else if (warp == MMA_WARP) {
-        // ===== MMA issuer: one thread; specialised on the number of accumulator sub-tiles =====
-        if (lane == 0) {
+    } else if (warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS) {
+        // ===== MMA issuers: one thread per warp; specialised on the number of accumulator sub-tiles =====
+        const int w = warp - MMA_WARP;
+        if (lane == 0 && w < n_issuers) {
             const uint32_t as = smem_u32(A_smem), ws = smem_u32(W_smem);
             if (a.split) {
                 switch (a.msub) {
-                    case 1: mma_role<NT, 1, true>(a, bars, as, ws, tmem_base); break;
-                    case 2: mma_role<NT, 2, true>(a, bars, as, ws, tmem_base); break;
+                    case 1: mma_role<NT, 1, 1, true>(a, bars, as, ws, tmem_base, w); break;
+                    case 2: mma_role<NT, 2, 2, true>(a, bars, as, ws, tmem_base, w); break;
                     default: break;
                 }
             } else {
                 switch (a.msub) {
-                    case 1: mma_role<NT, 1, false>(a, bars, as, ws, tmem_base); break;
-                    case 2: if (NT <= 128) mma_role<NT, 2, false>(a, bars, as, ws, tmem_base); break;
-                    case 4: if (NT <= 64) mma_role<NT, 4, false>(a, bars, as, ws, tmem_base); break;
-                    case 8: if (NT <= 32) mma_role<NT, 8, false>(a, bars, as, ws, tmem_base); break;
+                    case 1: mma_role<NT, 1, 1, false>(a, bars, as, ws, tmem_base, w); break;
+                    case 2: if (NT <= 128) mma_role<NT, 2, 2, false>(a, bars, as, ws, tmem_base, w); break;
+                    case 4: if (NT <= 64) mma_role<NT, 4, 4, false>(a, bars, as, ws, tmem_base, w); break;
+                    case 8: if (NT <= 32) mma_role<NT, 8, 4, false>(a, bars, as, ws, tmem_base, w); break;
                     default: break;
                 }
             }
@@ -475,44 +514,87 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
             const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
             const int n0 = nt * NT, q0 = rt * a.msub * 128;
             const int accb = it & 1;
-            mbar_wait(bars.acc_full(accb), (it >> 1) & 1);
+            mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1);
             tc_fence_after();
             const long boff = (long)b * a.y_bs;
             if (a.dbg & 4) {
                 // what-if: no epilogue work
             } else if (a.y_planar) {
-                // ---- planar bf16 output [Cout/8][y_T][8]: lane = row, one 16-byte store per 8 columns; the residuals of
-                //      the next 16-column unit are fetched before the current one is read from TMEM ----
+                // ---- planar bf16 output [Cout/8][y_T][8]: lane = row, one 16-byte store per 8 columns.  Columns outer (bias
+                //      and column offsets live in registers), sub-tiles inner with the next sub-tile's residuals in flight ----
                 const int ncg = (c_end - c_begin) >> 4;
-                const int units = a.msub * ncg;
-                long o0 = -1, o1 = -1;
-                uint4 r1a = make_uint4(0u, 0u, 0u, 0u), r1b = r1a, r2a = r1a, r2b = r1a;
-                auto fetch = [&](int ms, int cgi, long& p0, long& p1, uint4& x1a, uint4& x1b, uint4& x2a, uint4& x2b) {
-                    const int q = q0 + ms * 128 + quad * 32 + lane, n = n0 + c_begin + cgi * 16;
-                    p0 = planar_off(a, q, n); p1 = planar_off(a, q, n + 8);
-                    x1a = x1b = x2a = x2b = make_uint4(0u, 0u, 0u, 0u);
-                    if (a.R1) { if (p0 >= 0) x1a = *reinterpret_cast<const uint4*>(R1h + boff + p0); if (p1 >= 0) x1b = *reinterpret_cast<const uint4*>(R1h + boff + p1); }
-                    if (a.R2) { if (p0 >= 0) x2a = *reinterpret_cast<const uint4*>(R2h + boff + p0); if (p1 >= 0) x2b = *reinterpret_cast<const uint4*>(R2h + boff + p1); }
-                };
-                if (units > 0) fetch(0, 0, o0, o1, r1a, r1b, r2a, r2b);
-                int ms = 0, cgi = 0;
-                for (int u = 0; u < units; ++u) {
-                    int ms_n = ms, cgi_n = cgi + 1;
-                    if (cgi_n == ncg) { cgi_n = 0; ++ms_n; }
-                    long p0 = -1, p1 = -1; uint4 x1a, x1b, x2a, x2b;
-                    x1a = x1b = x2a = x2b = make_uint4(0u, 0u, 0u, 0u);
-                    if (u + 1 < units) fetch(ms_n, cgi_n, p0, p1, x1a, x1b, x2a, x2b);
-                    float v[16];
-                    const int cc = c_begin + cgi * 16;
-                    tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + ms * NT + cc), v);
-                    epi_bias_act(a, v, bias_s + n0 + cc);
-                    if (a.R1) { add_bf16x8(v, r1a); add_bf16x8(v + 8, r1b); }
-                    if (a.R2) { add_bf16x8(v, r2a); add_bf16x8(v + 8, r2b); }
-                    epi_scale_post(a, v);
-                    if (o0 >= 0) *reinterpret_cast<uint4*>(a.Y16 + boff + o0) = pack8(v);
-                    if (o1 >= 0) *reinterpret_cast<uint4*>(a.Y16 + boff + o1) = pack8(v + 8);
-                    o0 = p0; o1 = p1; r1a = x1a; r1b = x1b; r2a = x2a; r2b = x2b;
-                    ms = ms_n; cgi = cgi_n;
+                const int q_lane = q0 + quad * 32 + lane;
+                const long gstride = (long)a.y_T * 8;                       // elements between 8-channel groups
+                const int t_step = 128 * a.up;
+                const bool has_r1 = a.R1 != nullptr, has_r2 = a.R2 != nullptr;
+                const Slope2 sl_out = make_slope2(a.out_slope), sl_post = make_slope2(a.post_slope);
+                for (int cgi = 0; cgi < ncg; ++cgi) {
+                    const int cc = c_begin + cgi * 16, n = n0 + cc;
+                    const int co = n & ((1 << a.cout_shift) - 1), r = n >> a.cout_shift;
+                    const int t0 = q_lane * a.up + r - a.up_pad;
+                    const long cbase = boff + (long)(co >> 3) * gstride;
+                    float bb[16];
+                    {
+                        const float4* b4 = reinterpret_cast<const float4*>(bias_s + n);
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) { const float4 t = b4[h]; bb[h * 4] = t.x; bb[h * 4 + 1] = t.y; bb[h * 4 + 2] = t.z; bb[h * 4 + 3] = t.w; }
+                    }
+                    const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + cc);
+                    uint4 r1a = make_uint4(0u, 0u, 0u, 0u), r1b = r1a, r2a = r1a, r2b = r1a;
+                    bool ok = q_lane < a.Q && (unsigned)t0 < (unsigned)a.y_T;
+                    long off = cbase + (long)t0 * 8;
+                    if (ok) {
+                        if (has_r1) { r1a = *reinterpret_cast<const uint4*>(R1h + off); r1b = *reinterpret_cast<const uint4*>(R1h + off + gstride); }
+                        if (has_r2) { r2a = *reinterpret_cast<const uint4*>(R2h + off); r2b = *reinterpret_cast<const uint4*>(R2h + off + gstride); }
+                    }
+                    for (int ms = 0; ms < a.msub; ++ms) {
+                        // residuals of the next sub-tile
+                        const int tn = t0 + (ms + 1) * t_step;
+                        const bool okn = ms + 1 < a.msub && q_lane + (ms + 1) * 128 < a.Q && (unsigned)tn < (unsigned)a.y_T;
+                        const long offn = cbase + (long)tn * 8;
+                        uint4 x1a = make_uint4(0u, 0u, 0u, 0u), x1b = x1a, x2a = x1a, x2b = x1a;
+                        if (okn) {
+                            if (has_r1) { x1a = *reinterpret_cast<const uint4*>(R1h + offn); x1b = *reinterpret_cast<const uint4*>(R1h + offn + gstride); }
+                            if (has_r2) { x2a = *reinterpret_cast<const uint4*>(R2h + offn); x2b = *reinterpret_cast<const uint4*>(R2h + offn + gstride); }
+                        }
+                        float v[16];
+                        tmem_ld16(tcol + (uint32_t)(ms * NT), v);
+#pragma unroll
+                        for (int i = 0; i < 16; i += 2) add_f32x2(v[i], v[i + 1], bb[i], bb[i + 1]);
+                        if (a.out_act != ACT_NONE && a.out_act != ACT_LRELU) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i], a.out_act, a.out_slope);
+                        }
+                        uint4 pa, pb;
+                        if (has_r1 || has_r2 || a.out_scale != 1.f) {
+                            if (a.out_act == ACT_LRELU) {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * a.out_slope);
+                            }
+                            if (has_r1) { add_bf16x8(v, r1a); add_bf16x8(v + 8, r1b); }
+                            if (has_r2) { add_bf16x8(v, r2a); add_bf16x8(v + 8, r2b); }
+                            if (a.out_scale != 1.f) {
+#pragma unroll
+                                for (int i = 0; i < 16; i += 2) mul_f32x2(v[i], v[i + 1], a.out_scale, a.out_scale);
+                            }
+                            pa = pack8(v); pb = pack8(v + 8);
+                        } else {
+                            pa = pack8(v); pb = pack8(v + 8);
+                            if (a.out_act == ACT_LRELU) {                  // on the packed values: 3 instructions per pair
+                                pa.x = lrelu_bf16x2(pa.x, sl_out); pa.y = lrelu_bf16x2(pa.y, sl_out); pa.z = lrelu_bf16x2(pa.z, sl_out); pa.w = lrelu_bf16x2(pa.w, sl_out);
+                                pb.x = lrelu_bf16x2(pb.x, sl_out); pb.y = lrelu_bf16x2(pb.y, sl_out); pb.z = lrelu_bf16x2(pb.z, sl_out); pb.w = lrelu_bf16x2(pb.w, sl_out);
+                            }
+                        }
+                        if (a.post_slope != 1.f) {
+                            pa.x = lrelu_bf16x2(pa.x, sl_post); pa.y = lrelu_bf16x2(pa.y, sl_post); pa.z = lrelu_bf16x2(pa.z, sl_post); pa.w = lrelu_bf16x2(pa.w, sl_post);
+                            pb.x = lrelu_bf16x2(pb.x, sl_post); pb.y = lrelu_bf16x2(pb.y, sl_post); pb.z = lrelu_bf16x2(pb.z, sl_post); pb.w = lrelu_bf16x2(pb.w, sl_post);
+                        }
+                        if (ok) {
+                            *reinterpret_cast<uint4*>(a.Y16 + off) = pa;
+                            *reinterpret_cast<uint4*>(a.Y16 + off + gstride) = pb;
+                        }
+                        ok = okn; off = offn; r1a = x1a; r1b = x1b; r2a = x2a; r2b = x2b;
+                    }
                 }
             } else {
                 // ---- row-major output (fp32 and/or bf16): lane = row, 16 consecutive columns per store group ----
@@ -667,11 +749,10 @@ void launch_from_planar(masg_ctx* c, cudaStream_t s, const bf16* x, float* out, 
 void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
     MASG_CHECK(d.w32 != nullptr, "tc_prepare_weights: fp32 GEMM weights missing");
     int NT = 0;
-    const int cands[5] = {256, 128, 80, 64, 32};
-    for (int i = 0; i < 5 && !NT; ++i) if (d.N % cands[i] == 0) NT = cands[i];
-    MASG_CHECK(NT != 0, "conv_tc: N=%d is not a multiple of 32/64/80/128/256 (unsupported configuration)", d.N);
+    const int cands[4] = {128, 80, 64, 32};
+    for (int i = 0; i < 4 && !NT; ++i) if (d.N % cands[i] == 0) NT = cands[i];
+    MASG_CHECK(NT != 0, "conv_tc: N=%d is not a multiple of 32/64/80/128 (unsupported configuration)", d.N);
     int KW = (d.Cin % 64 == 0) ? 64 : (d.Cin % 32 == 0 ? 32 : 16);
-    if (NT == 256 && KW == 64) KW = 32;                     // keep one blob <= 16 KB
     while (split && NT * KW * 4 > W_STAGE_BYTES && KW > 16) KW /= 2;
     MASG_CHECK(d.Cin % KW == 0, "conv_tc: Cin=%d must be a multiple of 16", d.Cin);
     size_t n = (size_t)d.taps * d.Cin * d.N;
@@ -804,7 +885,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
 #define MASG_TC_CASE(NTV)                                                                       \
     case NTV: if (tma_in) launch_inst<NTV, true>(a, tm, grid, smem, s); else launch_inst<NTV, false>(a, tm, grid, smem, s); break;
     switch (NT) {
-        MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128) MASG_TC_CASE(256)
+        MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128)
         default: MASG_CHECK(false, "conv_tc: unsupported N tile %d", NT);
     }
 #undef MASG_TC_CASE
