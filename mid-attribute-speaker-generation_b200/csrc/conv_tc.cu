@@ -34,7 +34,6 @@
 //     row-major rows or planar bf16 (lane = time row, so each store instruction writes 512 contiguous bytes).
 #include "common.cuh"
 #include "tc.cuh"
-#include <cuda.h>
 
 namespace {
 
@@ -105,11 +104,6 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-// 4-D TMA tile copy global -> shared (coordinates innermost first); out-of-range elements are zero-filled
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
-    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
-                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -335,7 +329,7 @@ __device__ __forceinline__ long planar_off(const TcArgs& a, int q, int n) {
 }
 
 template <int NT, bool TMA_IN>
-__global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const __grid_constant__ CUtensorMap tmap) {
+__global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     // header: mbarriers + TMEM base; then the bias row, the activation slots and the weight ring
     const Bars bars{smem_u32(smem)};
@@ -358,7 +352,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
         for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), n_issuers); mbar_init(bars.acc_empty(i), EPI_WARPS); }
         for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), n_issuers); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if (TMA_IN) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap)) : "memory");
     }
     for (int i = threadIdx.x; i < a.N; i += NTHREADS) bias_s[i] = a.bias ? a.bias[i % a.bias_mod] : 0.f;
     if (warp == MMA_WARP) {
@@ -445,20 +438,55 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a, const _
             }
         }
     } else if (warp == T_WARP) {
-        // ===== TMA issuer (planar input): one (128 + halo)-row block per accumulator sub-tile and channel chunk =====
-        if (TMA_IN && lane == 0 && !(a.dbg & 2)) {
+        // ===== activation copy warp (planar input).  In the planar layout the rows [t, t + Rb) of one 8-channel group are
+        // one contiguous run of Rb*16 bytes, so every (sub-tile, channel group) block is a single 1-D bulk async copy
+        // (cp.async.bulk -> UBLKCP), one per lane.  (A 4-D tensor-map copy of the same box has a 16-byte innermost
+        // dimension and was measured at ~16 B/clk/SM, 3.9 TB/s chip-wide.)  Rows outside [0, Tin) — the conv zero padding,
+        // only in the first / last tile of an utterance — are zero-filled by the lane before the copies are issued. =====
+        if (TMA_IN && !(a.dbg & 2)) {
             int slot = 0; uint32_t phase = 0;
-            const int cg_per_chunk = a.KC >> 3;
+            const int cgpc = a.KC >> 3;
+            const int n_copies = a.msub * cgpc;
+            const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
             for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
-                    mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1);
+                    if (lane == 0) mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1);
+                    __syncwarp();
                     const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
-                    mbar_expect_tx(bar, (uint32_t)a.a_tx);
-                    const uint32_t dst = smem_u32(A_smem + (size_t)slot * a.a_bytes);
-                    for (int ms = 0; ms < a.msub; ++ms)
-                        tma_load_4d(dst + (uint32_t)(ms * a.a_blk_bytes), &tmap, 0, q_lo + ms * 128, kc * cg_per_chunk, b, bar);
+                    uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
+                    const uint32_t dst = smem_u32(dst_g);
+                    // valid row range of every sub-tile block and the bytes the barrier has to expect
+                    uint32_t tx = 0; bool edge = false;
+                    for (int ms = 0; ms < a.msub; ++ms) {
+                        const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = min(t0 + a.Rp, a.Tin);
+                        if (hi > lo) tx += (uint32_t)(hi - lo) * 16u * (uint32_t)cgpc;
+                        edge |= (lo > t0) || (hi < t0 + a.Rp);
+                    }
+                    if (edge) {
+                        for (int idx = lane; idx < n_copies; idx += 32) {
+                            const int ms = idx / cgpc, g = idx - ms * cgpc;
+                            const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = max(min(t0 + a.Rp, a.Tin), lo);
+                            uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)ms * a.a_blk_bytes + (size_t)g * a.Rp * 16);
+                            for (int r = 0; r < min(lo - t0, a.Rp); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                            for (int r = max(hi - t0, 0); r < a.Rp; ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                        }
+                        fence_proxy_async();
+                        __syncwarp();
+                    }
+                    if (lane == 0) {
+                        if (tx) mbar_expect_tx(bar, tx); else mbar_arrive(bar);
+                    }
+                    __syncwarp();
+                    for (int idx = lane; idx < n_copies; idx += 32) {
+                        const int ms = idx / cgpc, g = idx - ms * cgpc;
+                        const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = min(t0 + a.Rp, a.Tin);
+                        if (hi > lo) {
+                            const uint8_t* src = X8 + (((size_t)b * (a.Cin >> 3) + (size_t)(kc * cgpc + g)) * a.Tin + lo) * 16;
+                            bulk_g2s(dst + (uint32_t)(ms * a.a_blk_bytes) + (uint32_t)((g * a.Rp + (lo - t0)) * 16), src, (uint32_t)(hi - lo) * 16u, bar);
+                        }
+                    }
                     if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
                 }
             }
@@ -711,25 +739,10 @@ __global__ void k_from_planar(const bf16* __restrict__ x, float* __restrict__ ou
 }
 
 template <int NT, bool TMA_IN>
-void launch_inst(const TcArgs& a, const CUtensorMap& tm, dim3 grid, size_t smem, cudaStream_t s) {
+void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
-    k_conv_tc<NT, TMA_IN><<<grid, NTHREADS, smem, s>>>(a, tm);
-}
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn encode_tiled_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
-        MASG_CHECK(p != nullptr && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
-        fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    return fn;
+    k_conv_tc<NT, TMA_IN><<<grid, NTHREADS, smem, s>>>(a);
 }
 
 }  // namespace
@@ -866,24 +879,12 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     MASG_CHECK(a.in_act == ACT_NONE || a.in_act == ACT_LRELU || !tma_in, "conv_tc: planar input supports leaky-relu only");
     const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
-    CUtensorMap tm;
-    memset(&tm, 0, sizeof(tm));
-    if (tma_in) {
-        const cuuint64_t dims[4] = {8, (cuuint64_t)io.Tin, (cuuint64_t)(d.Cin / 8), (cuuint64_t)io.B};
-        const cuuint64_t strides[3] = {16, (cuuint64_t)io.Tin * 16, (cuuint64_t)io.Tin * d.Cin * 2};
-        const cuuint32_t box[4] = {8, (cuuint32_t)a.Rp, (cuuint32_t)(KC / 8), 1};
-        const cuuint32_t estr[4] = {1, 1, 1, 1};
-        MASG_CHECK(((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
-        CUresult r = encode_tiled_fn()(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(io.X), dims, strides, box, estr,
-                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        MASG_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) for T=%d C=%d B=%d box rows %d", (int)r, io.Tin, d.Cin, io.B, a.Rp);
-    }
+    MASG_CHECK(!tma_in || ((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
     static int n_sm = 0;
     if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
     dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
 #define MASG_TC_CASE(NTV)                                                                       \
-    case NTV: if (tma_in) launch_inst<NTV, true>(a, tm, grid, smem, s); else launch_inst<NTV, false>(a, tm, grid, smem, s); break;
+    case NTV: if (tma_in) launch_inst<NTV, true>(a, grid, smem, s); else launch_inst<NTV, false>(a, grid, smem, s); break;
     switch (NT) {
         MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128)
         default: MASG_CHECK(false, "conv_tc: unsupported N tile %d", NT);
