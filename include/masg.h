@@ -90,6 +90,13 @@ int masg_length_regulate(masg_ctx* ctx, void* stream, const float* x, const floa
 int masg_bucketize_embed_add(masg_ctx* ctx, void* stream, const float* v, const float* bins, int n_bins_m1,
                              const float* table, int64_t rows, int C, float* x, int64_t* idx_out /*nullable*/);
 
+/* MultiHeadAttention core (transformer/SubLayers.py:43-52 + transformer/Modules.py:14-25) alone, for parity tests:
+ * qkv fp32 [B, S, 768] = q | k | v (2 heads x 128 each, as the concatenated projection writes them), lens int64 [B]
+ * (keys >= lens[b] are masked with -inf before the softmax; query rows >= lens[b] are written as zeros — the
+ * reference computes and then zeroes them, Layers.py:25) -> out fp32 [B, S, 256] (heads concatenated).
+ * MASG_PREC_BF16: tcgen05 kernel (bf16 hi+lo operands, scores and output in TMEM); MASG_PREC_FP32: fp32 SIMT kernel. */
+int masg_attention(masg_ctx* ctx, void* stream, const float* qkv, const int64_t* lens, int B, int S, float* out);
+
 /* hifigan.Generator.forward (hifigan/models.py:149-165): mel fp32 [B, 80, T] → wav fp32 [B, 1, 256 T].
  * wav_i16 (nullable): int16 [B, 256 T] = C-cast of wav*32768 as utils/model.py:82-85 (wrap, not saturate).
  * mel_is_channels_last != 0: mel is [B, T, 80] (postnet output layout; skips the transpose that

@@ -344,6 +344,14 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     API_END(c)
 }
 
+int masg_attention(masg_ctx* c, void* stream, const float* qkv, const int64_t* lens, int B, int S, float* out) {
+    API_BEGIN(c)
+    MASG_CHECK(qkv && lens && out && B > 0 && S > 0, "bad argument");
+    if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, (cudaStream_t)stream, qkv, lens, B, S, out);
+    else launch_attention_f32(c, (cudaStream_t)stream, qkv, lens, B, S, out);
+    API_END(c)
+}
+
 int masg_profile(masg_ctx* c, int enable) {
     API_BEGIN(c)
     c->profiling = enable != 0;

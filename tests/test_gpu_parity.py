@@ -405,3 +405,30 @@ def test_conv_kernel_matches_torch(precision, case):
     err = (y.cpu() - ref).abs().max().item()
     print("conv %s %s: max-abs err %.3e, %.3f ms" % (precision, case, err, ms.value))
     assert err <= {"fp32": 2e-4, "bf16-split": 2e-4, "bf16": 4e-2, "bf16-act": 8e-2}[precision]
+
+
+# ------------------------------------------------------------------------------------------------
+# masked multi-head attention alone (tcgen05 kernel in bf16 mode) against the reference formula in torch fp64
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("B,S,lens", [(3, 200, [200, 77, 1]), (2, 600, [600, 389]), (2, 1300, [1300, 1025]), (2, 130, [129, 0])])
+def test_attention_matches_reference_formula(precision, B, S, lens):
+    """transformer/SubLayers.py:43-52 + Modules.py:14-25: softmax(q k^T / sqrt(128), -inf at pad keys) v per head; pad
+    query rows compared as zeros (the reference zeroes them after the LayerNorm, Layers.py:25)."""
+    from masg_b200 import _lib
+    cx = _lib.default_context(DEV, precision)
+    g = torch.Generator().manual_seed(S + B)
+    qkv = torch.randn(B, S, 768, generator=g) * 1.5
+    lens_t = torch.tensor(lens, dtype=torch.int64)
+    q, k, v = [t.double().view(B, S, 2, 128).permute(0, 2, 1, 3) for t in qkv.split(256, dim=2)]
+    att = q @ k.transpose(2, 3) / np.power(128, 0.5)
+    key_pad = torch.arange(S)[None, :] >= lens_t[:, None]
+    att = att.masked_fill(key_pad[:, None, None, :], float("-inf"))
+    ref = (torch.softmax(att, dim=3) @ v).permute(0, 2, 1, 3).reshape(B, S, 256)
+    ref = torch.nan_to_num(ref).masked_fill(key_pad[:, :, None], 0.0).float()
+    qg, lg = qkv.to(DEV), lens_t.to(DEV)
+    out = torch.full((B, S, 256), 7.0, device=DEV)
+    cx.check(cx.lib.masg_attention(cx.h, cx.stream(), P(qg), P(lg), B, S, P(out)), "attention")
+    err = (out.cpu() - ref).abs().max().item()
+    print("attention %s B=%d S=%d: max-abs err %.3e" % (precision, B, S, err))
+    assert err <= 2e-4
