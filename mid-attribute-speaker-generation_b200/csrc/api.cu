@@ -338,6 +338,12 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     CUDA_OK(cudaStreamSynchronize(s));
     float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
     if (ms_out) *ms_out = ms / reps;
+    if (getenv("MASG_TC_DEBUG") && (atoi(getenv("MASG_TC_DEBUG")) & 16)) {
+        unsigned long long st[16]; tc_debug_stats(st, true);
+        const double n = 148.0 * (reps + 1);
+        fprintf(stderr, "  [tc stats, kcycles per CTA per launch] issuer: wait acc_empty %.0f a_full %.0f w_full %.0f of total %.0f | epilogue: wait acc_full %.0f of %.0f | copy warp wait a_empty %.0f | weight warp wait w_empty %.0f | worker wait a_raw %.0f\n",
+                st[0] / n / 1e3, st[1] / n / 1e3, st[2] / n / 1e3, st[3] / n / 1e3, st[4] / n / 1e3, st[5] / n / 1e3, st[6] / n / 1e3, st[7] / n / 1e3, st[8] / n / 1e3);
+    }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (act_bf16) { launch_from_planar(c, s, y16, y, B, (int)So, Cout); CUDA_OK(cudaStreamSynchronize(s)); }
     while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }

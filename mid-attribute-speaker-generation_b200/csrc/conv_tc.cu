@@ -105,6 +105,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// one lane of the (converged) warp; the same lane every time, so MMAs and their commits come from one thread
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -200,6 +206,10 @@ __device__ __forceinline__ uint4 convert_piece(const TcArgs& a, const uint4 r0, 
     return o;
 }
 
+// MASG_TC_DEBUG & 16: cycles spent waiting, per role (issuer 0, epilogue warp 0, copy warp, weight warp), summed over CTAs
+__device__ unsigned long long g_tc_stats[16];
+#define STAT_WAIT(flag, idx, stmt) do { if (flag) { const long long _t = clock64(); stmt; atomicAdd(&g_tc_stats[idx], (unsigned long long)(clock64() - _t)); } else { stmt; } } while (0)
+
 struct Bars {                                            // mbarrier addresses (shared window), 8 bytes each
     uint32_t base;
     __device__ uint32_t a_full(int i) const { return base + 8u * i; }
@@ -218,8 +228,9 @@ struct Bars {                                            // mbarrier addresses (
 // the same barrier sequence as the others; every release barrier therefore expects NI commits.  (Measured: one
 // thread sustains ~56 cycles per MMA, the tensor core needs 40 at N=32 and 48 at N=64 — shared-memory operand reads,
 // (4096 + 32 N) bytes at 128 B/clk — so two to four issuers are needed to keep it busy.)
-template <int NT, int MS, int NI, bool SPLIT>
-__device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base, const int w) {
+template <int NT, int MS, int NI, bool SPLIT, int W>
+__device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base) {
+    constexpr int w = W;                                   // issuer index: compile-time, so every value below is warp-uniform
     constexpr int MSL = MS / NI;
     // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -231,11 +242,13 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
     const uint32_t blob16 = (uint32_t)a.blob_bytes >> 4, a_half16 = (uint32_t)a.a_half >> 4, w_half16 = blob16 >> 1;
     const int n_chunks = a.Cin / a.KC, subs = a.KC / a.KW, ksteps = a.KW >> 4;
     const bool no_w = a.dbg & 1, no_a = a.dbg & 2, no_mma = a.dbg & 8;
+    const bool st = (a.dbg & 16) && w == 0 && (threadIdx.x & 31) == 0;
+    const long long t_begin = st ? clock64() : 0;
     int wslot = 0, aslot = 0, it = 0;
     uint32_t wphase = 0, aphase = 0;
     for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
         const int accb = it & 1;
-        mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1);             // epilogue has drained this accumulator set
+        STAT_WAIT(st, 0, mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1));   // epilogue has drained this accumulator set
         tc_fence_after();
         const uint32_t tacc_w = tmem_base + (uint32_t)(accb * MS * NT + w * NT);
         uint32_t accum = 0;
@@ -243,44 +256,48 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
         bool have_stage = false;
         uint32_t wbase16 = 0;
         for (int kc = 0; kc < n_chunks; ++kc) {
-            if (!no_a) { mbar_wait(bars.a_full(aslot), aphase); tc_fence_after(); }
+            if (!no_a) { STAT_WAIT(st, 1, mbar_wait(bars.a_full(aslot), aphase)); tc_fence_after(); }
             const uint32_t abase16 = (a_smem + (uint32_t)aslot * (uint32_t)a.a_bytes) >> 4;
             for (int sub = 0; sub < subs; ++sub) {
                 uint32_t a_tap = abase16 + (uint32_t)sub * a_sub + (uint32_t)(a.off0 - a.off_lo);
                 for (int j = 0; j < a.taps; ++j, a_tap += (uint32_t)a.tstep) {
                     if (g == a.G) {                                        // next weight stage
                         if (have_stage) {
-                            if (!no_w) tc_commit(bars.w_empty(wslot));
+                            if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));
                             if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
                         }
-                        if (!no_w) { mbar_wait(bars.w_full(wslot), wphase); tc_fence_after(); }
+                        if (!no_w) { STAT_WAIT(st, 2, mbar_wait(bars.w_full(wslot), wphase)); tc_fence_after(); }
                         wbase16 = (w_smem + (uint32_t)wslot * (uint32_t)a.stage_bytes) >> 4;
                         g = 0; have_stage = true;
                     }
                     uint32_t a_lo = (a_fixed | a_tap) + (uint32_t)w * a_ms, w_lo = w_fixed | (wbase16 + (uint32_t)g * blob16);
                     ++g;
                     if (no_mma) continue;
-                    for (int ks = 0; ks < ksteps; ++ks, a_lo += a_ks, w_lo += w_ks) {
+                    if (elect_one()) {
+                        for (int ks = 0; ks < ksteps; ++ks, a_lo += a_ks, w_lo += w_ks) {
 #pragma unroll
-                        for (int i = 0; i < MSL; ++i) {
-                            const uint32_t d = tacc_w + (uint32_t)(i * NI * NT), al = a_lo + (uint32_t)(i * NI) * a_ms;
-                            tc_mma(d, al, w_lo, desc_hi, idesc, accum);
-                            if (SPLIT) {
-                                tc_mma(d, al + a_half16, w_lo, desc_hi, idesc, 1u);
-                                tc_mma(d, al, w_lo + w_half16, desc_hi, idesc, 1u);
+                            for (int i = 0; i < MSL; ++i) {
+                                const uint32_t d = tacc_w + (uint32_t)(i * NI * NT), al = a_lo + (uint32_t)(i * NI) * a_ms;
+                                tc_mma(d, al, w_lo, desc_hi, idesc, (ks == 0) ? accum : 1u);
+                                if (SPLIT) {
+                                    tc_mma(d, al + a_half16, w_lo, desc_hi, idesc, 1u);
+                                    tc_mma(d, al, w_lo + w_half16, desc_hi, idesc, 1u);
+                                }
                             }
                         }
-                        accum = 1u;
                     }
+                    __syncwarp();
+                    accum = 1u;
                 }
             }
-            if (!no_a) tc_commit(bars.a_empty(aslot));                     // chunk consumed -> slot may be overwritten
+            if (!no_a && elect_one()) tc_commit(bars.a_empty(aslot));                     // chunk consumed -> slot may be overwritten
             if (++aslot == A_SLOTS) { aslot = 0; aphase ^= 1; }
         }
-        if (!no_w) tc_commit(bars.w_empty(wslot));                         // the weight stream restarts on a stage boundary per tile
+        if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));          // the weight stream restarts on a stage boundary per tile
         if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
-        tc_commit(bars.acc_full(accb));
+        if (elect_one()) tc_commit(bars.acc_full(accb));
     }
+    if (st) atomicAdd(&g_tc_stats[3], (unsigned long long)(clock64() - t_begin));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -376,7 +393,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                 int slot = 0; uint32_t phase = 0;
                 for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                     for (int kc = 0; kc < n_chunks; ++kc) {
-                        mbar_wait_relaxed(bars.a_raw(slot), phase);
+                        STAT_WAIT((a.dbg & 16) && tid == 0, 8, mbar_wait_relaxed(bars.a_raw(slot), phase));
                         uint4* p = reinterpret_cast<uint4*>(A_smem + (size_t)slot * a.a_bytes);
                         for (int i = tid; i < pieces; i += A_THREADS) {
                             uint4 v = p[i];
@@ -452,7 +469,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
-                    if (lane == 0) mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1);
+                    if (lane == 0) STAT_WAIT(a.dbg & 16, 6, mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1));
                     __syncwarp();
                     const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
                     uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
@@ -499,7 +516,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                 const int nt = tile % a.n_ntiles;
                 const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
                 for (int st = 0; st < n_stages; ++st) {
-                    mbar_wait_relaxed(bars.w_empty(slot), phase ^ 1);
+                    STAT_WAIT(a.dbg & 16, 7, mbar_wait_relaxed(bars.w_empty(slot), phase ^ 1));
                     const int nb = min(a.G, a.n_blobs - st * a.G);
                     const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
                     mbar_expect_tx(bars.w_full(slot), bytes);
@@ -511,23 +528,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     } else if (warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS) {
         // ===== MMA issuers: one thread per warp; specialised on the number of accumulator sub-tiles =====
         const int w = warp - MMA_WARP;
-        if (lane == 0 && w < n_issuers) {
+        if (w < n_issuers) {
             const uint32_t as = smem_u32(A_smem), ws = smem_u32(W_smem);
+#define MASG_ROLE(MSV, NIV, SPL, WV) mma_role<NT, MSV, NIV, SPL, WV>(a, bars, as, ws, tmem_base)
             if (a.split) {
-                switch (a.msub) {
-                    case 1: mma_role<NT, 1, 1, true>(a, bars, as, ws, tmem_base, w); break;
-                    case 2: mma_role<NT, 2, 2, true>(a, bars, as, ws, tmem_base, w); break;
-                    default: break;
-                }
-            } else {
-                switch (a.msub) {
-                    case 1: mma_role<NT, 1, 1, false>(a, bars, as, ws, tmem_base, w); break;
-                    case 2: if (NT <= 128) mma_role<NT, 2, 2, false>(a, bars, as, ws, tmem_base, w); break;
-                    case 4: if (NT <= 64) mma_role<NT, 4, 4, false>(a, bars, as, ws, tmem_base, w); break;
-                    case 8: if (NT <= 32) mma_role<NT, 8, 4, false>(a, bars, as, ws, tmem_base, w); break;
-                    default: break;
-                }
+                if (a.msub == 1) MASG_ROLE(1, 1, true, 0);
+                else if (a.msub == 2 && NT <= 128) { if (w == 0) MASG_ROLE(2, 2, true, 0); else MASG_ROLE(2, 2, true, 1); }
+            } else if (a.msub == 1) {
+                MASG_ROLE(1, 1, false, 0);
+            } else if (a.msub == 2 && NT <= 128) {
+                if (w == 0) MASG_ROLE(2, 2, false, 0); else MASG_ROLE(2, 2, false, 1);
+            } else if (a.msub == 4 && NT <= 64) {
+                switch (w) { case 0: MASG_ROLE(4, 4, false, 0); break; case 1: MASG_ROLE(4, 4, false, 1); break;
+                             case 2: MASG_ROLE(4, 4, false, 2); break; default: MASG_ROLE(4, 4, false, 3); break; }
+            } else if (a.msub == 8 && NT <= 32) {
+                switch (w) { case 0: MASG_ROLE(8, 4, false, 0); break; case 1: MASG_ROLE(8, 4, false, 1); break;
+                             case 2: MASG_ROLE(8, 4, false, 2); break; default: MASG_ROLE(8, 4, false, 3); break; }
             }
+#undef MASG_ROLE
         }
         __syncwarp();
     } else {
@@ -538,11 +556,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         const float* R1f = reinterpret_cast<const float*>(a.R1); const bf16* R1h = reinterpret_cast<const bf16*>(a.R1);
         const float* R2f = reinterpret_cast<const float*>(a.R2); const bf16* R2h = reinterpret_cast<const bf16*>(a.R2);
         int it = 0;
+        const long long t_epi0 = clock64();
         for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
             const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
             const int n0 = nt * NT, q0 = rt * a.msub * 128;
             const int accb = it & 1;
-            mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1);
+            STAT_WAIT((a.dbg & 16) && threadIdx.x == 0, 4, mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1));
             tc_fence_after();
             const long boff = (long)b * a.y_bs;
             if (a.dbg & 4) {
@@ -689,6 +708,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             __syncwarp();
             if (lane == 0) mbar_arrive(bars.acc_empty(accb));
         }
+        if ((a.dbg & 16) && threadIdx.x == 0) atomicAdd(&g_tc_stats[5], (unsigned long long)(clock64() - t_epi0));
     }
     tc_fence_before();
     __syncthreads();
@@ -746,6 +766,11 @@ void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
 }
 
 }  // namespace
+
+void tc_debug_stats(unsigned long long* out16, bool reset) {
+    CUDA_OK(cudaMemcpyFromSymbol(out16, g_tc_stats, sizeof(unsigned long long) * 16));
+    if (reset) { unsigned long long z[16] = {0}; CUDA_OK(cudaMemcpyToSymbol(g_tc_stats, z, sizeof(z))); }
+}
 
 void launch_to_planar(masg_ctx* c, cudaStream_t s, const float* x, bf16* out, int B, int T, int C) {
     MASG_CHECK(C % 8 == 0, "planar layout needs C %% 8 == 0 (C=%d)", C);

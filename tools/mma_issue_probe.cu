@@ -30,7 +30,7 @@ __device__ __forceinline__ void wait(uint32_t bar, uint32_t parity) {
 }
 
 template <int N>
-__global__ void __launch_bounds__(256, 1) k_issue(int mode, int iters, int nwarps, long long* out) {
+__global__ void __launch_bounds__(256, 1) k_issue(int mode, int iters, int nwarps, long long* out, int a_shift16, int b_shift16) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar[8];
     __shared__ uint32_t tslot;
@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(256, 1) k_issue(int mode, int iters, int nwarp
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t hi = (128u >> 4) | (1u << 14);
     const uint32_t a_fixed = 1040u << 16, b_fixed = (uint32_t)N << 16;
-    const uint32_t a0 = a_fixed | (smem_u32(smem) >> 4), b0 = b_fixed | ((smem_u32(smem) + 140 * 1024) >> 4);
+    const uint32_t a0 = a_fixed | ((smem_u32(smem) >> 4) + a_shift16), b0 = b_fixed | (((smem_u32(smem) + 140 * 1024) >> 4) + b_shift16);
     constexpr int MS = 512 / N > 8 ? 8 : 512 / N;
     long long t0 = 0, t1 = 0;
     if (mode == 0 || mode == 3) {
@@ -125,11 +125,11 @@ __global__ void __launch_bounds__(256, 1) k_issue(int mode, int iters, int nwarp
 }
 
 template <int N>
-static void run(const char* name, int mode, int nwarps) {
+static void run(const char* name, int mode, int nwarps, int a_shift16 = 0, int b_shift16 = 0) {
     long long* d; cudaMalloc(&d, 128); cudaMemset(d, 0, 128);
     cudaFuncSetAttribute(k_issue<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     const int iters = 2048;
-    for (int r = 0; r < 2; ++r) k_issue<N><<<1, 256, 160 * 1024>>>(mode, iters, nwarps, d);
+    for (int r = 0; r < 2; ++r) k_issue<N><<<1, 256, 160 * 1024>>>(mode, iters, nwarps, d, a_shift16, b_shift16);
     long long h[16]; cudaMemcpy(h, d, 128, cudaMemcpyDeviceToHost);
     cudaError_t e = cudaDeviceSynchronize();
     long long mx = 0; for (int w = 0; w < (mode == 3 ? nwarps : 1); ++w) mx = h[w * 2] > mx ? h[w * 2] : mx;
@@ -144,5 +144,10 @@ template <int N> static void all() {
     run<N>("C converged warp, elect per 8 MMAs", 2, 1);
     run<N>("D 2 warps x one thread, disjoint accumulators", 3, 2);
     run<N>("D 4 warps x one thread, disjoint accumulators", 3, 4);
+    run<N>("D 4 warps, A start shifted 1 row (16 B)", 3, 4, 1, 0);
+    run<N>("D 4 warps, A start shifted 3 rows", 3, 4, 3, 0);
+    run<N>("D 4 warps, A start shifted 4 rows", 3, 4, 4, 0);
+    run<N>("D 4 warps, B start shifted 3 rows", 3, 4, 0, 3);
+    run<N>("D 4 warps, A and B shifted 3 rows", 3, 4, 3, 3);
 }
 int main() { all<32>(); all<64>(); all<128>(); all<256>(); return 0; }
