@@ -46,6 +46,20 @@ def _peaks():
     return {"tflops": 1400.0, "hbm": 6650.0, "src": "fallback (B200_PROFILING.md)"}
 
 
+def _ncu_traffic():
+    """DRAM bytes (read + written) per k_conv_tc launch, from the newest committed `ncu --set full` capture of one C3 step
+    (profiles/r*_ncu_full_conv_tc_*.csv, written by tools/ncu_summary.py).  A profiler number, reported beside the live ones."""
+    import csv, glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv_tc_*.csv")))
+    if not files:
+        return None, None
+    rows = list(csv.DictReader(open(files[-1])))
+    if not rows:
+        return None, None
+    tot = sum((float(r["dram_rd_MB"]) + float(r["dram_wr_MB"])) * 1e6 for r in rows)
+    return tot / len(rows), "%s: %d launches of one C3 step, %.1f GB in total" % (os.path.basename(files[-1]), len(rows), tot / 1e9)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -336,6 +350,7 @@ def run_ours(args):
     e0.record(); step_device(); e1.record(); torch.cuda.synchronize()
     step_ms_plain = e0.elapsed_time(e1)
     pk = _peaks()
+    traffic, traffic_src = _ncu_traffic()
 
     # ---- p50 per-utterance latency (config 2: batch 1, 50 phonemes, host ids in -> int16 audio on the host) ----
     b1 = syn.make_batch(1, 50, seed=1235, accents_const=4)
@@ -369,7 +384,8 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": "k_conv_tc (tcgen05 implicit-GEMM conv1d/linear/convT)", "achieved": ach, "peak": pk["tflops"],
-                     "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": None, "peak_source": pk["src"],
+                     "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "traffic_source": traffic_src, "peak_source": pk["src"],
                      "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": step_ms_plain,
                      "share_of_step": k_ms / step_ms_plain if step_ms_plain else None,
                      "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per launch"},

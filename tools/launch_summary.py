@@ -10,7 +10,7 @@ def ms(x):
     return v / 1e6 if u == 'ns' else v / 1e3 if u == 'us' else v
 names = [re.sub(r'\(.*', '', x['Kernel Name']).replace('void <unnamed>::', '').replace('<unnamed>::', '').replace('void ', '') for x in rows]
 posts = [i for i, n in enumerate(names) if 'k_conv_post' in n]
-start, end = posts[-2] + 1, posts[-1]
+start, end = (posts[-2] + 1, posts[-1]) if len(posts) > 1 else (0, len(rows) - 1)   # a --profile-range capture holds exactly one step
 agg = collections.OrderedDict(); tot = 0.0
 for i in range(start, end + 1):
     a = agg.setdefault(names[i], [0, 0.0]); a[0] += 1; a[1] += ms(rows[i]); tot += ms(rows[i])
