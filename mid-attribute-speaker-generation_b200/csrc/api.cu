@@ -344,8 +344,58 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         fprintf(stderr, "  [tc stats, kcycles per CTA per launch] issuer: wait acc_empty %.0f a_full %.0f w_full %.0f of total %.0f | epilogue: wait acc_full %.0f of %.0f | copy warp wait a_empty %.0f | weight warp wait w_empty %.0f | worker wait a_raw %.0f\n",
                 st[0] / n / 1e3, st[1] / n / 1e3, st[2] / n / 1e3, st[3] / n / 1e3, st[4] / n / 1e3, st[5] / n / 1e3, st[6] / n / 1e3, st[7] / n / 1e3, st[8] / n / 1e3);
     }
+    if (getenv("MASG_TC_DEBUG") && (atoi(getenv("MASG_TC_DEBUG")) & 32)) {
+        // timeline of CTA 0 (last launch): one line per tile, cycles relative to the first printed event
+        static long long tr[5 * 96 * 4];
+        const int nt = tc_debug_trace(tr, 5 * 96 * 4, true);
+        auto at = [&](int role, int it, int e) { return tr[(role * nt + it) * 4 + e]; };
+        const int i0 = 40, i1 = 56;
+        const long long base = at(0, i0, 0);
+        fprintf(stderr, "  [tc trace, CTA 0, cycles] tile | copy: wait-begin slot-free issued | worker: landed done | issuer: acc-free a-ready committed | epilogue: idle acc-full done\n");
+        for (int it = i0; it < i1; ++it) {
+            fprintf(stderr, "   %3d |", it);
+            const int ne[4] = {3, 2, 3, 3};
+            for (int role = 0; role < 4; ++role) {
+                for (int e = 0; e < ne[role]; ++e) fprintf(stderr, " %7lld", at(role, it, e) ? at(role, it, e) - base : -1LL);
+                fprintf(stderr, " |");
+            }
+            fprintf(stderr, "\n");
+        }
+    }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (act_bf16) { launch_from_planar(c, s, y16, y, B, (int)So, Cout); CUDA_OK(cudaStreamSynchronize(s)); }
+    while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }
+    API_END(c)
+}
+
+int masg_respair(masg_ctx* c, void* stream, const float* x, const float* acc, int B, int T, int C, const float* w1,
+                 const float* b1, const float* w2, const float* b2, int k, int dilation, float out_scale, float post_slope,
+                 int reps, float* y, float* ms_out) {
+    API_BEGIN(c)
+    cudaStream_t s = (cudaStream_t)stream;
+    MASG_CHECK(x && w1 && w2 && b1 && b2 && y && B > 0 && T > 0 && reps >= 1, "bad argument");
+    MASG_CHECK(c->precision == MASG_PREC_BF16, "masg_respair: the fused pair exists in MASG_PREC_BF16 only");
+    const size_t keep = c->owned.size();
+    ConvDesc d1 = make_conv(c, s, w1, b1, C, C, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, false);
+    ConvDesc d2 = make_conv(c, s, w2, b2, C, C, k, (k - 1) / 2, 1, nullptr, nullptr, false);
+    MASG_CHECK(respair_tc_supported(c, d1, d2), "masg_respair: unsupported pair C=%d k=%d dilation=%d", C, k, dilation);
+    const size_t n = (size_t)B * T * C;
+    bf16 *x16 = nullptr, *y16 = nullptr, *a16 = nullptr;
+    CUDA_OK(cudaMalloc(&x16, n * 2)); c->owned.push_back(x16);
+    CUDA_OK(cudaMalloc(&y16, n * 2)); c->owned.push_back(y16);
+    launch_to_planar(c, s, x, x16, B, T, C);
+    if (acc) { CUDA_OK(cudaMalloc(&a16, n * 2)); c->owned.push_back(a16); launch_to_planar(c, s, acc, a16, B, T, C); }
+    launch_respair_tc(c, s, d1, d2, x16, B, T, y16, a16, out_scale, post_slope);
+    cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));
+    CUDA_OK(cudaEventRecord(e0, s));
+    for (int r = 0; r < reps; ++r) launch_respair_tc(c, s, d1, d2, x16, B, T, y16, a16, out_scale, post_slope);
+    CUDA_OK(cudaEventRecord(e1, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms_out) *ms_out = ms / reps;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    launch_from_planar(c, s, y16, y, B, T, C);
+    CUDA_OK(cudaStreamSynchronize(s));
     while (c->owned.size() > keep) { cudaFree(c->owned.back()); c->owned.pop_back(); }
     API_END(c)
 }

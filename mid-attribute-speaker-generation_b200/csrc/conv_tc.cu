@@ -34,8 +34,10 @@
 //     row-major rows or planar bf16 (lane = time row, so each store instruction writes 512 contiguous bytes).
 #include "common.cuh"
 #include "tc.cuh"
+#include "tc_ptx.cuh"
 
 namespace {
+using namespace tcptx;
 
 // warp roles of the persistent CTA (704 threads, one CTA per SM)
 constexpr int EPI_WARPS = 8;            // warps 0-7: epilogue (warp % 4 = TMEM lane quadrant, warp / 4 = column half)
@@ -73,118 +75,6 @@ struct TcArgs {
 };
 
 // ---------------------------------------------------------------------------------------------
-// PTX wrappers
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(20000u) : "memory");
-    }
-}
-// same, for roles that can afford to sleep: the hardware parks the thread for up to the hinted time instead of
-// re-polling, which keeps 16+ waiting warps from competing with the MMA thread for the shared-memory pipe
-__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(1000000u) : "memory");
-    }
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-// one lane of the (converged) warp; the same lane every time, so MMAs and their commits come from one thread
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]; both operands K-major.  Descriptors are passed as (lo, hi) halves so that
-// advancing an operand is one 32-bit add.
-__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
-                 ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
-}
-// 32 lanes x 16 consecutive fp32 columns; the wait is part of the same statement so the registers are defined after it
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
-        "tcgen05.wait::ld.sync.aligned;"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr) : "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-// streaming 128-bit global load (read-only path, no L1 allocation: every activation byte is used once per tile)
-__device__ __forceinline__ uint4 ld_nc(const uint4* p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ float act_apply(float v, int act, float slope) {
-    switch (act) {
-        case ACT_RELU: return fmaxf(v, 0.f);
-        case ACT_TANH: return tanhf(v);
-        case ACT_LRELU: return v > 0.f ? v : v * slope;
-        default: return v;
-    }
-}
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
-__device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
-    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
-}
-// leaky-relu on two packed bf16 values in three packed instructions.  The slope is carried as c1 + c2 (c1 = bf16(slope),
-// c2 = bf16(slope - c1)) and y = fma(x, c1, x * c2) is rounded once, so y is the correctly rounded bf16 of slope * x
-// to within 2e-6 relative; lrelu(x) = max(x, y) for 0 < slope < 1.
-struct Slope2 { uint32_t c1, c2; };
-__device__ __forceinline__ Slope2 make_slope2(float slope) {
-    const bf16 h = __float2bfloat16_rn(slope);
-    const float l = slope - __bfloat162float(h);
-    Slope2 r; r.c1 = pack_bf16(__bfloat162float(h), __bfloat162float(h)); r.c2 = pack_bf16(l, l);
-    return r;
-}
-__device__ __forceinline__ uint32_t lrelu_bf16x2(uint32_t x, const Slope2 s) {
-    uint32_t t, y, r;
-    asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(t) : "r"(x), "r"(s.c2));
-    asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(y) : "r"(x), "r"(s.c1), "r"(t));
-    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(y));
-    return r;
-}
-// packed fp32 pair arithmetic (sm_100 f32x2 pipe): halves the instruction count of the epilogue's elementwise passes
-__device__ __forceinline__ void add_f32x2(float& a0, float& a1, const float b0, const float b1) {
-    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tadd.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
-        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
-}
-__device__ __forceinline__ void mul_f32x2(float& a0, float& a1, const float b0, const float b1) {
-    asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tmul.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
-        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
-}
-
-// ---------------------------------------------------------------------------------------------
 // Worker staging of row-major fp32 activations: one 16-byte piece = 8 consecutive channels of one row.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint4 convert_piece(const TcArgs& a, const uint4 r0, const uint4 r1, bool ok, uint4& lo) {
@@ -209,6 +99,12 @@ __device__ __forceinline__ uint4 convert_piece(const TcArgs& a, const uint4 r0, 
 // MASG_TC_DEBUG & 16: cycles spent waiting, per role (issuer 0, epilogue warp 0, copy warp, weight warp), summed over CTAs
 __device__ unsigned long long g_tc_stats[16];
 #define STAT_WAIT(flag, idx, stmt) do { if (flag) { const long long _t = clock64(); stmt; atomicAdd(&g_tc_stats[idx], (unsigned long long)(clock64() - _t)); } else { stmt; } } while (0)
+
+// MASG_TC_DEBUG & 32: timeline of CTA 0 — clock64 at the hand-over points of every role for its first TRACE_TILES tiles.
+// roles: 0 copy warp, 1 worker 0, 2 issuer 0, 3 epilogue warp 0, 4 weight warp; events are role-specific (see tc_debug_trace users)
+constexpr int TRACE_TILES = 96, TRACE_EVTS = 4, TRACE_ROLES = 5;
+__device__ long long g_tc_trace[TRACE_ROLES * TRACE_TILES * TRACE_EVTS];
+#define TRACE(on, role, it, evt) do { if ((on) && (it) < TRACE_TILES) g_tc_trace[((role) * TRACE_TILES + (it)) * TRACE_EVTS + (evt)] = clock64(); } while (0)
 
 struct Bars {                                            // mbarrier addresses (shared window), 8 bytes each
     uint32_t base;
@@ -244,12 +140,14 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
     const bool no_w = a.dbg & 1, no_a = a.dbg & 2, no_mma = a.dbg & 8;
     const bool st = (a.dbg & 16) && w == 0 && (threadIdx.x & 31) == 0;
     const long long t_begin = st ? clock64() : 0;
+    const bool tr = (a.dbg & 32) && w == 0 && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
     int wslot = 0, aslot = 0, it = 0;
     uint32_t wphase = 0, aphase = 0;
     for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
         const int accb = it & 1;
         STAT_WAIT(st, 0, mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1));   // epilogue has drained this accumulator set
         tc_fence_after();
+        TRACE(tr, 2, it, 0);
         const uint32_t tacc_w = tmem_base + (uint32_t)(accb * MS * NT + w * NT);
         uint32_t accum = 0;
         int g = a.G;                                                       // forces a stage fetch before the first blob
@@ -257,6 +155,7 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
         uint32_t wbase16 = 0;
         for (int kc = 0; kc < n_chunks; ++kc) {
             if (!no_a) { STAT_WAIT(st, 1, mbar_wait(bars.a_full(aslot), aphase)); tc_fence_after(); }
+            if (kc == 0) TRACE(tr, 2, it, 1);
             const uint32_t abase16 = (a_smem + (uint32_t)aslot * (uint32_t)a.a_bytes) >> 4;
             for (int sub = 0; sub < subs; ++sub) {
                 uint32_t a_tap = abase16 + (uint32_t)sub * a_sub + (uint32_t)(a.off0 - a.off_lo);
@@ -296,6 +195,7 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
         if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));          // the weight stream restarts on a stage boundary per tile
         if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
         if (elect_one()) tc_commit(bars.acc_full(accb));
+        TRACE(tr, 2, it, 2);
     }
     if (st) atomicAdd(&g_tc_stats[3], (unsigned long long)(clock64() - t_begin));
 }
@@ -388,12 +288,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         } else if (TMA_IN) {
             // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled =====
             if (a.in_act != ACT_NONE) {
-                const int pieces = (a.msub * a.a_blk_bytes) >> 4;
+                const int pieces = a.a_tx >> 4;
                 const Slope2 sl = make_slope2(a.in_slope);
-                int slot = 0; uint32_t phase = 0;
-                for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+                int slot = 0, it = 0; uint32_t phase = 0;
+                const bool tr = (a.dbg & 32) && blockIdx.x == 0 && tid == 0;
+                for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
                     for (int kc = 0; kc < n_chunks; ++kc) {
                         STAT_WAIT((a.dbg & 16) && tid == 0, 8, mbar_wait_relaxed(bars.a_raw(slot), phase));
+                        if (kc == 0) TRACE(tr, 1, it, 0);
                         uint4* p = reinterpret_cast<uint4*>(A_smem + (size_t)slot * a.a_bytes);
                         for (int i = tid; i < pieces; i += A_THREADS) {
                             uint4 v = p[i];
@@ -403,6 +305,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                         }
                         fence_proxy_async();                  // generic-proxy stores -> visible to the tensor core (async proxy)
                         mbar_arrive(bars.a_full(slot));
+                        if (kc == 0) TRACE(tr, 1, it, 1);
                         if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
                     }
                 }
@@ -461,31 +364,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         // dimension and was measured at ~16 B/clk/SM, 3.9 TB/s chip-wide.)  Rows outside [0, Tin) — the conv zero padding,
         // only in the first / last tile of an utterance — are zero-filled by the lane before the copies are issued. =====
         if (TMA_IN && !(a.dbg & 2)) {
-            int slot = 0; uint32_t phase = 0;
+            int slot = 0, it = 0; uint32_t phase = 0;
+            const bool tr = (a.dbg & 32) && blockIdx.x == 0 && lane == 0;
             const int cgpc = a.KC >> 3;
-            const int n_copies = a.msub * cgpc;
             const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
-            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
+                    if (kc == 0) TRACE(tr, 0, it, 0);
                     if (lane == 0) STAT_WAIT(a.dbg & 16, 6, mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1));
                     __syncwarp();
+                    if (kc == 0) TRACE(tr, 0, it, 1);
                     const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
                     uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
                     const uint32_t dst = smem_u32(dst_g);
-                    // valid row range of every sub-tile block and the bytes the barrier has to expect
-                    uint32_t tx = 0; bool edge = false;
-                    for (int ms = 0; ms < a.msub; ++ms) {
-                        const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = min(t0 + a.Rp, a.Tin);
-                        if (hi > lo) tx += (uint32_t)(hi - lo) * 16u * (uint32_t)cgpc;
-                        edge |= (lo > t0) || (hi < t0 + a.Rp);
-                    }
-                    if (edge) {
-                        for (int idx = lane; idx < n_copies; idx += 32) {
-                            const int ms = idx / cgpc, g = idx - ms * cgpc;
-                            const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = max(min(t0 + a.Rp, a.Tin), lo);
-                            uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)ms * a.a_blk_bytes + (size_t)g * a.Rp * 16);
+                    // the tile is ONE [KC/8][Rp][8] block (its msub*128 rows + the halo): one contiguous run per 8-channel group
+                    const int t0 = q_lo, lo = max(t0, 0), hi = max(min(t0 + a.Rp, a.Tin), lo);
+                    const uint32_t run = (uint32_t)(hi - lo) * 16u;
+                    if (lo > t0 || hi < t0 + a.Rp) {
+                        for (int g = lane; g < cgpc; g += 32) {
+                            uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)g * a.Rp * 16);
                             for (int r = 0; r < min(lo - t0, a.Rp); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
                             for (int r = max(hi - t0, 0); r < a.Rp; ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
                         }
@@ -493,17 +392,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                         __syncwarp();
                     }
                     if (lane == 0) {
-                        if (tx) mbar_expect_tx(bar, tx); else mbar_arrive(bar);
+                        if (run) mbar_expect_tx(bar, run * (uint32_t)cgpc); else mbar_arrive(bar);
                     }
                     __syncwarp();
-                    for (int idx = lane; idx < n_copies; idx += 32) {
-                        const int ms = idx / cgpc, g = idx - ms * cgpc;
-                        const int t0 = q_lo + ms * 128, lo = max(t0, 0), hi = min(t0 + a.Rp, a.Tin);
-                        if (hi > lo) {
+                    if (run) {
+                        for (int g = lane; g < cgpc; g += 32) {
                             const uint8_t* src = X8 + (((size_t)b * (a.Cin >> 3) + (size_t)(kc * cgpc + g)) * a.Tin + lo) * 16;
-                            bulk_g2s(dst + (uint32_t)(ms * a.a_blk_bytes) + (uint32_t)((g * a.Rp + (lo - t0)) * 16), src, (uint32_t)(hi - lo) * 16u, bar);
+                            bulk_g2s(dst + (uint32_t)((g * a.Rp + (lo - t0)) * 16), src, run, bar);
                         }
                     }
+                    if (kc == 0) TRACE(tr, 0, it, 2);
                     if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
                 }
             }
@@ -561,8 +459,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
             const int n0 = nt * NT, q0 = rt * a.msub * 128;
             const int accb = it & 1;
+            const bool tr = (a.dbg & 32) && blockIdx.x == 0 && threadIdx.x == 0;
+            TRACE(tr, 3, it, 0);
             STAT_WAIT((a.dbg & 16) && threadIdx.x == 0, 4, mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1));
             tc_fence_after();
+            TRACE(tr, 3, it, 1);
             const long boff = (long)b * a.y_bs;
             if (a.dbg & 4) {
                 // what-if: no epilogue work
@@ -707,6 +608,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             tc_fence_before();                              // order this warp's tcgen05.ld before the release below
             __syncwarp();
             if (lane == 0) mbar_arrive(bars.acc_empty(accb));
+            TRACE(tr, 3, it, 2);
         }
         if ((a.dbg & 16) && threadIdx.x == 0) atomicAdd(&g_tc_stats[5], (unsigned long long)(clock64() - t_epi0));
     }
@@ -772,6 +674,14 @@ void tc_debug_stats(unsigned long long* out16, bool reset) {
     if (reset) { unsigned long long z[16] = {0}; CUDA_OK(cudaMemcpyToSymbol(g_tc_stats, z, sizeof(z))); }
 }
 
+int tc_debug_trace(long long* out, int max_elems, bool reset) {
+    const int n = TRACE_ROLES * TRACE_TILES * TRACE_EVTS;
+    if (max_elems < n) return -1;
+    CUDA_OK(cudaMemcpyFromSymbol(out, g_tc_trace, sizeof(long long) * n));
+    if (reset) { static long long z[TRACE_ROLES * TRACE_TILES * TRACE_EVTS]; CUDA_OK(cudaMemcpyToSymbol(g_tc_trace, z, sizeof(z))); }
+    return TRACE_TILES;
+}
+
 void launch_to_planar(masg_ctx* c, cudaStream_t s, const float* x, bf16* out, int B, int T, int C) {
     MASG_CHECK(C % 8 == 0, "planar layout needs C %% 8 == 0 (C=%d)", C);
     const long n = (long)B * T * (C / 8);
@@ -831,23 +741,24 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub /= 2;
     int KC = 0;
     if (tma_in) {
-        // one [KC/8][Rb][8] block per accumulator sub-tile (its 128 rows + the halo), filled by one TMA tile copy
+        // one [KC/8][Rb][8] block per tile (its msub*128 rows + the halo); sub-tile ms starts 128 rows further down; every
+        // 8-channel group is one contiguous run in HBM, moved by a single 1-D bulk copy
         MASG_CHECK(io.x_ld == d.Cin, "conv_tc: planar input must have exactly Cin=%d channels", d.Cin);
-        const int Rb = (128 + halo + 7) & ~7;
-        MASG_CHECK(Rb <= 256, "conv_tc: conv halo %d exceeds the TMA box (Cin=%d taps=%d tstep=%d)", halo, d.Cin, d.taps, d.tstep);
+        int Rb = 0;
         for (;;) {
+            Rb = (msub * 128 + halo + 7) & ~7;
             for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
                 if ((d.Cin / d.KW) % m) continue;
                 const int kc = m * d.KW;
-                if ((size_t)msub * Rb * kc * 2 <= (size_t)A_SLOT_BYTES && kc / 8 <= 256) KC = kc;
+                if ((size_t)Rb * kc * 2 <= (size_t)A_SLOT_BYTES) KC = kc;
             }
             if (KC || msub == 1) break;
             msub /= 2;
         }
         MASG_CHECK(KC > 0, "conv_tc: activation tile does not fit shared memory (Cin=%d taps=%d tstep=%d)", d.Cin, d.taps, d.tstep);
-        a.Rp = Rb; a.rows = Rb; a.a_blk_bytes = Rb * KC * 2; a.a_tx = msub * a.a_blk_bytes;
+        a.Rp = Rb; a.rows = Rb; a.a_blk_bytes = Rb * KC * 2; a.a_tx = a.a_blk_bytes;
         a.a_bytes = (a.a_tx + 1023) & ~1023; a.a_half = 0;
-        a.a_lbo16 = Rb; a.a_ms16 = a.a_blk_bytes >> 4;
+        a.a_lbo16 = Rb; a.a_ms16 = 128;
     } else {
         // one shared [KC/8][Rp][8] tile (rows + halo) staged by the worker warps; sub-tile ms starts 128 rows further down
         MASG_CHECK(io.x_ld % 8 == 0 && io.x_bs % 8 == 0, "conv_tc: x_ld=%d / batch stride must be multiples of 8", io.x_ld);

@@ -125,19 +125,22 @@ static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT,
             const int rb = i * 3 + j;
             const bf16* y = xu;
             for (int m = 0; m < 3; ++m) {
-                // h = lrelu(c1(lrelu(y))); y' = c2(h) + y   (models.py:96-103)
-                convP(c, s, c->hg_c1[rb][m], y, true, B, So, h, So, ACT_LRELU, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)So);
-                if (m < 2) {
-                    bf16* yn = (y == ya) ? yb : ya;
-                    convP(c, s, c->hg_c2[rb][m], h, true, B, So, yn, So, ACT_NONE, ACT_NONE, y, nullptr, 1.f, 1.f, (int)So);
-                    y = yn;
+                // h = lrelu(c1(lrelu(y))); y' = c2(h) + y   (models.py:96-103).  Last pair of the block: fold the MRF sum,
+                // the /3 and the leaky-relu that follows it (models.py:155-161: slope 0.1 before the next upsampler,
+                // F.leaky_relu's default 0.01 before conv_post)
+                const bool last = m == 2;
+                bf16* yn = last ? xs : ((y == ya) ? yb : ya);
+                const bf16* acc = (last && j > 0) ? xs : nullptr;
+                const float scale = (last && j == 2) ? (1.0f / 3.0f) : 1.f;
+                const float post = (last && j == 2) ? (i < 3 ? 0.1f : 0.01f) : 1.f;
+                if (respair_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
+                    // narrow stages: both convs in one kernel, h stays in shared memory (respair_tc.cu)
+                    launch_respair_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
                 } else {
-                    // last pair of the block: fold the MRF sum, the /3 and the leaky-relu that follows it (models.py:155-161:
-                    // slope 0.1 before the next upsampler, F.leaky_relu's default 0.01 before conv_post)
-                    const float post = j == 2 ? (i < 3 ? 0.1f : 0.01f) : 1.f;
-                    convP(c, s, c->hg_c2[rb][m], h, true, B, So, xs, So, ACT_NONE, ACT_NONE, y, j > 0 ? xs : nullptr,
-                          j == 2 ? (1.0f / 3.0f) : 1.f, post, (int)So);
+                    convP(c, s, c->hg_c1[rb][m], y, true, B, So, h, So, ACT_LRELU, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)So);
+                    convP(c, s, c->hg_c2[rb][m], h, true, B, So, yn, So, ACT_NONE, ACT_NONE, y, acc, scale, post, (int)So);
                 }
+                y = yn;
             }
         }
         x = xs; S = So;

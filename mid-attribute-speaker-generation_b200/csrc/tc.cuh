@@ -10,3 +10,9 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
 // MASG_TC_DEBUG & 16 wait-cycle counters of k_conv_tc (summed over CTAs): [0..3] issuer 0: acc_empty, a_full, w_full waits, total;
 // [4,5] epilogue warp 0: acc_full wait, total; [6] copy warp a_empty wait; [7] weight warp w_empty wait; [8] worker a_raw wait
 void tc_debug_stats(unsigned long long* out16, bool reset);
+int tc_debug_trace(long long* out, int max_elems, bool reset);   // MASG_TC_DEBUG & 32: [5 roles][96 tiles][4 events] clock64 of CTA 0
+// fused ResBlock1 pair y = (c2(lrelu(c1(lrelu(x)))) + x [+ R2]) * out_scale [-> lrelu(post_slope)] on planar bf16 [B][C/8][T][8]
+// (respair_tc.cu); supported for C = 32 (k = 3, 7, 11) and C = 64 (k = 3) — the pairs whose weights fit shared memory
+bool respair_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc& d2);
+void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const ConvDesc& d2, const bf16* X, int B, int T,
+                       bf16* Y, const bf16* R2, float out_scale, float post_slope);

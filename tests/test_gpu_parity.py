@@ -408,6 +408,56 @@ def test_conv_kernel_matches_torch(precision, case):
 
 
 # ------------------------------------------------------------------------------------------------
+# the fused ResBlock1 pair kernel (respair_tc.cu) against torch conv1d with the same bf16 rounding points
+# (x, weights, the intermediate h and the output are bf16; accumulation fp32) — hifigan/models.py:96-103
+# ------------------------------------------------------------------------------------------------
+RESPAIR_CASES = [
+    # B, T, C, k, dilation, with MRF accumulator, out_scale, post_slope
+    (2, 1500, 32, 3, 1, False, 1.0, 1.0),
+    (2, 1000, 32, 7, 3, False, 1.0, 1.0),
+    (1, 777, 32, 11, 5, True, 1.0 / 3.0, 0.01),      # last pair of the last block of a stage
+    (3, 100, 32, 11, 1, True, 1.0, 1.0),              # utterance shorter than one tile
+    (1, 246 * 3, 32, 11, 3, False, 1.0, 1.0),         # T an exact multiple of the output rows per tile
+    (2, 300, 64, 3, 5, False, 1.0, 0.1),
+    (1, 2100, 64, 3, 1, True, 1.0, 1.0),
+]
+
+
+@pytest.mark.parametrize("case", RESPAIR_CASES)
+def test_fused_resblock_pair_matches_torch(case):
+    import torch.nn.functional as F
+    from masg_b200 import _lib
+    B, T, C, k, dil, with_acc, scale, post = case
+    cx = _lib.default_context(DEV, "bf16")
+    g = torch.Generator().manual_seed(sum(int(1000 * v) for v in case) % 9973)
+    bf = lambda t: t.to(torch.bfloat16).to(torch.float32)
+    x = torch.randn(B, T, C, generator=g)
+    acc = torch.randn(B, T, C, generator=g) if with_acc else None
+    w1 = torch.randn(C, C, k, generator=g) / (C * k) ** 0.5
+    w2 = torch.randn(C, C, k, generator=g) / (C * k) ** 0.5
+    b1, b2 = torch.randn(C, generator=g) * 0.3, torch.randn(C, generator=g) * 0.3
+    xb = bf(x)
+    h = F.conv1d(bf(F.leaky_relu(xb, 0.1)).transpose(1, 2), bf(w1), b1, dilation=dil, padding=(k * dil - dil) // 2)
+    h = bf(F.leaky_relu(h, 0.1))
+    ref = F.conv1d(h, bf(w2), b2, padding=(k - 1) // 2).transpose(1, 2) + xb
+    if with_acc:
+        ref = ref + bf(acc)
+    ref = ref * scale
+    if post != 1.0:
+        ref = F.leaky_relu(ref, post)
+    to = lambda t: t.contiguous().to(DEV)
+    xg, w1g, w2g, b1g, b2g = to(x), to(w1), to(w2), to(b1), to(b2)
+    ag = to(acc) if with_acc else None
+    y = torch.full((B, T, C), 7.0, device=DEV)
+    ms = ctypes.c_float(0)
+    cx.check(cx.lib.masg_respair(cx.h, cx.stream(), P(xg), P(ag) if with_acc else None, B, T, C, P(w1g), P(b1g), P(w2g), P(b2g), k, dil,
+                                 scale, post, 1, P(y), ctypes.byref(ms)), "respair")
+    err = (y.cpu() - ref).abs().max().item()
+    print("respair %s: max-abs err %.3e (|ref| max %.2f), %.3f ms" % (case, err, ref.abs().max().item(), ms.value))
+    assert err <= 4e-2                                 # one bf16 ulp of the output (|y| < 8) + re-rounding of h at ties
+
+
+# ------------------------------------------------------------------------------------------------
 # masked multi-head attention alone (tcgen05 kernel in bf16 mode) against the reference formula in torch fp64
 # ------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
