@@ -393,6 +393,23 @@ int masg_respair(masg_ctx* c, void* stream, const float* x, const float* acc, in
     CUDA_OK(cudaStreamSynchronize(s));
     float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
     if (ms_out) *ms_out = ms / reps;
+    if (getenv("MASG_TC_DEBUG") && (atoi(getenv("MASG_TC_DEBUG")) & 32)) {
+        static long long tr[5 * 96 * 4];
+        const int nt = respair_debug_trace(tr, 5 * 96 * 4);
+        auto at = [&](int role, int it, int e) { return tr[(role * nt + it) * 4 + e]; };
+        const int i0 = 40, i1 = 52;
+        const long long base = at(0, i0, 0);
+        fprintf(stderr, "  [respair trace, CTA 0, cycles] tile | copy: wait-begin slot-free issued | worker: landed done | issuer: P1-ready P1-committed P2-ready P2-committed | E1: acc1-full h-written | E2: requested acc2-full stored\n");
+        for (int it = i0; it < i1; ++it) {
+            fprintf(stderr, "   %3d |", it);
+            const int ne[5] = {3, 2, 4, 2, 3};
+            for (int role = 0; role < 5; ++role) {
+                for (int e = 0; e < ne[role]; ++e) fprintf(stderr, " %7lld", at(role, it, e) ? at(role, it, e) - base : -1LL);
+                fprintf(stderr, " |");
+            }
+            fprintf(stderr, "\n");
+        }
+    }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     launch_from_planar(c, s, y16, y, B, T, C);
     CUDA_OK(cudaStreamSynchronize(s));

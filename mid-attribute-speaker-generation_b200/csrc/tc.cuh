@@ -12,7 +12,8 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
 void tc_debug_stats(unsigned long long* out16, bool reset);
 int tc_debug_trace(long long* out, int max_elems, bool reset);   // MASG_TC_DEBUG & 32: [5 roles][96 tiles][4 events] clock64 of CTA 0
 // fused ResBlock1 pair y = (c2(lrelu(c1(lrelu(x)))) + x [+ R2]) * out_scale [-> lrelu(post_slope)] on planar bf16 [B][C/8][T][8]
-// (respair_tc.cu); supported for C = 32 (k = 3, 7, 11) and C = 64 (k = 3) — the pairs whose weights fit shared memory
+// (respair_tc.cu); supported for C = 32 (k = 3, 7, 11) and C = 64 (k = 3, 7) — the pairs whose weights fit shared memory
 bool respair_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc& d2);
 void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const ConvDesc& d2, const bf16* X, int B, int T,
                        bf16* Y, const bf16* R2, float out_scale, float post_slope);
+int respair_debug_trace(long long* out, int max_elems);      // MASG_TC_DEBUG & 32: [5 roles][96 tiles][4 events] clock64 of CTA 0

@@ -420,6 +420,8 @@ RESPAIR_CASES = [
     (1, 246 * 3, 32, 11, 3, False, 1.0, 1.0),         # T an exact multiple of the output rows per tile
     (2, 300, 64, 3, 5, False, 1.0, 0.1),
     (1, 2100, 64, 3, 1, True, 1.0, 1.0),
+    (2, 1100, 64, 7, 5, True, 1.0 / 3.0, 0.1),       # weights fill shared memory: 2 activation slots, 1 h buffer
+    (1, 250, 64, 7, 1, False, 1.0, 1.0),
 ]
 
 

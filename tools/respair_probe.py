@@ -11,7 +11,7 @@ from masg_b200 import _lib
 CASES = [  # name, B, T, C, k, dil
     ("s4 k3 d1", 64, 153600, 32, 3, 1), ("s4 k3 d5", 64, 153600, 32, 3, 5), ("s4 k7 d3", 64, 153600, 32, 7, 3),
     ("s4 k11 d1", 64, 153600, 32, 11, 1), ("s4 k11 d5", 64, 153600, 32, 11, 5),
-    ("s3 k3 d1", 64, 76800, 64, 3, 1), ("s3 k3 d5", 64, 76800, 64, 3, 5),
+    ("s3 k3 d1", 64, 76800, 64, 3, 1), ("s3 k3 d5", 64, 76800, 64, 3, 5), ("s3 k7 d3", 64, 76800, 64, 7, 3),
 ]
 
 def main():
