@@ -71,6 +71,7 @@ struct TcArgs {
     int y_planar, y_T, up, up_pad, cout_shift;         // planar bf16 output [B][Cout/8][y_T][8]; t = q*up + n/Cout - up_pad
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale; float post_slope;
+    int w_stages;                                      // weight ring depth (3 with 32 KB stages, else 4 with 16 KB stages)
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
 
@@ -163,7 +164,7 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
                     if (g == a.G) {                                        // next weight stage
                         if (have_stage) {
                             if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));
-                            if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
+                            if (++wslot == a.w_stages) { wslot = 0; wphase ^= 1; }
                         }
                         if (!no_w) { STAT_WAIT(st, 2, mbar_wait(bars.w_full(wslot), wphase)); tc_fence_after(); }
                         wbase16 = (w_smem + (uint32_t)wslot * (uint32_t)a.stage_bytes) >> 4;
@@ -193,7 +194,7 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
             if (++aslot == A_SLOTS) { aslot = 0; aphase ^= 1; }
         }
         if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));          // the weight stream restarts on a stage boundary per tile
-        if (++wslot == W_STAGES) { wslot = 0; wphase ^= 1; }
+        if (++wslot == a.w_stages) { wslot = 0; wphase ^= 1; }
         if (elect_one()) tc_commit(bars.acc_full(accb));
         TRACE(tr, 2, it, 2);
     }
@@ -221,7 +222,7 @@ __device__ __forceinline__ void epi_bias_act(const TcArgs& a, float (&v)[16], co
 }
 __device__ __forceinline__ void add_bf16x8(float* v, const uint4 u) {
     const float2 t0 = unpack_bf16(u.x), t1 = unpack_bf16(u.y), t2 = unpack_bf16(u.z), t3 = unpack_bf16(u.w);
-    v[0] += t0.x; v[1] += t0.y; v[2] += t1.x; v[3] += t1.y; v[4] += t2.x; v[5] += t2.y; v[6] += t3.x; v[7] += t3.y;
+    add_f32x2(v[0], v[1], t0.x, t0.y); add_f32x2(v[2], v[3], t1.x, t1.y); add_f32x2(v[4], v[5], t2.x, t2.y); add_f32x2(v[6], v[7], t3.x, t3.y);
 }
 __device__ __forceinline__ void epi_scale_post(const TcArgs& a, float (&v)[16]) {
     if (a.out_scale != 1.f) {
@@ -243,6 +244,88 @@ __device__ __forceinline__ long planar_off(const TcArgs& a, int q, int n) {
     const int t = q * a.up + r - a.up_pad;
     if (q >= a.Q || t < 0 || t >= a.y_T) return -1;
     return ((long)(co >> 3) * a.y_T + t) * 8;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Planar bf16 epilogue [Cout/8][y_T][8] (HiFi-GAN layers): lane = time row, one 16-byte store per 8 columns.  Columns
+// outer (bias and column offsets in registers), sub-tiles inner.  Specialised on the residuals so that a plain conv
+// (bias -> leaky-relu -> store) is ~70 instructions per 16 columns; with residuals the next sub-tile's rows are requested
+// before this sub-tile's accumulator is read.  (The generic version of this loop cost ~200 instructions per 16 columns and
+// set the pace of every HBM-bound layer: profiles/r1_conv_tc_trace.log.)
+// ---------------------------------------------------------------------------------------------
+template <int NT, bool HAS_R1, bool HAS_R2>
+__device__ __forceinline__ void epi_planar(const TcArgs& a, const uint32_t tacc, const float* bias_s, const int n0, const int q0,
+                                           const long boff, const int quad, const int half, const int lane) {
+    constexpr int c_split = ((NT / 16 + 1) / 2) * 16;
+    const int c_begin = half ? c_split : 0, c_end = half ? NT : c_split;
+    const bf16* R1h = reinterpret_cast<const bf16*>(a.R1); const bf16* R2h = reinterpret_cast<const bf16*>(a.R2);
+    const int q_lane = q0 + quad * 32 + lane;
+    const long gstride = (long)a.y_T * 8;                                   // elements between 8-channel groups
+    const int t_step = 128 * a.up;
+    const bool lrelu_out = a.out_act == ACT_LRELU, other_act = a.out_act != ACT_NONE && a.out_act != ACT_LRELU;
+    const bool scaled = a.out_scale != 1.f, post = a.post_slope != 1.f;
+    const Slope2 sl_out = make_slope2(a.out_slope), sl_post = make_slope2(a.post_slope);
+    for (int cc = c_begin; cc < c_end; cc += 16) {
+        const int n = n0 + cc;
+        const int co = n & ((1 << a.cout_shift) - 1), r = n >> a.cout_shift;
+        const int t0 = q_lane * a.up + r - a.up_pad;
+        const long cbase = boff + (long)(co >> 3) * gstride;
+        const float4* b4 = reinterpret_cast<const float4*>(bias_s + n);
+        const float4 ba = b4[0], bb = b4[1], bc = b4[2], bd = b4[3];
+        uint4 r1a, r1b, r2a, r2b;
+        bool ok = q_lane < a.Q && (unsigned)t0 < (unsigned)a.y_T;
+        long off = cbase + (long)t0 * 8;
+        if (HAS_R1) { r1a = r1b = make_uint4(0u, 0u, 0u, 0u); if (ok) { r1a = *reinterpret_cast<const uint4*>(R1h + off); r1b = *reinterpret_cast<const uint4*>(R1h + off + gstride); } }
+        if (HAS_R2) { r2a = r2b = make_uint4(0u, 0u, 0u, 0u); if (ok) { r2a = *reinterpret_cast<const uint4*>(R2h + off); r2b = *reinterpret_cast<const uint4*>(R2h + off + gstride); } }
+        for (int ms = 0; ms < a.msub; ++ms) {
+            // rows of the next sub-tile
+            const int tn = t0 + (ms + 1) * t_step;
+            const bool okn = ms + 1 < a.msub && q_lane + (ms + 1) * 128 < a.Q && (unsigned)tn < (unsigned)a.y_T;
+            const long offn = cbase + (long)tn * 8;
+            uint4 x1a, x1b, x2a, x2b;
+            if (HAS_R1) { x1a = x1b = make_uint4(0u, 0u, 0u, 0u); if (okn) { x1a = *reinterpret_cast<const uint4*>(R1h + offn); x1b = *reinterpret_cast<const uint4*>(R1h + offn + gstride); } }
+            if (HAS_R2) { x2a = x2b = make_uint4(0u, 0u, 0u, 0u); if (okn) { x2a = *reinterpret_cast<const uint4*>(R2h + offn); x2b = *reinterpret_cast<const uint4*>(R2h + offn + gstride); } }
+            float v[16];
+            tmem_ld16(tacc + (uint32_t)(ms * NT + cc), v);
+            add_f32x2(v[0], v[1], ba.x, ba.y); add_f32x2(v[2], v[3], ba.z, ba.w); add_f32x2(v[4], v[5], bb.x, bb.y); add_f32x2(v[6], v[7], bb.z, bb.w);
+            add_f32x2(v[8], v[9], bc.x, bc.y); add_f32x2(v[10], v[11], bc.z, bc.w); add_f32x2(v[12], v[13], bd.x, bd.y); add_f32x2(v[14], v[15], bd.z, bd.w);
+            if (other_act) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i], a.out_act, a.out_slope);
+            }
+            uint4 pa, pb;
+            if (HAS_R1 || HAS_R2 || scaled) {
+                if (lrelu_out) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * a.out_slope);
+                }
+                if (HAS_R1) { add_bf16x8(v, r1a); add_bf16x8(v + 8, r1b); }
+                if (HAS_R2) { add_bf16x8(v, r2a); add_bf16x8(v + 8, r2b); }
+                if (scaled) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 2) mul_f32x2(v[i], v[i + 1], a.out_scale, a.out_scale);
+                }
+                pa = pack8(v); pb = pack8(v + 8);
+            } else {
+                pa = pack8(v); pb = pack8(v + 8);
+                if (lrelu_out) {                                   // on the packed values: 3 instructions per pair
+                    pa.x = lrelu_bf16x2(pa.x, sl_out); pa.y = lrelu_bf16x2(pa.y, sl_out); pa.z = lrelu_bf16x2(pa.z, sl_out); pa.w = lrelu_bf16x2(pa.w, sl_out);
+                    pb.x = lrelu_bf16x2(pb.x, sl_out); pb.y = lrelu_bf16x2(pb.y, sl_out); pb.z = lrelu_bf16x2(pb.z, sl_out); pb.w = lrelu_bf16x2(pb.w, sl_out);
+                }
+            }
+            if (post) {
+                pa.x = lrelu_bf16x2(pa.x, sl_post); pa.y = lrelu_bf16x2(pa.y, sl_post); pa.z = lrelu_bf16x2(pa.z, sl_post); pa.w = lrelu_bf16x2(pa.w, sl_post);
+                pb.x = lrelu_bf16x2(pb.x, sl_post); pb.y = lrelu_bf16x2(pb.y, sl_post); pb.z = lrelu_bf16x2(pb.z, sl_post); pb.w = lrelu_bf16x2(pb.w, sl_post);
+            }
+            if (ok) {
+                *reinterpret_cast<uint4*>(a.Y16 + off) = pa;
+                *reinterpret_cast<uint4*>(a.Y16 + off + gstride) = pb;
+            }
+            ok = okn; off = offn;
+            if (HAS_R1) { r1a = x1a; r1b = x1b; }
+            if (HAS_R2) { r2a = x2a; r2b = x2b; }
+        }
+    }
 }
 
 template <int NT, bool TMA_IN>
@@ -419,7 +502,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     const uint32_t bytes = (uint32_t)nb * a.blob_bytes;
                     mbar_expect_tx(bars.w_full(slot), bytes);
                     bulk_g2s(smem_u32(W_smem + (size_t)slot * a.stage_bytes), src + (size_t)st * a.G * a.blob_bytes, bytes, bars.w_full(slot));
-                    if (++slot == W_STAGES) { slot = 0; phase ^= 1; }
+                    if (++slot == a.w_stages) { slot = 0; phase ^= 1; }
                 }
             }
         }
@@ -468,82 +551,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             if (a.dbg & 4) {
                 // what-if: no epilogue work
             } else if (a.y_planar) {
-                // ---- planar bf16 output [Cout/8][y_T][8]: lane = row, one 16-byte store per 8 columns.  Columns outer (bias
-                //      and column offsets live in registers), sub-tiles inner with the next sub-tile's residuals in flight ----
-                const int ncg = (c_end - c_begin) >> 4;
-                const int q_lane = q0 + quad * 32 + lane;
-                const long gstride = (long)a.y_T * 8;                       // elements between 8-channel groups
-                const int t_step = 128 * a.up;
-                const bool has_r1 = a.R1 != nullptr, has_r2 = a.R2 != nullptr;
-                const Slope2 sl_out = make_slope2(a.out_slope), sl_post = make_slope2(a.post_slope);
-                for (int cgi = 0; cgi < ncg; ++cgi) {
-                    const int cc = c_begin + cgi * 16, n = n0 + cc;
-                    const int co = n & ((1 << a.cout_shift) - 1), r = n >> a.cout_shift;
-                    const int t0 = q_lane * a.up + r - a.up_pad;
-                    const long cbase = boff + (long)(co >> 3) * gstride;
-                    float bb[16];
-                    {
-                        const float4* b4 = reinterpret_cast<const float4*>(bias_s + n);
-#pragma unroll
-                        for (int h = 0; h < 4; ++h) { const float4 t = b4[h]; bb[h * 4] = t.x; bb[h * 4 + 1] = t.y; bb[h * 4 + 2] = t.z; bb[h * 4 + 3] = t.w; }
-                    }
-                    const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols + cc);
-                    uint4 r1a = make_uint4(0u, 0u, 0u, 0u), r1b = r1a, r2a = r1a, r2b = r1a;
-                    bool ok = q_lane < a.Q && (unsigned)t0 < (unsigned)a.y_T;
-                    long off = cbase + (long)t0 * 8;
-                    if (ok) {
-                        if (has_r1) { r1a = *reinterpret_cast<const uint4*>(R1h + off); r1b = *reinterpret_cast<const uint4*>(R1h + off + gstride); }
-                        if (has_r2) { r2a = *reinterpret_cast<const uint4*>(R2h + off); r2b = *reinterpret_cast<const uint4*>(R2h + off + gstride); }
-                    }
-                    for (int ms = 0; ms < a.msub; ++ms) {
-                        // residuals of the next sub-tile
-                        const int tn = t0 + (ms + 1) * t_step;
-                        const bool okn = ms + 1 < a.msub && q_lane + (ms + 1) * 128 < a.Q && (unsigned)tn < (unsigned)a.y_T;
-                        const long offn = cbase + (long)tn * 8;
-                        uint4 x1a = make_uint4(0u, 0u, 0u, 0u), x1b = x1a, x2a = x1a, x2b = x1a;
-                        if (okn) {
-                            if (has_r1) { x1a = *reinterpret_cast<const uint4*>(R1h + offn); x1b = *reinterpret_cast<const uint4*>(R1h + offn + gstride); }
-                            if (has_r2) { x2a = *reinterpret_cast<const uint4*>(R2h + offn); x2b = *reinterpret_cast<const uint4*>(R2h + offn + gstride); }
-                        }
-                        float v[16];
-                        tmem_ld16(tcol + (uint32_t)(ms * NT), v);
-#pragma unroll
-                        for (int i = 0; i < 16; i += 2) add_f32x2(v[i], v[i + 1], bb[i], bb[i + 1]);
-                        if (a.out_act != ACT_NONE && a.out_act != ACT_LRELU) {
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i], a.out_act, a.out_slope);
-                        }
-                        uint4 pa, pb;
-                        if (has_r1 || has_r2 || a.out_scale != 1.f) {
-                            if (a.out_act == ACT_LRELU) {
-#pragma unroll
-                                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * a.out_slope);
-                            }
-                            if (has_r1) { add_bf16x8(v, r1a); add_bf16x8(v + 8, r1b); }
-                            if (has_r2) { add_bf16x8(v, r2a); add_bf16x8(v + 8, r2b); }
-                            if (a.out_scale != 1.f) {
-#pragma unroll
-                                for (int i = 0; i < 16; i += 2) mul_f32x2(v[i], v[i + 1], a.out_scale, a.out_scale);
-                            }
-                            pa = pack8(v); pb = pack8(v + 8);
-                        } else {
-                            pa = pack8(v); pb = pack8(v + 8);
-                            if (a.out_act == ACT_LRELU) {                  // on the packed values: 3 instructions per pair
-                                pa.x = lrelu_bf16x2(pa.x, sl_out); pa.y = lrelu_bf16x2(pa.y, sl_out); pa.z = lrelu_bf16x2(pa.z, sl_out); pa.w = lrelu_bf16x2(pa.w, sl_out);
-                                pb.x = lrelu_bf16x2(pb.x, sl_out); pb.y = lrelu_bf16x2(pb.y, sl_out); pb.z = lrelu_bf16x2(pb.z, sl_out); pb.w = lrelu_bf16x2(pb.w, sl_out);
-                            }
-                        }
-                        if (a.post_slope != 1.f) {
-                            pa.x = lrelu_bf16x2(pa.x, sl_post); pa.y = lrelu_bf16x2(pa.y, sl_post); pa.z = lrelu_bf16x2(pa.z, sl_post); pa.w = lrelu_bf16x2(pa.w, sl_post);
-                            pb.x = lrelu_bf16x2(pb.x, sl_post); pb.y = lrelu_bf16x2(pb.y, sl_post); pb.z = lrelu_bf16x2(pb.z, sl_post); pb.w = lrelu_bf16x2(pb.w, sl_post);
-                        }
-                        if (ok) {
-                            *reinterpret_cast<uint4*>(a.Y16 + off) = pa;
-                            *reinterpret_cast<uint4*>(a.Y16 + off + gstride) = pb;
-                        }
-                        ok = okn; off = offn; r1a = x1a; r1b = x1b; r2a = x2a; r2b = x2b;
-                    }
-                }
+                const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols);
+                if (a.R1 == nullptr) epi_planar<NT, false, false>(a, tacc, bias_s, n0, q0, boff, quad, half, lane);
+                else if (a.R2 == nullptr) epi_planar<NT, true, false>(a, tacc, bias_s, n0, q0, boff, quad, half, lane);
+                else epi_planar<NT, true, true>(a, tacc, bias_s, n0, q0, boff, quad, half, lane);
             } else {
                 // ---- row-major output (fp32 and/or bf16): lane = row, 16 consecutive columns per store group ----
                 const int gc = ((a.R1 || a.R2) && !a.r_bf16) ? 16 : 32;     // columns per residual prefetch group (4 x 16 bytes)
@@ -788,7 +799,20 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     }
     a.msub = msub; a.KC = KC;
     a.blob_bytes = d.KW * NT * 2 * (int)a_mul;
+    a.n_blobs = (d.Cin / d.KW) * d.taps;
+    // weight ring: every stage costs the issuers one barrier round trip, so stages hold two 16 KB blobs (three stages)
+    // when that fits beside the activation slots and the stream is long, else 16 KB (four stages)
+    a.w_stages = W_STAGES;
     a.G = std::max(1, W_STAGE_BYTES / a.blob_bytes);
+    {
+        static int big = -1;
+        if (big < 0) { const char* e = getenv("MASG_TC_WSTAGE32"); big = e ? atoi(e) : 1; }
+        const int g2 = std::max(1, 2 * W_STAGE_BYTES / a.blob_bytes);
+        const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + 3 * (size_t)g2 * a.blob_bytes;
+        // measured at the C3 shapes: a gain for the long weight streams (k = 11: 22 / 44 blobs per tile, +8 % / +13 %), a loss for
+        // the short ones (k = 3, 7 and the upsamplers), where the shallower ring shows at every tile start
+        if (big && !d.split && a.blob_bytes == W_STAGE_BYTES && a.n_blobs >= 20 && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
+    }
     a.stage_bytes = a.G * a.blob_bytes;
     a.n_blobs = (d.Cin / d.KW) * d.taps;
     int cols = 32; while (cols < 2 * msub * NT) cols *= 2;
@@ -813,7 +837,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
                    "conv_tc: output row stride/offset/bias period must be multiples of 16");
     }
     MASG_CHECK(a.in_act == ACT_NONE || a.in_act == ACT_LRELU || !tma_in, "conv_tc: planar input supports leaky-relu only");
-    const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)W_STAGES * a.stage_bytes;
+    const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)a.w_stages * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
     MASG_CHECK(!tma_in || ((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
     static int n_sm = 0;

@@ -436,8 +436,9 @@ template <bool XBF>
 __global__ void __launch_bounds__(256)
 k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias, long S, float slope,
             float* __restrict__ wav, int16_t* __restrict__ wav16) {
-    __shared__ float xs[262 * 33];
-    __shared__ float ws[7 * 32];
+    constexpr int XS = 36;                                   // row stride in floats: 16-byte aligned rows, conflict-free 128-bit accesses
+    __shared__ __align__(16) float xs[262 * XS];
+    __shared__ __align__(16) float ws[7 * 32];
     int b = blockIdx.y; long s0 = (long)blockIdx.x * 256;
     int tid = threadIdx.x;
     if (tid < 224) ws[tid] = w[tid];
@@ -453,9 +454,10 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
 #pragma unroll
                 for (int k = 0; k < 4; ++k) { f[2 * k] = __uint_as_float(w4[k] << 16); f[2 * k + 1] = __uint_as_float(w4[k] & 0xffff0000u); }
             }
-            float* dst = &xs[r * 33 + g * 8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) dst[k] = f[k] > 0.f ? f[k] : f[k] * slope;
+            for (int k = 0; k < 8; ++k) f[k] = f[k] > 0.f ? f[k] : f[k] * slope;
+            float4* dst = reinterpret_cast<float4*>(&xs[r * XS + g * 8]);
+            dst[0] = make_float4(f[0], f[1], f[2], f[3]); dst[1] = make_float4(f[4], f[5], f[6], f[7]);
         }
     } else {
         for (int i = tid; i < 262 * 8; i += 256) {
@@ -465,8 +467,7 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
             if (srow >= 0 && srow < S) v = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xv) + ((long)b * S + srow) * 32)[c4];
             v.x = v.x > 0.f ? v.x : v.x * slope; v.y = v.y > 0.f ? v.y : v.y * slope;
             v.z = v.z > 0.f ? v.z : v.z * slope; v.w = v.w > 0.f ? v.w : v.w * slope;
-            float* dst = &xs[r * 33 + c4 * 4];
-            dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+            *reinterpret_cast<float4*>(&xs[r * XS + c4 * 4]) = v;
         }
     }
     __syncthreads();
@@ -475,9 +476,13 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
     float acc = bias;
 #pragma unroll
     for (int j = 0; j < 7; ++j) {
-        const float* row = &xs[(tid + j) * 33];
+        const float4* row = reinterpret_cast<const float4*>(&xs[(tid + j) * XS]);
+        const float4* wr = reinterpret_cast<const float4*>(&ws[j * 32]);
 #pragma unroll
-        for (int cc = 0; cc < 32; ++cc) acc += row[cc] * ws[j * 32 + cc];
+        for (int c4 = 0; c4 < 8; ++c4) {                       // same summation order as before: channels ascending within a tap
+            const float4 xv4 = row[c4], wv = wr[c4];
+            acc += xv4.x * wv.x; acc += xv4.y * wv.y; acc += xv4.z * wv.z; acc += xv4.w * wv.w;
+        }
     }
     float y = tanhf(acc);
     if (wav) wav[(long)b * S + sidx] = y;

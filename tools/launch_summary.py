@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: one step of bench.py (the launches between the
 last two k_conv_post), grouped by kernel and, for k_conv_tc, by position in the graph."""
-import csv, re, sys, collections
+import csv, re, sys, collections, signal
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 path = sys.argv[1]
 with open(path) as f:
     rows = list(csv.DictReader([l for l in f if not l.startswith('==')]))
