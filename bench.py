@@ -377,7 +377,7 @@ def run_ours(args):
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": B * world, "phonemes": L, "frames_per_utt": 3 * L, "parallelism": "dp%d" % world,
-                   "precision": args.precision + (" (HiFi-GAN plain bf16; FastSpeech2 split-bf16 hi/lo, 3 MMAs per K step)" if args.precision == "bf16" else ""),
+                   "precision": args.precision + (" (HiFi-GAN bf16; FastSpeech2 encoder + variance predictors split-bf16 hi/lo, 3 MMAs per K step; decoder, mel_linear, PostNet fp16 operands; fp32 accumulation everywhere)" if args.precision == "bf16" else ""),
                    "weights": "seeded random init (no checkpoint in the reference tree)",
                    "l2": "256 MiB flush buffer written before every timed step; activations (GBs per step) far exceed the 126 MB L2"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},

@@ -7,7 +7,7 @@
 #include <algorithm>
 
 ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
-                   const float* scale, const float* bias_override, bool split);
+                   const float* scale, const float* bias_override, int mode);
 
 static thread_local std::string g_err;
 

@@ -53,7 +53,7 @@ struct ConvDesc {
     const float* bias = nullptr;      // [bias_mod]
     // tcgen05 path (conv_tc.cu): bf16 weights pre-tiled into UMMA no-swizzle K-major blobs
     // [n_tile = N/NT][ci = Cin/KW][tap][KW/8][NT][8]; one blob = one (channel slab, tap) B operand
-    const bf16* w16 = nullptr; int NT = 0, KW = 0, split = 0;
+    const bf16* w16 = nullptr; int NT = 0, KW = 0, split = 0, f16 = 0;   // f16: the blobs hold fp16, not bf16
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc

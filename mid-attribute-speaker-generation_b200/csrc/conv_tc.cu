@@ -64,6 +64,7 @@ struct TcArgs {
     int Cin, N, taps, off0, tstep;
     int KW, KC, G, a_bytes, stage_bytes, blob_bytes, n_blobs;
     int msub, rows, Rp, off_lo, tmem_cols, split, a_half;
+    int f16;                                           // operands are fp16 (single pass, 11-bit mantissa) instead of bf16
     int a_lbo16, a_ms16, a_tx, a_blk_bytes;            // operand strides in 16-byte units; TMA bytes per chunk; bytes per ms block
     int B, row_tiles, n_ntiles, total_tiles;
     // output
@@ -87,6 +88,10 @@ __device__ __forceinline__ uint4 convert_piece(const TcArgs& a, const uint4 r0, 
     if (a.in_act != ACT_NONE) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = act_apply(f[i], a.in_act, a.in_slope);
+    }
+    if (a.f16) {
+        o.x = pack_f16(f[0], f[1]); o.y = pack_f16(f[2], f[3]); o.z = pack_f16(f[4], f[5]); o.w = pack_f16(f[6], f[7]);
+        return o;
     }
     o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]); o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
     if (a.split) {                                       // residual of the bf16 rounding, itself rounded to bf16
@@ -130,7 +135,8 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
     constexpr int w = W;                                   // issuer index: compile-time, so every value below is warp-uniform
     constexpr int MSL = MS / NI;
     // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t ab_fmt = a.f16 ? 0u : ((1u << 7) | (1u << 10));                         // A / B format: 0 = fp16, 1 = bf16
+    const uint32_t idesc = (1u << 4) | ab_fmt | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);                     // SBO = 128 B, descriptor version 1
     const uint32_t a_fixed = (uint32_t)a.a_lbo16 << 16, w_fixed = (uint32_t)NT << 16;     // LBO fields (16-byte units)
     const uint32_t a_ks = 2u * (uint32_t)a.a_lbo16, w_ks = 2u * (uint32_t)NT;              // one K=16 step = two 8-channel groups
@@ -643,6 +649,7 @@ __global__ void k_tile_w(const float* __restrict__ w32, bf16* __restrict__ out, 
     int ci = (int)(r % (Cin / KW)); int t = (int)(r / (Cin / KW));
     long row = (long)j * Cin + (long)ci * KW + k8 * 8 + e;
     float w = w32[row * N + (long)t * NT + n];
+    if (split == 2) { reinterpret_cast<__half*>(out)[i] = __float2half_rn(w); return; }      // fp16 single-pass layers
     bf16 hi = __float2bfloat16_rn(w);
     if (!split) { out[i] = hi; return; }
     long blob = i / ((long)KW * NT), within = i % ((long)KW * NT);
@@ -705,7 +712,8 @@ void launch_from_planar(masg_ctx* c, cudaStream_t s, const bf16* x, float* out, 
     c->launches++;
 }
 
-void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
+void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
+    const bool split = mode == 1;
     MASG_CHECK(d.w32 != nullptr, "tc_prepare_weights: fp32 GEMM weights missing");
     int NT = 0;
     const int cands[4] = {128, 80, 64, 32};
@@ -718,9 +726,9 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, bool split) {
     bf16* w16 = nullptr;
     CUDA_OK(cudaMalloc(&w16, n * sizeof(bf16) * (split ? 2 : 1)));
     c->owned.push_back(w16);
-    k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, w16, d.Cin, d.N, d.taps, NT, KW, split ? 1 : 0);
+    k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, w16, d.Cin, d.N, d.taps, NT, KW, mode);
     c->launches++;
-    d.w16 = w16; d.NT = NT; d.KW = KW; d.split = split ? 1 : 0;
+    d.w16 = w16; d.NT = NT; d.KW = KW; d.split = split ? 1 : 0; d.f16 = mode == 2 ? 1 : 0;
 }
 
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
@@ -736,7 +744,8 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
     a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
-    a.KW = d.KW; a.split = d.split;
+    a.KW = d.KW; a.split = d.split; a.f16 = d.f16;
+    MASG_CHECK(!d.f16 || !io.x_planar, "conv_tc: fp16 layers take row-major fp32 activations");
     const int NT = d.NT;
     const size_t a_mul = d.split ? 2 : 1;
     int off_lo = d.off0, off_hi = d.off0;

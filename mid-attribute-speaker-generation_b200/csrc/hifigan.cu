@@ -6,7 +6,7 @@
 #include "tc.cuh"
 
 ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bias, int Cout, int Cin, int k, int pad, int dil,
-                   const float* scale, const float* bias_override, bool split);
+                   const float* scale, const float* bias_override, int mode);
 
 template <typename T> static T* dev_alloc(masg_ctx* c, size_t n) {
     T* p = nullptr;

@@ -2,6 +2,7 @@
 // TMEM load, packed bf16 / f32x2 arithmetic.  sm_100a only.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace tcptx {
 
@@ -105,6 +106,10 @@ __device__ __forceinline__ float act_apply(float v, int act, float slope) {
 }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t pack_f16(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
