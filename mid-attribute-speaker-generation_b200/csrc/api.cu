@@ -301,7 +301,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     API_BEGIN(c)
     cudaStream_t s = (cudaStream_t)stream;
     MASG_CHECK(x && w && y && B > 0 && T > 0 && reps >= 1, "bad argument");
-    const int split = flags & 1, act_bf16 = (flags & 2) && c->precision == MASG_PREC_BF16, residual = flags & 4;
+    const int split = (flags & 8) ? 2 : (flags & 1), act_bf16 = (flags & 2) && c->precision == MASG_PREC_BF16, residual = flags & 4;
     MASG_CHECK(!residual || (Cin == Cout && stride_transposed == 0), "residual needs Cin == Cout and a plain conv");
     const size_t keep = c->owned.size();
     ConvDesc d; int Q = T; long So = T;
@@ -313,10 +313,10 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         float* w32 = nullptr; CUDA_OK(cudaMalloc(&w32, (size_t)2 * Cin * u * Cout * 4)); c->owned.push_back(w32);
         launch_repack_convT_w(c, s, w, Cin, Cout, k, u, w32);
         d.w32 = w32; d.bias = bias;
-        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d, split != 0);
+        if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d, split);
         Q = T + 1; So = (long)T * u;
     } else {
-        d = make_conv(c, s, w, bias, Cout, Cin, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, split != 0);
+        d = make_conv(c, s, w, bias, Cout, Cin, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, split);
     }
     ConvIO io;
     io.X = x; io.x_ld = Cin; io.x_bs = (long)T * Cin; io.Tin = T; io.Y = y; io.y_bs = So * Cout; io.y_limit = So * Cout;

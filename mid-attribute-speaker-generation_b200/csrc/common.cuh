@@ -111,6 +111,7 @@ struct ConvIO {
     const void* X = nullptr; int x_bf16 = 0; long x_bs = 0; int x_ld = 0; int Tin = 0;   // input rows [B][Tin][x_ld] fp32, or
     int x_planar = 0;                                                        // bf16 planar [B][x_ld/8][Tin][8] (tcgen05 path only)
     int y_planar = 0, y_T = 0;                                               // Y16 is planar [B][Cout/8][y_T][8] (residuals too)
+    int y_f16 = 0;                                                           // planar output holds fp16 (feeds an fp16 layer), not bf16
     float post_slope = 1.f;                                                  // trailing leaky-relu after residuals and scale (1 = none)
     float* Y = nullptr; bf16* Y16 = nullptr; long y_bs = 0; long y_limit = 0;  // fp32 and/or bf16 output, valid elements per batch
     int B = 1, Q = 0;                                                        // rows computed per batch

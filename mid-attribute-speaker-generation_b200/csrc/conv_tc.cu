@@ -64,6 +64,7 @@ struct TcArgs {
     int Cin, N, taps, off0, tstep;
     int KW, KC, G, a_bytes, stage_bytes, blob_bytes, n_blobs;
     int msub, rows, Rp, off_lo, tmem_cols, split, a_half;
+    int y_f16;                                         // planar output is fp16
     int f16;                                           // operands are fp16 (single pass, 11-bit mantissa) instead of bf16
     int a_lbo16, a_ms16, a_tx, a_blk_bytes;            // operand strides in 16-byte units; TMA bytes per chunk; bytes per ms block
     int B, row_tiles, n_ntiles, total_tiles;
@@ -240,6 +241,9 @@ __device__ __forceinline__ void epi_scale_post(const TcArgs& a, float (&v)[16]) 
         for (int i = 0; i < 16; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * a.post_slope;
     }
 }
+__device__ __forceinline__ uint4 pack8h(const float* v) {
+    return make_uint4(pack_f16(v[0], v[1]), pack_f16(v[2], v[3]), pack_f16(v[4], v[5]), pack_f16(v[6], v[7]));
+}
 __device__ __forceinline__ uint4 pack8(const float* v) {
     return make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
@@ -311,9 +315,9 @@ __device__ __forceinline__ void epi_planar(const TcArgs& a, const uint32_t tacc,
 #pragma unroll
                     for (int i = 0; i < 16; i += 2) mul_f32x2(v[i], v[i + 1], a.out_scale, a.out_scale);
                 }
-                pa = pack8(v); pb = pack8(v + 8);
+                if (a.y_f16) { pa = pack8h(v); pb = pack8h(v + 8); } else { pa = pack8(v); pb = pack8(v + 8); }
             } else {
-                pa = pack8(v); pb = pack8(v + 8);
+                if (a.y_f16) { pa = pack8h(v); pb = pack8h(v + 8); } else { pa = pack8(v); pb = pack8(v + 8); }
                 if (lrelu_out) {                                   // on the packed values: 3 instructions per pair
                     pa.x = lrelu_bf16x2(pa.x, sl_out); pa.y = lrelu_bf16x2(pa.y, sl_out); pa.z = lrelu_bf16x2(pa.z, sl_out); pa.w = lrelu_bf16x2(pa.w, sl_out);
                     pb.x = lrelu_bf16x2(pb.x, sl_out); pb.y = lrelu_bf16x2(pb.y, sl_out); pb.z = lrelu_bf16x2(pb.z, sl_out); pb.w = lrelu_bf16x2(pb.w, sl_out);
@@ -745,7 +749,10 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
     a.KW = d.KW; a.split = d.split; a.f16 = d.f16;
-    MASG_CHECK(!d.f16 || !io.x_planar, "conv_tc: fp16 layers take row-major fp32 activations");
+    MASG_CHECK(!io.x_planar || !io.in_act || !d.f16, "conv_tc: planar fp16 input has no input activation");
+    a.y_f16 = io.y_f16;
+    MASG_CHECK(!io.y_f16 || (io.y_planar && io.out_act != ACT_LRELU && io.post_slope == 1.f && !io.R1 && !io.R2),
+               "conv_tc: fp16 planar output supports bias + relu / tanh only");
     const int NT = d.NT;
     const size_t a_mul = d.split ? 2 : 1;
     int off_lo = d.off0, off_hi = d.off0;

@@ -169,6 +169,29 @@ static void conv32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* 
     launch_conv(c, s, d, io);
 }
 
+// fp16 layer -> fp16 layer hand-over (decoder side, MASG_PREC_BF16): the producer's epilogue writes the activation as planar
+// fp16 [B][C/8][T][8] — the tcgen05 operand layout — and the consumer moves it with bulk async copies, no conversion pass.
+static void conv_to_planar16(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const void* X, bool x_planar, int x_ld, int B, int T,
+                             bf16* Y16, int out_act) {
+    ConvIO io;
+    io.X = X; io.x_ld = x_ld; io.x_bs = (long)T * x_ld; io.Tin = T; io.x_planar = x_planar; io.x_bf16 = x_planar;
+    io.Y16 = Y16; io.y_planar = 1; io.y_f16 = 1; io.y_T = T; io.y_bs = (long)T * d.N; io.y_limit = io.y_bs;
+    io.B = B; io.Q = T; io.out_act = out_act;
+    launch_conv(c, s, d, io);
+}
+static void conv_from_planar16(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const bf16* X16, int B, int T, float* Y,
+                               int out_act = ACT_NONE, const float* R1 = nullptr) {
+    ConvIO io;
+    io.X = X16; io.x_ld = d.Cin; io.x_bs = (long)T * d.Cin; io.Tin = T; io.x_planar = 1; io.x_bf16 = 1;
+    io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
+    launch_conv(c, s, d, io);
+}
+static bool f16_chain(const masg_ctx* c, const ConvDesc& a, const ConvDesc& b) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("MASG_F16_PLANAR"); on = e ? atoi(e) : 1; }
+    return on && c->precision == MASG_PREC_BF16 && a.f16 && b.f16 && (a.N & (a.N - 1)) == 0 && a.N >= 64;
+}
+
 static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S) {
     // in place on x: every consumer of the old x has been enqueued before the LayerNorm overwrites it
     size_t rows = (size_t)B * S, mk = ar.mark();
@@ -183,8 +206,13 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     ar.restore(mk);
     float* h = ar.get<float>(rows * 1024);
     float* y2 = ar.get<float>(rows * 256);
-    conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
-    conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
+    if (f16_chain(c, L.w1, L.w2)) {                                             // h only feeds w_2: planar fp16, never fp32
+        conv_to_planar16(c, s, L.w1, x, false, 256, B, S, (bf16*)h, ACT_RELU);
+        conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
+    } else {
+        conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
+        conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
+    }
     launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x);       // LN + masked_fill (Layers.py:28)
     ar.restore(mk);
 }
@@ -267,9 +295,17 @@ void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, ui
     for (auto& Lr : c->dec) fft_block_f32(c, s, ar, Lr, x, lens, B, T);
     conv32(c, s, c->mel_linear, x, 256, B, T, mel);                             // pads become bias (fastspeech2.py:242)
     float* h1 = ar.get<float>(rows * 512); float* h2 = ar.get<float>(rows * 512);
-    conv32(c, s, c->postnet[0], mel, 80, B, T, h1, ACT_TANH);
-    conv32(c, s, c->postnet[1], h1, 512, B, T, h2, ACT_TANH);
-    conv32(c, s, c->postnet[2], h2, 512, B, T, h1, ACT_TANH);
-    conv32(c, s, c->postnet[3], h1, 512, B, T, h2, ACT_TANH);
-    conv32(c, s, c->postnet[4], h2, 512, B, T, post, ACT_NONE, mel);            // + residual (fastspeech2.py:244)
+    if (f16_chain(c, c->postnet[0], c->postnet[1]) && f16_chain(c, c->postnet[3], c->postnet[4])) {
+        conv_to_planar16(c, s, c->postnet[0], mel, false, 80, B, T, (bf16*)h1, ACT_TANH);
+        conv_to_planar16(c, s, c->postnet[1], h1, true, 512, B, T, (bf16*)h2, ACT_TANH);
+        conv_to_planar16(c, s, c->postnet[2], h2, true, 512, B, T, (bf16*)h1, ACT_TANH);
+        conv_to_planar16(c, s, c->postnet[3], h1, true, 512, B, T, (bf16*)h2, ACT_TANH);
+        conv_from_planar16(c, s, c->postnet[4], (const bf16*)h2, B, T, post, ACT_NONE, mel);
+    } else {
+        conv32(c, s, c->postnet[0], mel, 80, B, T, h1, ACT_TANH);
+        conv32(c, s, c->postnet[1], h1, 512, B, T, h2, ACT_TANH);
+        conv32(c, s, c->postnet[2], h2, 512, B, T, h1, ACT_TANH);
+        conv32(c, s, c->postnet[3], h1, 512, B, T, h2, ACT_TANH);
+        conv32(c, s, c->postnet[4], h2, 512, B, T, post, ACT_NONE, mel);        // + residual (fastspeech2.py:244)
+    }
 }

@@ -9,7 +9,7 @@ import torch
 import masg_b200  # noqa
 from masg_b200 import _lib
 
-# name, B, T, Cin, Cout, k, dil, ups, slope, flags(2=bf16 acts,4=residual,1=split)
+# name, B, T, Cin, Cout, k, dil, ups, slope, flags(2=bf16 acts,4=residual,1=split,8=fp16 single pass)
 CASES = [
     ("hg s4 c1 k3 d1", 64, 153600, 32, 32, 3, 1, 0, 0.1, 2),
     ("hg s4 c2 k3 +res", 64, 153600, 32, 32, 3, 1, 0, 0.1, 6),
@@ -25,6 +25,11 @@ CASES = [
     ("fs2 dec w2 k1 (split)", 64, 600, 1024, 256, 1, 1, 0, 0.0, 1),
     ("fs2 dec qkv (split)", 64, 600, 256, 768, 1, 1, 0, 0.0, 1),
     ("postnet 512 k5 (split)", 64, 600, 512, 512, 5, 1, 0, 0.0, 1),
+    ("fs2 dec w1 k9 (fp16)", 64, 600, 256, 1024, 9, 1, 0, 0.0, 8),
+    ("fs2 dec w2 k1 (fp16)", 64, 600, 1024, 256, 1, 1, 0, 0.0, 8),
+    ("fs2 dec qkv (fp16)", 64, 600, 256, 768, 1, 1, 0, 0.0, 8),
+    ("fs2 dec fc (fp16)", 64, 600, 256, 256, 1, 1, 0, 0.0, 8),
+    ("postnet 512 k5 (fp16)", 64, 600, 512, 512, 5, 1, 0, 0.0, 8),
 ]
 
 def main():
