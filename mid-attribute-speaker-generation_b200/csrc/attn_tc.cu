@@ -15,13 +15,15 @@
 //     the transposed V block while warps 0-3 are busy with the softmax of the same key block.
 // Padded query rows are written as zeros (they are zeroed after the LayerNorm anyway, Layers.py:25).
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace {
 
 constexpr int AQ = 128;                  // queries per CTA = keys per block = head dim
 constexpr int AT_THREADS = 256;
 constexpr int TILE_BYTES = AQ * 128 * 2; // one bf16 operand tile [16][128][8]
-constexpr int AT_SMEM = 6 * TILE_BYTES + 1024;
+constexpr int AT_SMEM = 6 * TILE_BYTES + 1024;      // split-bf16: Q, K / V^T, P as hi + lo
+constexpr int AT_SMEM_F16 = 3 * TILE_BYTES + 1024;  // fp16 single pass: two CTAs per SM
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -38,23 +40,42 @@ __device__ __forceinline__ void split8(const float* f, uint4& hi, uint4& lo) {
     }
     hi = make_uint4(h[0], h[1], h[2], h[3]); lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
+__device__ __forceinline__ uint4 half8(const float* f) {
+    uint32_t h[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { __half2 t = __floats2half2_rn(f[2 * i], f[2 * i + 1]); h[i] = *reinterpret_cast<uint32_t*>(&t); }
+    return make_uint4(h[0], h[1], h[2], h[3]);
+}
+// operand conversion: split-bf16 (hi + lo tiles) or, F16, one fp16 tile (the decoder side: nothing downstream of it decides an integer)
+template <bool F16>
+__device__ __forceinline__ void put8(const float* f, uint8_t* hi, uint8_t* lo, size_t piece) {
+    if (F16) { *reinterpret_cast<uint4*>(hi + piece * 16) = half8(f); return; }
+    uint4 h, l;
+    split8(f, h, l);
+    *reinterpret_cast<uint4*>(hi + piece * 16) = h;
+    *reinterpret_cast<uint4*>(lo + piece * 16) = l;
+}
+template <bool F16>
 __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint32_t a_addr, uint32_t b_addr, uint32_t accumulate) {
     // SWIZZLE_NONE K-major descriptors: LBO = 2048 B (between 8-column groups), SBO = 128 B (between 8-row groups)
     const uint32_t hi = (128u >> 4) | (1u << 14);
     const uint32_t a_lo = ((2048u >> 4) << 16) | (a_addr >> 4), b_lo = ((2048u >> 4) << 16) | (b_addr >> 4);
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | (F16 ? 0u : ((1u << 7) | (1u << 10))) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
                  ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 // D (+)= (Ah + Al) x (Bh + Bl) without the lo x lo term, K = 128 (8 steps of 16)
+template <bool F16>
 __device__ __forceinline__ void mma_split_k128(uint32_t tmem_d, uint32_t ah, uint32_t al, uint32_t bh, uint32_t bl, bool first) {
 #pragma unroll
     for (int ks = 0; ks < 8; ++ks) {
         const uint32_t o = (uint32_t)ks * 4096u;
-        mma_bf16(tmem_d, ah + o, bh + o, (first && ks == 0) ? 0u : 1u);
-        mma_bf16(tmem_d, al + o, bh + o, 1u);
-        mma_bf16(tmem_d, ah + o, bl + o, 1u);
+        mma_bf16<F16>(tmem_d, ah + o, bh + o, (first && ks == 0) ? 0u : 1u);
+        if (!F16) {
+            mma_bf16<F16>(tmem_d, al + o, bh + o, 1u);
+            mma_bf16<F16>(tmem_d, ah + o, bl + o, 1u);
+        }
     }
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
@@ -80,6 +101,7 @@ __device__ __forceinline__ void commit_and_wait(uint32_t bar, uint32_t& phase, b
 
 // rows [row0, row0 + 128) x 128 columns of a row-major fp32 matrix (row stride 768) -> [16][128][8] bf16 hi / lo tiles;
 // rows >= row_limit are zero.  Lane = row: conflict-free 16-byte shared stores, 32-byte global sectors fully used.
+template <bool F16>
 __device__ __forceinline__ void load_rows_tile(const float* __restrict__ src, int row0, int row_limit, float scale,
                                                uint8_t* hi, uint8_t* lo, int tid, int nthreads) {
     for (int i = tid; i < 16 * AQ; i += nthreads) {
@@ -91,13 +113,11 @@ __device__ __forceinline__ void load_rows_tile(const float* __restrict__ src, in
             f[0] = a.x * scale; f[1] = a.y * scale; f[2] = a.z * scale; f[3] = a.w * scale;
             f[4] = b.x * scale; f[5] = b.y * scale; f[6] = b.z * scale; f[7] = b.w * scale;
         }
-        uint4 h, l;
-        split8(f, h, l);
-        *reinterpret_cast<uint4*>(hi + (size_t)i * 16) = h;
-        *reinterpret_cast<uint4*>(lo + (size_t)i * 16) = l;
+        put8<F16>(f, hi, lo, (size_t)i);
     }
 }
 // transposed: B operand of P V is V^T, [16 key groups][128 value columns][8 keys]; thread = value column
+template <bool F16>
 __device__ __forceinline__ void load_vt_tile(const float* __restrict__ src, int key0, int key_limit, uint8_t* hi, uint8_t* lo, int n) {
 #pragma unroll 2
     for (int kg = 0; kg < 16; ++kg) {
@@ -107,19 +127,18 @@ __device__ __forceinline__ void load_vt_tile(const float* __restrict__ src, int 
             const int key = key0 + kg * 8 + i;
             f[i] = key < key_limit ? __ldg(src + (size_t)key * 768 + n) : 0.f;
         }
-        uint4 h, l;
-        split8(f, h, l);
-        *reinterpret_cast<uint4*>(hi + (size_t)(kg * AQ + n) * 16) = h;
-        *reinterpret_cast<uint4*>(lo + (size_t)(kg * AQ + n) * 16) = l;
+        put8<F16>(f, hi, lo, (size_t)(kg * AQ + n));
     }
 }
 
-__global__ void __launch_bounds__(AT_THREADS, 1)
+template <bool F16>
+__global__ void __launch_bounds__(AT_THREADS, F16 ? 2 : 1)
 k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, int S, float* __restrict__ out) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* Qh = smem + 1024; uint8_t* Ql = Qh + TILE_BYTES;
-    uint8_t* Kh = Ql + TILE_BYTES; uint8_t* Kl = Kh + TILE_BYTES;          // K block in pass 1/2, then V^T block in pass 2
-    uint8_t* Ph = Kl + TILE_BYTES; uint8_t* Pl = Ph + TILE_BYTES;
+    constexpr int NP = F16 ? 1 : 2;                                        // tiles per operand (hi [+ lo])
+    uint8_t* Qh = smem + 1024; uint8_t* Ql = Qh + TILE_BYTES;              // (the lo pointers are never dereferenced when F16)
+    uint8_t* Kh = Qh + NP * TILE_BYTES; uint8_t* Kl = Kh + TILE_BYTES;     // K block in pass 1/2, then V^T block in pass 2
+    uint8_t* Ph = Kh + NP * TILE_BYTES; uint8_t* Pl = Ph + TILE_BYTES;
     const uint32_t bar = smem_u32(smem);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + 64);
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * AQ;
@@ -142,7 +161,7 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32((const void*)tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    load_rows_tile(base + h * 128, q0, S, 1.0f / 11.313708498984761f, Qh, Ql, tid, AT_THREADS);     // q / np.power(128, 0.5)
+    load_rows_tile<F16>(base + h * 128, q0, S, 1.0f / 11.313708498984761f, Qh, Ql, tid, AT_THREADS);     // q / np.power(128, 0.5)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -157,12 +176,12 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
 
     // ---------------- pass 1: row maxima and softmax denominators ----------------
     for (int kb = 0; kb < nkb; ++kb) {
-        load_rows_tile(base + 256 + h * 128, kb * AQ, len, 1.f, Kh, Kl, tid, AT_THREADS);
+        load_rows_tile<F16>(base + 256 + h * 128, kb * AQ, len, 1.f, Kh, Kl, tid, AT_THREADS);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            mma_split_k128(tS, qh, ql, kh, kl, true);
+            mma_split_k128<F16>(tS, qh, ql, kh, kl, true);
         }
         commit_and_wait(bar, phase, tid == 0);
         if (warp < 4) {
@@ -193,12 +212,12 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
     // ---------------- pass 2: P = softmax rows (normalised), O += P V ----------------
     for (int kb = 0; kb < nkb; ++kb) {
         if (kb > 0) commit_and_wait(bar, phase, false);                     // P V of the previous block has read Kh/Kl and Ph/Pl
-        load_rows_tile(base + 256 + h * 128, kb * AQ, len, 1.f, Kh, Kl, tid, AT_THREADS);
+        load_rows_tile<F16>(base + 256 + h * 128, kb * AQ, len, 1.f, Kh, Kl, tid, AT_THREADS);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            mma_split_k128(tS, qh, ql, kh, kl, true);
+            mma_split_k128<F16>(tS, qh, ql, kh, kl, true);
         }
         commit_and_wait(bar, phase, tid == 0);
         if (warp < 4) {
@@ -209,23 +228,18 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
                 tmem_ld16(tS + trow + (uint32_t)c, v);
 #pragma unroll
                 for (int i = 0; i < 16; ++i) v[i] = (c + i < nvalid) ? __expf(v[i] - m) * inv_l : 0.f;
-                uint4 hh, ll;
-                split8(v, hh, ll);
-                *reinterpret_cast<uint4*>(Ph + (size_t)((c >> 3) * AQ + r) * 16) = hh;
-                *reinterpret_cast<uint4*>(Pl + (size_t)((c >> 3) * AQ + r) * 16) = ll;
-                split8(v + 8, hh, ll);
-                *reinterpret_cast<uint4*>(Ph + (size_t)(((c >> 3) + 1) * AQ + r) * 16) = hh;
-                *reinterpret_cast<uint4*>(Pl + (size_t)(((c >> 3) + 1) * AQ + r) * 16) = ll;
+                put8<F16>(v, Ph, Pl, (size_t)((c >> 3) * AQ + r));
+                put8<F16>(v + 8, Ph, Pl, (size_t)(((c >> 3) + 1) * AQ + r));
             }
         } else {
-            load_vt_tile(base + 512 + h * 128, kb * AQ, len, Kh, Kl, tid - 128);
+            load_vt_tile<F16>(base + 512 + h * 128, kb * AQ, len, Kh, Kl, tid - 128);
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            mma_split_k128(tO, ph, pl, kh, kl, kb == 0);
+            mma_split_k128<F16>(tO, ph, pl, kh, kl, kb == 0);
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
         }
     }
@@ -251,11 +265,16 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
 
 }  // namespace
 
-void launch_attention_tc(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out) {
+void launch_attention_tc(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out, int f16) {
     dim3 grid((S + AQ - 1) / AQ, 2, B);
     static bool attr_set = false;
-    if (!attr_set) { CUDA_OK(cudaFuncSetAttribute(k_attention_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM)); attr_set = true; }
-    k_attention_tc<<<grid, AT_THREADS, AT_SMEM, s>>>(qkv, lens, S, out);
+    if (!attr_set) {
+        CUDA_OK(cudaFuncSetAttribute(k_attention_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        CUDA_OK(cudaFuncSetAttribute(k_attention_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM_F16));
+        attr_set = true;
+    }
+    if (f16) k_attention_tc<true><<<grid, AT_THREADS, AT_SMEM_F16, s>>>(qkv, lens, S, out);
+    else k_attention_tc<false><<<grid, AT_THREADS, AT_SMEM, s>>>(qkv, lens, S, out);
     CUDA_OK(cudaGetLastError());
     c->launches++;
 }

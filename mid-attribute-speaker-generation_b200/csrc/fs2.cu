@@ -199,7 +199,7 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     float* att = ar.get<float>(rows * 256);
     float* y = ar.get<float>(rows * 256);
     conv32(c, s, L.qkv, x, 256, B, S, qkv);
-    if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att);
+    if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
     else launch_attention_f32(c, s, qkv, lens, B, S, att);
     conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                         // fc(out) + residual
     launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x);        // LN + masked_fill (Layers.py:25)
