@@ -47,7 +47,7 @@ def _peaks():
 
 
 def _ncu_traffic():
-    """DRAM bytes (read + written) per k_conv_tc launch, from the newest committed `ncu --set full` capture of one C3 step
+    """DRAM bytes (read + written) per k_conv_tc / k_respair_tc launch, from the newest committed `ncu --set full` capture of one C3 step
     (profiles/r*_ncu_full_conv_tc_*.csv, written by tools/ncu_summary.py).  A profiler number, reported beside the live ones."""
     import csv, glob
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv_tc_*.csv")))
@@ -383,12 +383,12 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "clocks": clk,
-        "roofline": {"bound": "tensor", "kernel": "k_conv_tc (tcgen05 implicit-GEMM conv1d/linear/convT)", "achieved": ach, "peak": pk["tflops"],
+        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc (tcgen05 implicit-GEMM conv1d / linear / convT and the fused ResBlock pairs)", "achieved": ach, "peak": pk["tflops"],
                      "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
                      "traffic_source": traffic_src, "peak_source": pk["src"],
                      "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": step_ms_plain,
                      "share_of_step": k_ms / step_ms_plain if step_ms_plain else None,
-                     "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per launch"},
+                     "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per conv (both convs of a fused pair)"},
         "cpu_baseline": cpu,
         "latency_p50_ms": {"value": lat[len(lat) // 2], "config": "C2: batch 1, 50 phonemes, host ids -> int16 audio on host (masg_synthesize_host), 20 runs"},
     }

@@ -129,7 +129,7 @@ void launch_add_rowvec(masg_ctx* c, cudaStream_t s, float* x, const float* v, in
 void launch_add_pos(masg_ctx* c, cudaStream_t s, float* x, const float* pos, int B, int T, int C);
 // y = LN(x (+res)) * g + b ; rows with t >= lens[b] are zeroed when lens != null
 void launch_layernorm(masg_ctx* c, cudaStream_t s, const float* x, const float* res, const float* g, const float* b,
-                      const int64_t* lens, int B, int T, float* y);
+                      const int64_t* lens, int B, int T, float* y, bf16* y16_planar = nullptr);   // + planar fp16 copy [B][32][T][8]
 // out[b,t] = (t < lens[b]) ? dot(x[b,t,:], w) + bias : 0
 void launch_rowdot_mask(masg_ctx* c, cudaStream_t s, const float* x, const float* w, float bias, const int64_t* lens,
                         int B, int T, float scale, float* out);

@@ -166,6 +166,11 @@ static void conv32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* 
     ConvIO io;
     io.X = X; io.x_ld = x_ld; io.x_bs = (long)T * x_ld; io.Tin = T;
     io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
+    if (d.taps == 1 && c->precision == MASG_PREC_BF16) {
+        // a k = 1 layer is a plain GEMM over the B*T rows: no utterance boundaries, so no partly filled last tile per
+        // utterance (T = 600 fills 2.3 tiles of 256 rows)
+        io.B = 1; io.Q = B * T; io.Tin = B * T; io.x_bs = 0; io.y_bs = 0; io.y_limit = (long)B * T * d.N;
+    }
     launch_conv(c, s, d, io);
 }
 
@@ -186,34 +191,45 @@ static void conv_from_planar16(masg_ctx* c, cudaStream_t s, const ConvDesc& d, c
     io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
     launch_conv(c, s, d, io);
 }
+static bool ln_planar(int bit) {                 // MASG_LN_PLANAR: 1 = w_1 input, 2 = QKV input as planar fp16 from the LayerNorm
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("MASG_LN_PLANAR"); on = e ? atoi(e) : 3; }
+    return (on & bit) != 0;
+}
 static bool f16_chain(const masg_ctx* c, const ConvDesc& a, const ConvDesc& b) {
     static int on = -1;
     if (on < 0) { const char* e = getenv("MASG_F16_PLANAR"); on = e ? atoi(e) : 1; }
     return on && c->precision == MASG_PREC_BF16 && a.f16 && b.f16 && (a.N & (a.N - 1)) == 0 && a.N >= 64;
 }
 
-static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S) {
+// xp_in: planar fp16 copy of x from the previous block's LayerNorm (nullable); xp_out: where this block's last LayerNorm
+// leaves the same for the next block (nullable).  Decoder side in MASG_PREC_BF16 only (fp16 layers).
+static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S,
+                          const bf16* xp_in = nullptr, bf16* xp_out = nullptr) {
     // in place on x: every consumer of the old x has been enqueued before the LayerNorm overwrites it
     size_t rows = (size_t)B * S, mk = ar.mark();
     float* qkv = ar.get<float>(rows * 768);
     float* att = ar.get<float>(rows * 256);
     float* y = ar.get<float>(rows * 256);
-    conv32(c, s, L.qkv, x, 256, B, S, qkv);
+    if (xp_in) conv_from_planar16(c, s, L.qkv, xp_in, B, S, qkv);
+    else conv32(c, s, L.qkv, x, 256, B, S, qkv);
     if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
     else launch_attention_f32(c, s, qkv, lens, B, S, att);
     conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                         // fc(out) + residual
-    launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x);        // LN + masked_fill (Layers.py:25)
-    ar.restore(mk);
+    const bool chain = f16_chain(c, L.w1, L.w2);
+    bf16* xp1 = (chain && ln_planar(1)) ? ar.get<bf16>(rows * 256) : nullptr;   // LN output as w_1's operand
+    launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x, xp1);   // LN + masked_fill (Layers.py:25)
     float* h = ar.get<float>(rows * 1024);
     float* y2 = ar.get<float>(rows * 256);
-    if (f16_chain(c, L.w1, L.w2)) {                                             // h only feeds w_2: planar fp16, never fp32
-        conv_to_planar16(c, s, L.w1, x, false, 256, B, S, (bf16*)h, ACT_RELU);
+    if (chain) {                                                                // h only feeds w_2: planar fp16, never fp32
+        if (xp1) conv_to_planar16(c, s, L.w1, xp1, true, 256, B, S, (bf16*)h, ACT_RELU);
+        else conv_to_planar16(c, s, L.w1, x, false, 256, B, S, (bf16*)h, ACT_RELU);
         conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
     } else {
         conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
         conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
     }
-    launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x);       // LN + masked_fill (Layers.py:28)
+    launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x, xp_out);   // LN + masked_fill (Layers.py:28)
     ar.restore(mk);
 }
 
@@ -292,7 +308,13 @@ void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, ui
     float* x = c->tap_dec;
     CUDA_OK(cudaMemcpyAsync(x, c->tap_lr, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
     launch_add_pos(c, s, x, pos, B, T, 256);
-    for (auto& Lr : c->dec) fft_block_f32(c, s, ar, Lr, x, lens, B, T);
+    {
+        // between decoder blocks the LayerNorm output also travels as planar fp16 (the next block's QKV operand)
+        const bool pl = c->precision == MASG_PREC_BF16 && !c->dec.empty() && c->dec[0].qkv.f16 && ln_planar(2);
+        bf16* xp[2] = {pl ? ar.get<bf16>((size_t)B * T * 256) : nullptr, pl ? ar.get<bf16>((size_t)B * T * 256) : nullptr};
+        for (size_t i = 0; i < c->dec.size(); ++i)
+            fft_block_f32(c, s, ar, c->dec[i], x, lens, B, T, (pl && i > 0) ? xp[(i - 1) & 1] : nullptr, (pl && i + 1 < c->dec.size()) ? xp[i & 1] : nullptr);
+    }
     conv32(c, s, c->mel_linear, x, 256, B, T, mel);                             // pads become bias (fastspeech2.py:242)
     float* h1 = ar.get<float>(rows * 512); float* h2 = ar.get<float>(rows * 512);
     if (f16_chain(c, c->postnet[0], c->postnet[1]) && f16_chain(c, c->postnet[3], c->postnet[4])) {

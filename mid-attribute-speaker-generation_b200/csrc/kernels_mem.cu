@@ -3,6 +3,7 @@
 // weight repacking.  All are coalesced 128-bit accesses with warp-shuffle reductions; one warp owns
 // one 256-channel row (2 x float4 per lane).
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include <curand_kernel.h>
 
 #define FULL 0xffffffffu
@@ -92,13 +93,20 @@ void launch_add2(masg_ctx* c, cudaStream_t s, const float* a, const float* b, fl
 // ------------------------------------------------------------------------------------------------
 __global__ void k_layernorm256(const float4* __restrict__ x, const float4* __restrict__ res,
                                const float4* __restrict__ g, const float4* __restrict__ b,
-                               const int64_t* __restrict__ lens, long rows, int T, float4* __restrict__ y) {
+                               const int64_t* __restrict__ lens, long rows, int T, float4* __restrict__ y,
+                               uint2* __restrict__ y16) {
     long row = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     int lane = threadIdx.x & 31;
     if (row >= rows) return;
+    // optional second output: planar fp16 [B][32][T][8] (the tcgen05 operand layout of the next fp16 layer).  Lane l holds
+    // channels 4l..4l+3 and 128+4l..: half an 8-channel group each, written as 8-byte pieces
+    const long bq = row / T, tq = row % T;
+    uint2* p16a = y16 ? y16 + (((bq * 32 + (lane >> 1)) * T + tq) * 2 + (lane & 1)) : nullptr;
+    uint2* p16b = y16 ? y16 + (((bq * 32 + 16 + (lane >> 1)) * T + tq) * 2 + (lane & 1)) : nullptr;
     if (lens && (row % T) >= lens[row / T]) {
         float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         y[row * 64 + lane] = z; y[row * 64 + lane + 32] = z;
+        if (y16) { *p16a = make_uint2(0u, 0u); *p16b = make_uint2(0u, 0u); }
         return;
     }
     float4 v0 = x[row * 64 + lane], v1 = x[row * 64 + lane + 32];
@@ -118,12 +126,18 @@ __global__ void k_layernorm256(const float4* __restrict__ x, const float4* __res
     o1.x = (v1.x - mean) * rstd * g1.x + b1.x; o1.y = (v1.y - mean) * rstd * g1.y + b1.y;
     o1.z = (v1.z - mean) * rstd * g1.z + b1.z; o1.w = (v1.w - mean) * rstd * g1.w + b1.w;
     y[row * 64 + lane] = o0; y[row * 64 + lane + 32] = o1;
+    if (y16) {
+        __half2 h0 = __floats2half2_rn(o0.x, o0.y), h1 = __floats2half2_rn(o0.z, o0.w);
+        __half2 h2 = __floats2half2_rn(o1.x, o1.y), h3 = __floats2half2_rn(o1.z, o1.w);
+        *p16a = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+        *p16b = make_uint2(*reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
+    }
 }
 void launch_layernorm(masg_ctx* c, cudaStream_t s, const float* x, const float* res, const float* g, const float* b,
-                      const int64_t* lens, int B, int T, float* y) {
+                      const int64_t* lens, int B, int T, float* y, bf16* y16_planar) {
     long rows = (long)B * T;
     k_layernorm256<<<cdiv(rows, 8), 256, 0, s>>>((const float4*)x, (const float4*)res, (const float4*)g,
-                                                 (const float4*)b, lens, rows, T, (float4*)y);
+                                                 (const float4*)b, lens, rows, T, (float4*)y, (uint2*)y16_planar);
     c->launches++;
 }
 

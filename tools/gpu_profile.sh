@@ -1,7 +1,7 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, a plain bench run, then the ncu passes of the same command
-# (launch list; full-set capture of every k_conv_tc launch of one step exported as CSV; a 6-launch
-# capture with source for the HiFi-GAN stage-2 convs).  Usage: gpurun --timeout 1500 -- tools/gpu_profile.sh [tag]
+# (launch list; full-set capture of every k_conv_tc / k_respair_tc launch of one step exported as CSV; a 4-launch
+# capture with source of the fused pair kernel).  Usage: gpurun --timeout 1500 -- tools/gpu_profile.sh [tag]
 tag=${1:-cur}
 out=gpurun_out
 mkdir -p $out
@@ -14,11 +14,11 @@ $CMD > $out/plain_$tag.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 4000 --csv --log-file $out/launches_$tag.csv $CMD > $out/ncu1_$tag.log 2>&1
 echo "ncu launches exit $?"
 $CMD > $out/plain_$tag.log 2>&1 &&
-ncu --set full --clock-control none --profile-from-start off -k regex:k_conv_tc -c 129 -o $out/prof_all_$tag -f $CMD > $out/ncu2_$tag.log 2>&1
+ncu --set full --clock-control none --profile-from-start off -k 'regex:k_conv_tc|k_respair_tc' -c 130 -o $out/prof_all_$tag -f $CMD > $out/ncu2_$tag.log 2>&1
 echo "ncu full exit $?"
 ncu -i $out/prof_all_$tag.ncu-rep --page raw --csv > $out/prof_all_$tag.csv 2>/dev/null
 ls -la $out/prof_all_$tag.ncu-rep; rm -f $out/prof_all_$tag.ncu-rep
 $CMD > $out/plain_$tag.log 2>&1 &&
-ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:k_conv_tc -s 73 -c 6 -o $out/prof_src_$tag -f $CMD > $out/ncu3_$tag.log 2>&1
+ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:k_respair_tc -s 9 -c 4 -o $out/prof_src_$tag -f $CMD > $out/ncu3_$tag.log 2>&1
 echo "ncu src exit $?"
 ls -la $out
