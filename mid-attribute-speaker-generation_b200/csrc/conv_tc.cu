@@ -822,11 +822,11 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.G = std::max(1, W_STAGE_BYTES / a.blob_bytes);
     {
         static int big = -1;
-        if (big < 0) { const char* e = getenv("MASG_TC_WSTAGE32"); big = e ? atoi(e) : 20; }    // minimum blobs per tile (0 = never)
+        if (big < 0) { const char* e = getenv("MASG_TC_WSTAGE32"); big = e ? atoi(e) : 6; }     // minimum blobs per tile (huge = never)
         const int g2 = std::max(1, 2 * W_STAGE_BYTES / a.blob_bytes);
         const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + 3 * (size_t)g2 * a.blob_bytes;
-        // measured at the C3 shapes: a gain for the long weight streams (k = 11: 22 / 44 blobs per tile, +8 % / +13 %), a loss for
-        // the short ones (k = 3, 7 and the upsamplers), where the shallower ring shows at every tile start
+        // measured at the C3 shapes (with the lean planar epilogue): +6 % at k = 7, +8 % / +13 % at k = 11 (stage 2 / stage 1),
+        // neutral for k = 3 and the upsamplers
         if (big && !d.split && a.blob_bytes == W_STAGE_BYTES && a.n_blobs >= big && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
     }
     a.stage_bytes = a.G * a.blob_bytes;

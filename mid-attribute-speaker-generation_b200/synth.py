@@ -96,6 +96,43 @@ def sample_speakers(fs2, n_sampled, n_interp, seed=0):
 
 
 # ------------------------------------------------------------------------------------------------
+# on-disk speaker artefacts, interchangeable with the reference's
+# ------------------------------------------------------------------------------------------------
+def speaker_names(gender, language, n, start=1):
+    """The reference's naming of generated speakers: '<gender>_<language>gen<NNN>' (examples_gen.py:267,
+    examples_gen_distri.py:214)."""
+    return ["%s_%sgen%03d" % (gender, language, i) for i in range(start, start + n)]
+
+
+def save_speaker_embeddings(out_dir, names, embs):
+    """One `<name>.npy` per speaker holding a float32 [1, 256] array — exactly what `np.save(output_path / speaker_name,
+    speaker_emb)` leaves behind (examples_gen.py:272, examples_gen_distri.py:218), written from one batched [N, 256] tensor."""
+    import os
+    embs = embs.detach().to("cpu", torch.float32).numpy() if torch.is_tensor(embs) else np.asarray(embs, dtype=np.float32)
+    assert embs.ndim == 2 and embs.shape[0] == len(names), "embs must be [N, D] with one name per row"
+    os.makedirs(out_dir, exist_ok=True)
+    paths = []
+    for name, e in zip(names, embs):
+        path = os.path.join(str(out_dir), name + ".npy")
+        np.save(path, e[None, :].copy())
+        paths.append(path)
+    return paths
+
+
+def load_speaker_embeddings(paths, device=None):
+    """Stack reference-format `.npy` speaker embeddings ([1, D] or [D] each) into one [N, D] float32 tensor, ready for
+    `synthesize_from_speaker_emb(..., speaker_emb=...)` (the reference feeds them one by one, synthesize.py:105-131)."""
+    rows = []
+    for p in paths:
+        a = np.load(str(p)).astype(np.float32)
+        assert a.ndim in (1, 2) and (a.ndim == 1 or a.shape[0] == 1), "%s: expected a [1, D] or [D] array, got %s" % (p, a.shape)
+        rows.append(a.reshape(-1))
+    assert rows and all(r.shape == rows[0].shape for r in rows), "speaker embeddings differ in size"
+    t = torch.from_numpy(np.stack(rows, 0))
+    return t.to(device) if device is not None else t
+
+
+# ------------------------------------------------------------------------------------------------
 # batch scheduler (host logic, CPU-testable): length-bucketed batches, LPT assignment to ranks
 # ------------------------------------------------------------------------------------------------
 def utterance_cost(L, frames_per_phoneme=3.0):

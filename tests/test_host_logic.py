@@ -139,3 +139,21 @@ def test_two_rank_sharding_gloo():
     lens = syn.c4_lengths(256)
     for rank, frames, count, tmax in res:
         assert frames == float(lens.sum() * 3) and count == 256.0 and tmax == 2.0
+
+
+def test_speaker_embedding_artefacts_round_trip(tmp_path):
+    """Reference on-disk format of generated speakers: one float32 [1, 256] .npy per speaker (examples_gen.py:272)."""
+    import numpy as np
+    import torch
+    from masg_b200 import synth
+    names = synth.speaker_names("F", "ja", 3)
+    assert names == ["F_jagen001", "F_jagen002", "F_jagen003"]
+    g = torch.Generator().manual_seed(3)
+    embs = torch.randn(3, 256, generator=g)
+    paths = synth.save_speaker_embeddings(tmp_path / "speakers_wsample", names, embs)
+    one = np.load(paths[1])
+    assert one.shape == (1, 256) and one.dtype == np.float32                 # what the reference's loaders expect
+    back = synth.load_speaker_embeddings(paths)
+    assert back.shape == (3, 256) and torch.equal(back, embs)
+    np.save(tmp_path / "flat.npy", embs[0].numpy())                            # a [256] array is accepted too
+    assert torch.equal(synth.load_speaker_embeddings([tmp_path / "flat.npy"])[0], embs[0])
