@@ -457,19 +457,30 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
     int tid = threadIdx.x;
     if (tid < 224) ws[tid] = w[tid];
     if (XBF) {
-        // planar bf16 input [B][4][S][8]: one 16-byte piece = 8 channels of one sample
-        for (int i = tid; i < 262 * 4; i += 256) {
-            int g = i / 262, r = i % 262;
-            long srow = s0 + r - 3;
-            float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (srow >= 0 && srow < S) {
-                uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(xv) + (((long)b * 4 + g) * S + srow) * 8);
-                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+        // planar bf16 input [B][4][S][8]: one 16-byte piece = 8 channels of one sample.  All of a thread's loads are issued
+        // before the first is used (5 x 16 bytes in flight per thread instead of 1)
+        constexpr int NP = (262 * 4 + 255) / 256;
+        uint4 u[NP];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { f[2 * k] = __uint_as_float(w4[k] << 16); f[2 * k + 1] = __uint_as_float(w4[k] & 0xffff0000u); }
-            }
+        for (int k = 0; k < NP; ++k) {
+            const int i = tid + k * 256;
+            const int g = i / 262, r = i % 262;
+            const long srow = s0 + r - 3;
+            u[k] = make_uint4(0u, 0u, 0u, 0u);
+            if (i < 262 * 4 && srow >= 0 && srow < S)
+                u[k] = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(xv) + (((long)b * 4 + g) * S + srow) * 8);
+        }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = f[k] > 0.f ? f[k] : f[k] * slope;
+        for (int k = 0; k < NP; ++k) {
+            const int i = tid + k * 256;
+            if (i >= 262 * 4) break;
+            const int g = i / 262, r = i % 262;
+            const uint32_t w4[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+            float f[8];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { f[2 * q] = __uint_as_float(w4[q] << 16); f[2 * q + 1] = __uint_as_float(w4[q] & 0xffff0000u); }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) f[q] = f[q] > 0.f ? f[q] : f[q] * slope;
             float4* dst = reinterpret_cast<float4*>(&xs[r * XS + g * 8]);
             dst[0] = make_float4(f[0], f[1], f[2], f[3]); dst[1] = make_float4(f[4], f[5], f[6], f[7]);
         }
