@@ -722,7 +722,6 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
     int NT = 0;
     const int cands[4] = {128, 80, 64, 32};
     for (int i = 0; i < 4 && !NT; ++i) if (d.N % cands[i] == 0) NT = cands[i];
-    MASG_CHECK(NT != 0, "conv_tc: N=%d is not a multiple of 32/64/80/128 (unsupported configuration)", d.N);
     int KW = (d.Cin % 64 == 0) ? 64 : (d.Cin % 32 == 0 ? 32 : 16);
     while (split && NT * KW * 4 > W_STAGE_BYTES && KW > 16) KW /= 2;
     MASG_CHECK(d.Cin % KW == 0, "conv_tc: Cin=%d must be a multiple of 16", d.Cin);

@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
             mbar_wait_relaxed(bars.x_raw(slot), u & 1);
             RP_TRACE(trace && tid == 0, 1, it, 0);
             uint4* p = reinterpret_cast<uint4*>(Xs + (size_t)slot * x_bytes);
-            for (int i = tid; i < pieces; i += RP_WORK_THREADS) {
+            for (int i = tid; i < pieces && !(a.dbg & 128); i += RP_WORK_THREADS) {   // dbg 128: what-if, no leaky-relu pass
                 uint4 v = p[i];
                 v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl); v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
                 p[i] = v;
