@@ -30,6 +30,7 @@ CASES = [
     ("fs2 dec qkv (fp16)", 64, 600, 256, 768, 1, 1, 0, 0.0, 8),
     ("fs2 dec fc (fp16)", 64, 600, 256, 256, 1, 1, 0, 0.0, 8),
     ("postnet 512 k5 (fp16)", 64, 600, 512, 512, 5, 1, 0, 0.0, 8),
+    ("hg s2 c2 k3 +res", 64, 38400, 128, 128, 3, 1, 0, 0.1, 6),
 ]
 
 def main():
