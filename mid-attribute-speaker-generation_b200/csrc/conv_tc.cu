@@ -73,6 +73,7 @@ struct TcArgs {
     int y_planar, y_T, up, up_pad, cout_shift;         // planar bf16 output [B][Cout/8][y_T][8]; t = q*up + n/Cout - up_pad
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale; float post_slope;
+    int w_resident;                                    // the whole weight set is one stage, loaded once per CTA
     int w_stages;                                      // weight ring depth (3 with 32 KB stages, else 4 with 16 KB stages)
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
@@ -506,6 +507,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
                 const int nt = tile % a.n_ntiles;
                 const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
+                if (a.w_resident && tile != (int)blockIdx.x) {       // resident weights: only the hand-shake, no copy
+                    mbar_wait_relaxed(bars.w_empty(0), phase ^ 1);
+                    mbar_arrive(bars.w_full(0));
+                    phase ^= 1;
+                    continue;
+                }
                 for (int st = 0; st < n_stages; ++st) {
                     STAT_WAIT(a.dbg & 16, 7, mbar_wait_relaxed(bars.w_empty(slot), phase ^ 1));
                     const int nb = min(a.G, a.n_blobs - st * a.G);
@@ -827,6 +834,18 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
         // measured at the C3 shapes (with the lean planar epilogue): +6 % at k = 7, +8 % / +13 % at k = 11 (stage 2 / stage 1),
         // neutral for k = 3 and the upsamplers
         if (big && !d.split && a.blob_bytes == W_STAGE_BYTES && a.n_blobs >= big && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
+    }
+    {
+        // small weight sets (C = 64 k = 11: 90 KB; C = 128 k = 3: 96 KB) stay resident: one stage holding every blob, loaded by
+        // the first tile of the CTA; later tiles only exchange the barrier
+        static int res = -1;
+        if (res < 0) { const char* e = getenv("MASG_TC_WRESIDENT"); res = e ? atoi(e) : 1; }
+        const size_t wbytes = (size_t)a.n_blobs * a.blob_bytes;
+        const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + wbytes;
+        a.w_resident = 0;
+        if (res && tma_in && !d.split && ntiles_n == 1 && wbytes <= 100 * 1024 && need <= (size_t)MAX_SMEM) {
+            a.w_resident = 1; a.G = a.n_blobs; a.w_stages = 1;
+        }
     }
     a.stage_bytes = a.G * a.blob_bytes;
     a.n_blobs = (d.Cin / d.KW) * d.taps;
