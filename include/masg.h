@@ -97,6 +97,11 @@ int masg_bucketize_embed_add(masg_ctx* ctx, void* stream, const float* v, const 
  * MASG_PREC_BF16: tcgen05 kernel (bf16 hi+lo operands, scores and output in TMEM); MASG_PREC_FP32: fp32 SIMT kernel. */
 int masg_attention(masg_ctx* ctx, void* stream, const float* qkv, const int64_t* lens, int B, int S, float* out);
 
+/* The same attention core as the decoder FFT blocks run it in MASG_PREC_BF16 (fp16 operands, planar hand-overs):
+ * qkv16 fp16 planar [B, 768/8, S, 8] (channel c of row t at ((c/8)*S + t)*8 + c%8; channels = q | k | v, 2 heads x 128),
+ * out16 fp16 planar [B, 256/8, S, 8].  Masking as masg_attention.  MASG_PREC_BF16 contexts only. */
+int masg_attention_planar(masg_ctx* ctx, void* stream, const void* qkv16, const int64_t* lens, int B, int S, void* out16);
+
 /* hifigan.Generator.forward (hifigan/models.py:149-165): mel fp32 [B, 80, T] → wav fp32 [B, 1, 256 T].
  * wav_i16 (nullable): int16 [B, 256 T] = C-cast of wav*32768 as utils/model.py:82-85 (wrap, not saturate).
  * mel_is_channels_last != 0: mel is [B, T, 80] (postnet output layout; skips the transpose that

@@ -42,6 +42,7 @@ SIGNATURES = {
     "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, c_int, P,
                             ctypes.POINTER(c_float)]),
     "masg_attention": (c_int, [P, P, P, P, c_int, c_int, P]),
+    "masg_attention_planar": (c_int, [P, P, P, P, c_int, c_int, P]),
     "masg_respair": (c_int, [P, P, P, P, c_int, c_int, c_int, P, P, P, P, c_int, c_int, c_float, c_float, c_int, P, P]),
     "masg_profile": (c_int, [P, c_int]),
     "masg_profile_read": (c_int, [P, P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64)]),

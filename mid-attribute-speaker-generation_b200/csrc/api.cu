@@ -425,6 +425,14 @@ int masg_attention(masg_ctx* c, void* stream, const float* qkv, const int64_t* l
     API_END(c)
 }
 
+int masg_attention_planar(masg_ctx* c, void* stream, const void* qkv16, const int64_t* lens, int B, int S, void* out16) {
+    API_BEGIN(c)
+    MASG_CHECK(qkv16 && lens && out16 && B > 0 && S > 0, "bad argument");
+    MASG_CHECK(c->precision == MASG_PREC_BF16, "masg_attention_planar is the tcgen05 fp16 kernel: MASG_PREC_BF16 contexts only");
+    launch_attention_f16p(c, (cudaStream_t)stream, qkv16, lens, B, S, out16);
+    API_END(c)
+}
+
 int masg_profile(masg_ctx* c, int enable) {
     API_BEGIN(c)
     c->profiling = enable != 0;

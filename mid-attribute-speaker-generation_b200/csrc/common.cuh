@@ -145,6 +145,8 @@ void launch_attention_f32(masg_ctx* c, cudaStream_t s, const float* qkv, const i
 // tcgen05 masked attention (attn_tc.cu), MASG_PREC_BF16
 // f16: fp16 single-pass operands, two CTAs per SM (decoder side); else split-bf16 hi + lo, 3 MMAs per product
 void launch_attention_tc(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out, int f16 = 0);
+// planar fp16 in ([B][96][S][8]) and out ([B][32][S][8]): attn_f16p.cu
+void launch_attention_f16p(masg_ctx* c, cudaStream_t s, const void* qkv, const int64_t* lens, int B, int S, void* out);
 void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int B, int C, int T, float* out_btc);
 void launch_conv_post(masg_ctx* c, cudaStream_t s, const void* x, int x_bf16, const float* w, float bias, int B, long S,
                       float in_slope, float* wav, int16_t* wav16);

@@ -861,7 +861,9 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.y_planar = io.y_planar;
     if (io.y_planar) {
         MASG_CHECK(io.Y16 != nullptr && io.Y == nullptr && io.y_T > 0, "conv_tc: planar output is bf16 only and needs y_T");
-        MASG_CHECK((a.bias_mod & (a.bias_mod - 1)) == 0 && a.bias_mod >= 8, "conv_tc: planar output needs a power-of-two channel count (%d)", a.bias_mod);
+        // transposed convs split a column into (phase, channel) with a shift; plain convs only need whole 8-channel groups
+        MASG_CHECK(a.bias_mod >= 8 && (d.up > 1 ? (a.bias_mod & (a.bias_mod - 1)) == 0 : a.bias_mod % 16 == 0),
+                   "conv_tc: planar output needs a power-of-two (transposed conv) / multiple-of-16 channel count (%d)", a.bias_mod);
         MASG_CHECK((io.R1 == nullptr && io.R2 == nullptr) || io.r_bf16, "conv_tc: planar residuals must be bf16");
         int sh = 0; while ((1 << sh) < a.bias_mod) ++sh;
         a.cout_shift = sh; a.y_T = io.y_T; a.up = d.up > 0 ? d.up : 1; a.up_pad = d.up_pad;

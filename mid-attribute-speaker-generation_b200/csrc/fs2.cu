@@ -202,6 +202,12 @@ static bool f16_chain(const masg_ctx* c, const ConvDesc& a, const ConvDesc& b) {
     return on && c->precision == MASG_PREC_BF16 && a.f16 && b.f16 && (a.N & (a.N - 1)) == 0 && a.N >= 64;
 }
 
+static bool attn_planar(const masg_ctx* c, const FFTLayer& L) {      // MASG_ATTN_PLANAR=0: fp32 row-major q|k|v and k_attention_tc
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("MASG_ATTN_PLANAR"); on = e ? atoi(e) : 1; }
+    return on && c->precision == MASG_PREC_BF16 && L.qkv.f16 && L.fc.f16;
+}
+
 // xp_in: planar fp16 copy of x from the previous block's LayerNorm (nullable); xp_out: where this block's last LayerNorm
 // leaves the same for the next block (nullable).  Decoder side in MASG_PREC_BF16 only (fp16 layers).
 static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer& L, float* x, const int64_t* lens, int B, int S,
@@ -211,11 +217,19 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     float* qkv = ar.get<float>(rows * 768);
     float* att = ar.get<float>(rows * 256);
     float* y = ar.get<float>(rows * 256);
-    if (xp_in) conv_from_planar16(c, s, L.qkv, xp_in, B, S, qkv);
-    else conv32(c, s, L.qkv, x, 256, B, S, qkv);
-    if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
-    else launch_attention_f32(c, s, qkv, lens, B, S, att);
-    conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                         // fc(out) + residual
+    if (attn_planar(c, L)) {
+        // fp16 layers: q | k | v and the attention output stay planar fp16 (operand layout end to end, attn_f16p.cu)
+        if (xp_in) conv_to_planar16(c, s, L.qkv, xp_in, true, 256, B, S, (bf16*)qkv, ACT_NONE);
+        else conv_to_planar16(c, s, L.qkv, x, false, 256, B, S, (bf16*)qkv, ACT_NONE);
+        launch_attention_f16p(c, s, qkv, lens, B, S, att);
+        conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, y, ACT_NONE, x); // fc(out) + residual
+    } else {
+        if (xp_in) conv_from_planar16(c, s, L.qkv, xp_in, B, S, qkv);
+        else conv32(c, s, L.qkv, x, 256, B, S, qkv);
+        if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
+        else launch_attention_f32(c, s, qkv, lens, B, S, att);
+        conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                     // fc(out) + residual
+    }
     const bool chain = f16_chain(c, L.w1, L.w2);
     bf16* xp1 = (chain && ln_planar(1)) ? ar.get<bf16>(rows * 256) : nullptr;   // LN output as w_1's operand
     launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x, xp1);   // LN + masked_fill (Layers.py:25)

@@ -484,3 +484,28 @@ def test_attention_matches_reference_formula(precision, B, S, lens):
     err = (out.cpu() - ref).abs().max().item()
     print("attention %s B=%d S=%d: max-abs err %.3e" % (precision, B, S, err))
     assert err <= 2e-4
+
+
+@pytest.mark.parametrize("B,S,lens", [(3, 200, [200, 77, 1]), (2, 600, [600, 389]), (2, 1300, [1300, 1025]), (2, 130, [129, 0]), (1, 128, [128])])
+def test_attention_planar_fp16_matches_reference_formula(B, S, lens):
+    """The decoder-side attention kernel (planar fp16 q|k|v in, planar fp16 out; V consumed as an MN-major operand straight
+    from the planar layout) against the same reference formula evaluated in fp64 on the fp16-rounded inputs."""
+    from masg_b200 import _lib
+    cx = _lib.default_context(DEV, "bf16")
+    g = torch.Generator().manual_seed(S + B)
+    qkv = (torch.randn(B, S, 768, generator=g) * 1.5).half()
+    lens_t = torch.tensor(lens, dtype=torch.int64)
+    q, k, v = [t.double().view(B, S, 2, 128).permute(0, 2, 1, 3) for t in qkv.split(256, dim=2)]
+    att = q @ k.transpose(2, 3) / np.power(128, 0.5)
+    key_pad = torch.arange(S)[None, :] >= lens_t[:, None]
+    att = att.masked_fill(key_pad[:, None, None, :], float("-inf"))
+    ref = (torch.softmax(att, dim=3) @ v).permute(0, 2, 1, 3).reshape(B, S, 256)
+    ref = torch.nan_to_num(ref).masked_fill(key_pad[:, :, None], 0.0).float()
+    planar = qkv.view(B, S, 96, 8).permute(0, 2, 1, 3).contiguous().to(DEV)          # [B][96][S][8]
+    lg = lens_t.to(DEV)
+    out = torch.full((B, 32, S, 8), 7.0, device=DEV, dtype=torch.float16)
+    cx.check(cx.lib.masg_attention_planar(cx.h, cx.stream(), P(planar), P(lg), B, S, P(out)), "attention_planar")
+    got = out.permute(0, 2, 1, 3).reshape(B, S, 256).float().cpu()
+    err = (got - ref).abs().max().item()
+    print("attention planar fp16 B=%d S=%d: max-abs err %.3e (|ref| max %.2f)" % (B, S, err, ref.abs().max().item()))
+    assert err <= 4e-3                                 # fp16 P (2^-11 relative) and the fp16 output ulp (|out| < 8: 2^-8 / 2)
