@@ -339,6 +339,90 @@ __device__ __forceinline__ void epi_planar(const TcArgs& a, const uint32_t tacc,
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Planar epilogue with residuals, full tiles (msub * NT = 256): a thread owns 8 steps of (16 columns, sub-tile).  The R1
+// rows of the first 4 steps are requested BEFORE the accumulator wait and the ring then stays 4 steps (8 x 16 bytes per
+// thread) ahead, so the global-load latencies overlap the tile's MMAs and each other; epi_planar above runs one step
+// ahead at best and eats most of one load latency per step — that made the second conv of every C = 128 / 256 ResBlock
+// pair epilogue-bound (0.53 ms against 0.27 ms for the first conv of the same shape).  R2 (the ResBlock-sum accumulator,
+// one launch in three) runs two steps ahead.
+// ---------------------------------------------------------------------------------------------
+constexpr int RES_STEPS = 8, RES_D2 = 2;
+// per-tile addressing of one thread (plain convs only: up = 1): step st = (column group st / MS, sub-tile st % MS) sits at
+// off0 + (st / MS) * 2 * gstride + (st % MS) * 1024 elements and is inside the utterance while (st % MS) * 128 < rows_left
+struct ResTile { long off0, gstride; int rows_left, cc0; };
+__device__ __forceinline__ ResTile epi_res_tile(const TcArgs& a, const int NT, const int n0, const int q0, const long boff, const int quad,
+                                                const int half, const int lane) {
+    ResTile t;
+    const int q = q0 + quad * 32 + lane;
+    t.cc0 = half ? NT / 2 : 0;
+    t.gstride = (long)a.y_T * 8;
+    t.off0 = boff + (long)((n0 + t.cc0) >> 3) * t.gstride + (long)q * 8;
+    t.rows_left = min(a.Q, a.y_T) - q;
+    return t;
+}
+template <int MS>
+__device__ __forceinline__ void epi_res_load(const ResTile& t, const bf16* R, const int st, uint4 (&r)[2]) {
+    const bf16* p = R + t.off0 + (long)(st / MS) * 2 * t.gstride + (st % MS) * 1024;
+    r[0] = r[1] = make_uint4(0u, 0u, 0u, 0u);
+    if ((st % MS) * 128 < t.rows_left) { r[0] = ld_nc(reinterpret_cast<const uint4*>(p)); r[1] = ld_nc(reinterpret_cast<const uint4*>(p + t.gstride)); }
+}
+template <int NT, int MS, bool HAS_R2>
+__device__ __forceinline__ void epi_res_run(const TcArgs& a, const ResTile& t, const uint32_t acc_full_bar, const uint32_t parity,
+                                            const uint32_t tacc, const float* bias_s, const int n0) {
+    static_assert((NT / 32) * MS == RES_STEPS, "eight steps per thread");
+    constexpr int RES_D1 = HAS_R2 ? 2 : 4;                  // 32 registers of residual rows in flight either way
+    uint4 r1[RES_STEPS][2], r2[RES_STEPS][2];
+#pragma unroll
+    for (int st = 0; st < RES_D1; ++st) epi_res_load<MS>(t, reinterpret_cast<const bf16*>(a.R1), st, r1[st]);
+    if (HAS_R2) {
+#pragma unroll
+        for (int st = 0; st < RES_D2; ++st) epi_res_load<MS>(t, reinterpret_cast<const bf16*>(a.R2), st, r2[st]);
+    }
+    mbar_wait_relaxed(acc_full_bar, parity);                // residual rows in flight while the tile's MMAs finish
+    tc_fence_after();
+    const bool lrelu_out = a.out_act == ACT_LRELU, other_act = a.out_act != ACT_NONE && a.out_act != ACT_LRELU;
+    const bool scaled = a.out_scale != 1.f, post = a.post_slope != 1.f;
+    const Slope2 sl_post = make_slope2(a.post_slope);
+#pragma unroll
+    for (int st = 0; st < RES_STEPS; ++st) {
+        const int cc = t.cc0 + (st / MS) * 16, ms = st % MS;
+        float v[16];
+        tmem_ld16(tacc + (uint32_t)(ms * NT + cc), v);
+        const float4* b4 = reinterpret_cast<const float4*>(bias_s + n0 + cc);
+        const float4 ba = b4[0], bb = b4[1], bc = b4[2], bd = b4[3];
+        add_f32x2(v[0], v[1], ba.x, ba.y); add_f32x2(v[2], v[3], ba.z, ba.w); add_f32x2(v[4], v[5], bb.x, bb.y); add_f32x2(v[6], v[7], bb.z, bb.w);
+        add_f32x2(v[8], v[9], bc.x, bc.y); add_f32x2(v[10], v[11], bc.z, bc.w); add_f32x2(v[12], v[13], bd.x, bd.y); add_f32x2(v[14], v[15], bd.z, bd.w);
+        if (other_act) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = act_apply(v[i], a.out_act, a.out_slope);
+        }
+        if (lrelu_out) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], v[i] * a.out_slope);
+        }
+        add_bf16x8(v, r1[st][0]); add_bf16x8(v + 8, r1[st][1]);
+        if (HAS_R2) { add_bf16x8(v, r2[st][0]); add_bf16x8(v + 8, r2[st][1]); }
+        if (st + RES_D1 < RES_STEPS) epi_res_load<MS>(t, reinterpret_cast<const bf16*>(a.R1), st + RES_D1, r1[st + RES_D1]);
+        if (HAS_R2 && st + RES_D2 < RES_STEPS) epi_res_load<MS>(t, reinterpret_cast<const bf16*>(a.R2), st + RES_D2, r2[st + RES_D2]);
+        if (scaled) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) mul_f32x2(v[i], v[i + 1], a.out_scale, a.out_scale);
+        }
+        uint4 pa, pb;
+        if (a.y_f16) { pa = pack8h(v); pb = pack8h(v + 8); } else { pa = pack8(v); pb = pack8(v + 8); }
+        if (post) {
+            pa.x = lrelu_bf16x2(pa.x, sl_post); pa.y = lrelu_bf16x2(pa.y, sl_post); pa.z = lrelu_bf16x2(pa.z, sl_post); pa.w = lrelu_bf16x2(pa.w, sl_post);
+            pb.x = lrelu_bf16x2(pb.x, sl_post); pb.y = lrelu_bf16x2(pb.y, sl_post); pb.z = lrelu_bf16x2(pb.z, sl_post); pb.w = lrelu_bf16x2(pb.w, sl_post);
+        }
+        if (ms * 128 < t.rows_left) {
+            bf16* p = a.Y16 + t.off0 + (long)(st / MS) * 2 * t.gstride + ms * 1024;
+            *reinterpret_cast<uint4*>(p) = pa;
+            *reinterpret_cast<uint4*>(p + t.gstride) = pb;
+        }
+    }
+}
+
 template <int NT, bool TMA_IN>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -553,6 +637,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         const int c_begin = half ? c_split : 0, c_end = half ? NT : c_split;
         const float* R1f = reinterpret_cast<const float*>(a.R1); const bf16* R1h = reinterpret_cast<const bf16*>(a.R1);
         const float* R2f = reinterpret_cast<const float*>(a.R2); const bf16* R2h = reinterpret_cast<const bf16*>(a.R2);
+        constexpr bool RES_FAST = NT == 32 || NT == 64 || NT == 128;
+        const bool res_fast = RES_FAST && a.y_planar && a.R1 != nullptr && a.up == 1 && a.up_pad == 0 && a.msub * NT == 256 && !(a.dbg & 64);
         int it = 0;
         const long long t_epi0 = clock64();
         for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
@@ -561,10 +647,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const int accb = it & 1;
             const bool tr = (a.dbg & 32) && blockIdx.x == 0 && threadIdx.x == 0;
             TRACE(tr, 3, it, 0);
+            const long boff = (long)b * a.y_bs;
+            if constexpr (RES_FAST) {
+                if (res_fast) {
+                    const ResTile rtile = epi_res_tile(a, NT, n0, q0, boff, quad, half, lane);
+                    const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols);
+                    if (a.R2 == nullptr) epi_res_run<NT, 256 / NT, false>(a, rtile, bars.acc_full(accb), (it >> 1) & 1, tacc, bias_s, n0);
+                    else epi_res_run<NT, 256 / NT, true>(a, rtile, bars.acc_full(accb), (it >> 1) & 1, tacc, bias_s, n0);
+                    TRACE(tr, 3, it, 1);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bars.acc_empty(accb));
+                    TRACE(tr, 3, it, 2);
+                    continue;
+                }
+            }
             STAT_WAIT((a.dbg & 16) && threadIdx.x == 0, 4, mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1));
             tc_fence_after();
             TRACE(tr, 3, it, 1);
-            const long boff = (long)b * a.y_bs;
             if (a.dbg & 4) {
                 // what-if: no epilogue work
             } else if (a.y_planar) {
