@@ -356,12 +356,12 @@ def run_ours(args):
     b1 = syn.make_batch(1, 50, seed=1235, accents_const=4)
     emb1 = sampler.sample()[:1].cpu().pin_memory()
     lat = []
-    for i in range(25):
+    for i in range(220):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         synth.synthesize_host(b1["texts"], b1["accents"], b1["src_lens"], emb1, 160)
         lat.append((time.perf_counter() - t0) * 1e3)
-    lat = sorted(lat[5:])
+    lat = sorted(lat[20:])
 
     if rank != 0:
         return 0
@@ -390,7 +390,149 @@ def run_ours(args):
                      "share_of_step": k_ms / step_ms_plain if step_ms_plain else None,
                      "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per conv (both convs of a fused pair)"},
         "cpu_baseline": cpu,
-        "latency_p50_ms": {"value": lat[len(lat) // 2], "config": "C2: batch 1, 50 phonemes, host ids -> int16 audio on host (masg_synthesize_host), 20 runs"},
+        "latency_p50_ms": {"value": lat[len(lat) // 2], "config": "C2: batch 1, 50 phonemes, host ids -> int16 audio on host (masg_synthesize_host), 200 timed runs after 20 warm-ups"},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+    return 0
+
+# ----------------------------------------------------------------------------------------------------------
+# the other shard-able configurations of BASELINE.json: C4 and C5, strong scaling
+# ----------------------------------------------------------------------------------------------------------
+def run_sharded(args):
+    """--workload c4: 4096 utterances, L = default_rng(0).integers(20, 301, 4096), sorted into length-bucketed batches under a
+    padded-frame budget, batches assigned to the ranks longest-processing-time-first (synth.plan_batches / assign_batches);
+    --workload c5: 16 utterances x 1000 phonemes (T = 3000), contiguous split of the batch over the ranks.
+    One step = one pass over the whole job (total work fixed -> "strong"); value = job audio-seconds / max-over-ranks time."""
+    import numpy as np
+    import torch
+    world, rank, local = _dist_setup(args.gpus)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); the synthesis path has no CPU fallback")
+    import masg_b200  # noqa: F401
+    from masg_b200 import synthetic as syn
+    from masg_b200.synth import plan_batches, assign_batches, shard_batch
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    fs2, voc, synth = build_models(args.precision, dev)
+    ctx = synth.ctx
+    if args.workload == "c4":
+        lengths = syn.c4_lengths(4096)
+        batches = plan_batches(lengths, frame_budget=args.frame_budget, max_batch=64)
+        mine = [batches[i] for i in assign_batches(batches, lengths, world)[rank]]
+        name = ("C4: 4096 utterances, 20-300 phonemes (numpy default_rng(0)), length-bucketed batches of <= 64 utterances / <= %d padded "
+                "frames, LPT assignment to ranks, 3 frames/phoneme, int16 audio out" % args.frame_budget)
+        seed0 = 1234 + 3
+    else:
+        lengths = np.full(16, 1000)
+        lo, hi = shard_batch(16, rank, world)
+        mine = [np.arange(lo, hi)] if hi > lo else []
+        batches = [np.arange(16)]
+        name = "C5: 16 utterances x 1000 phonemes (T = 3000), contiguous batch split over the ranks, int16 audio out"
+        seed0 = 1234 + 4
+    job_audio = float(lengths.sum()) * 3 * syn.HOP / syn.SAMPLING_RATE
+    sampler = SpeakerSampler(fs2, 32, 32, seed=77 + 100000 * rank)
+    work = []
+    for bi, idx in enumerate(mine):
+        b = syn.make_batch(len(idx), 0, seed=seed0 + 7919 * int(idx[0]), lens=lengths[idx])
+        work.append({"n": len(idx), "host": b, "dev": tuple(b[k].to(dev) for k in ("texts", "accents", "src_lens")),
+                     "frames": int(lengths[idx].sum()) * 3, "t_cap": 3 * int(lengths[idx].max()) + 8})
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([x], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    def pass_device():
+        frames = 0
+        for w in work:
+            emb = sampler.sample()[:w["n"]]
+            w16, mel_lens, _ = synth.synthesize(*w["dev"], emb)
+            frames += int(mel_lens.sum().item()) if args.check_lens else w["frames"]
+        return frames
+
+    pin_emb = torch.empty(64, 256, dtype=torch.float32).pin_memory()
+
+    def pass_host():
+        h2d = d2h = 0
+        for w in work:
+            emb = sampler.sample()[:w["n"]]
+            pin_emb[:w["n"]].copy_(emb, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            b = w["host"]
+            _, _, T, a, c = synth.synthesize_host(b["texts"], b["accents"], b["src_lens"], pin_emb[:w["n"]], w["t_cap"])
+            h2d += a; d2h += c + w["n"] * 256 * 4
+        return h2d, d2h
+
+    args.check_lens = True
+    my_frames = pass_device()                                               # warm-up pass 1 also checks the 3-frames-per-phoneme lengths
+    assert my_frames == sum(w["frames"] for w in work), "unexpected mel lengths"
+    args.check_lens = False
+    for _ in range(max(args.warmup, 3) - 1):
+        pass_device()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ctx.launch_count(reset=True)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)
+        ev[i][0].record()
+        pass_device()
+        ev[i][1].record()
+    barrier()
+    launches = ctx.launch_count()
+    ms_dev = max_over_ranks(sum(a.elapsed_time(b) for a, b in ev))
+    value = job_audio * args.steps / (ms_dev / 1e3)
+    pass_host()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        h2d, d2h = pass_host()
+    torch.cuda.synchronize()
+    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    ctx.profile(True)
+    pass_device()
+    k_ms, k_flops, k_n = ctx.profile_read()
+    ctx.profile(False)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); pass_device(); e1.record(); torch.cuda.synchronize()
+    pass_ms = e0.elapsed_time(e1)
+    if rank != 0:
+        return 0
+    pk = _peaks()
+    ach = k_flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "config": {"workload": name, "utterances": int(len(lengths)), "batches": len(batches), "batches_rank0": len(work), "job_audio_s": job_audio,
+                   "parallelism": "dp%d" % world, "precision": args.precision, "weights": "seeded random init",
+                   "l2": "256 MiB flush buffer written before every timed pass"},
+        "e2e": {"value": job_audio * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": ms_e2e / args.steps, "note": "rank 0's bytes; one masg_synthesize_host call per batch"},
+        "gpu_launches": int(launches), "clocks": clk,
+        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
+                     "traffic": None, "peak_source": pk["src"], "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": pass_ms,
+                     "share_of_step": k_ms / pass_ms if pass_ms else None,
+                     "how": "per-launch CUDA events over one extra pass of rank 0's share; FLOPs counted over the padded rows each launch processes"},
+        "cpu_baseline": None,
     }
     print(json.dumps(line))
     if world > 1:
@@ -407,12 +549,16 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"], help="c3 = the headline configuration (default); c4 / c5 = the sharded configurations of BASELINE.json")
+    ap.add_argument("--frame-budget", type=int, default=40000, help="c4: padded frames per batch")
     ap.add_argument("--profile-range", action="store_true", help="warm up, then run ONE step inside cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     import __graft_entry__
     __graft_entry__.build_if_needed()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload != "c3":
+        return run_sharded(args)
     return run_ours(args)
 
 
