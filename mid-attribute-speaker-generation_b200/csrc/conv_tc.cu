@@ -457,6 +457,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // programmatic dependent launch: everything above touched constants only; the weight warp (constants) and the issuers (shared
+    // memory / TMEM only) run ahead, every role that reads or writes activations waits for the previous grid of the stream
+    pdl_trigger();
+    if (warp != W_WARP && !(warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS)) pdl_wait();
 
     // tile id -> (batch b, row tile rt, column tile nt); a CTA walks ids blockIdx.x, blockIdx.x + gridDim.x, ...
     if (warp >= A_WARP0) {
@@ -793,7 +797,7 @@ template <int NT, bool TMA_IN>
 void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
-    k_conv_tc<NT, TMA_IN><<<grid, NTHREADS, smem, s>>>(a);
+    CUDA_OK(launch_pdl(k_conv_tc<NT, TMA_IN>, grid, NTHREADS, smem, s, a));
 }
 
 }  // namespace

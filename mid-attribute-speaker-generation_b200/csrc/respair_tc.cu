@@ -109,6 +109,14 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // programmatic dependent launch (see conv_tc.cu): the resident weights are requested before the wait
+    pdl_trigger();
+    if (warp == RP_COPY_WARP && lane == 0) {
+        mbar_expect_tx(bars.w_ready(), 2u * WBYTES);
+        bulk_g2s(smem_u32(W1s), a.W1, WBYTES, bars.w_ready());
+        bulk_g2s(smem_u32(W2s), a.W2, WBYTES, bars.w_ready());
+    }
+    if (!(warp >= RP_MMA_WARP && warp < RP_MMA_WARP + RP_ISSUERS)) pdl_wait();
 
     if (warp >= RP_WORK_WARP0) {
         // ===== workers: leaky-relu in place on the landed x tile =====
@@ -131,11 +139,6 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
         }
     } else if (warp == RP_COPY_WARP || warp == RP_COPY_WARP + 1) {
         // ===== copy warp: resident weights once, then one contiguous run per 8-channel group per tile =====
-        if (lane == 0 && warp == RP_COPY_WARP) {
-            mbar_expect_tx(bars.w_ready(), 2u * WBYTES);
-            bulk_g2s(smem_u32(W1s), a.W1, WBYTES, bars.w_ready());
-            bulk_g2s(smem_u32(W2s), a.W2, WBYTES, bars.w_ready());
-        }
         const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
         for (int it = warp - RP_COPY_WARP; it < n_my; it += 2) {
             const int tile = blockIdx.x + it * gridDim.x;
@@ -371,7 +374,7 @@ template <int C, int K, int XS, int NH>
 void launch_rp(const RpArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_respair_tc<C, K, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, RP_MAX_SMEM)); attr = true; }
-    k_respair_tc<C, K, XS, NH><<<grid, RP_THREADS, smem, s>>>(a);
+    CUDA_OK(launch_pdl(k_respair_tc<C, K, XS, NH>, grid, RP_THREADS, smem, s, a));
 }
 
 size_t rp_smem(int C, int K, int Rx, int xs, int nh) {

@@ -50,6 +50,10 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
     return pred != 0;
 }
+// programmatic dependent launch: the next kernel of the stream may begin its prologue (barrier init, TMEM allocation, bias and
+// weight loads: constants only) while this grid drains; it reads activations only after pdl_wait (= previous grid complete + flushed)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -140,6 +144,21 @@ __device__ __forceinline__ void add_f32x2(float& a0, float& a1, const float b0, 
 __device__ __forceinline__ void mul_f32x2(float& a0, float& a1, const float b0, const float b1) {
     asm("{\n\t.reg .b64 x, y;\n\tmov.b64 x, {%0, %1};\n\tmov.b64 y, {%2, %3};\n\tmul.rn.f32x2 x, x, y;\n\tmov.b64 {%0, %1}, x;\n\t}"
         : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+
+
+// launch with the programmatic-stream-serialization attribute (MASG_PDL=0 turns it off); the kernel must call pdl_wait()
+template <typename Kern, typename Args>
+inline cudaError_t launch_pdl(Kern kern, dim3 grid, int threads, size_t smem, cudaStream_t s, const Args& a) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("MASG_PDL"); on = e ? atoi(e) : 0; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(threads, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = on ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, a);
 }
 
 }  // namespace tcptx
