@@ -420,10 +420,10 @@ def run_sharded(args):
     ctx = synth.ctx
     if args.workload == "c4":
         lengths = syn.c4_lengths(4096)
-        batches = plan_batches(lengths, frame_budget=args.frame_budget, max_batch=64)
+        batches = plan_batches(lengths, frame_budget=args.frame_budget, max_batch=args.max_batch)
         mine = [batches[i] for i in assign_batches(batches, lengths, world)[rank]]
-        name = ("C4: 4096 utterances, 20-300 phonemes (numpy default_rng(0)), length-bucketed batches of <= 64 utterances / <= %d padded "
-                "frames, LPT assignment to ranks, 3 frames/phoneme, int16 audio out" % args.frame_budget)
+        name = ("C4: 4096 utterances, 20-300 phonemes (numpy default_rng(0)), length-bucketed batches of <= %d utterances / <= %d padded "
+                "frames, LPT assignment to ranks, 3 frames/phoneme, int16 audio out" % (args.max_batch, args.frame_budget))
         seed0 = 1234 + 3
     else:
         lengths = np.full(16, 1000)
@@ -433,7 +433,8 @@ def run_sharded(args):
         name = "C5: 16 utterances x 1000 phonemes (T = 3000), contiguous batch split over the ranks, int16 audio out"
         seed0 = 1234 + 4
     job_audio = float(lengths.sum()) * 3 * syn.HOP / syn.SAMPLING_RATE
-    sampler = SpeakerSampler(fs2, 32, 32, seed=77 + 100000 * rank)
+    nb = max(len(b) for b in batches)
+    sampler = SpeakerSampler(fs2, nb // 2, nb - nb // 2, seed=77 + 100000 * rank)
     work = []
     for bi, idx in enumerate(mine):
         b = syn.make_batch(len(idx), 0, seed=seed0 + 7919 * int(idx[0]), lens=lengths[idx])
@@ -463,7 +464,7 @@ def run_sharded(args):
             frames += int(mel_lens.sum().item()) if args.check_lens else w["frames"]
         return frames
 
-    pin_emb = torch.empty(64, 256, dtype=torch.float32).pin_memory()
+    pin_emb = torch.empty(nb, 256, dtype=torch.float32).pin_memory()
 
     def pass_host():
         h2d = d2h = 0
@@ -551,6 +552,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"], help="c3 = the headline configuration (default); c4 / c5 = the sharded configurations of BASELINE.json")
     ap.add_argument("--frame-budget", type=int, default=40000, help="c4: padded frames per batch")
+    ap.add_argument("--max-batch", type=int, default=64, help="c4: utterances per batch")
     ap.add_argument("--profile-range", action="store_true", help="warm up, then run ONE step inside cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     import __graft_entry__
