@@ -329,6 +329,11 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         io.X = x16; io.x_bf16 = 1; io.x_planar = 1; io.Y = nullptr; io.Y16 = y16; io.y_planar = 1; io.y_T = (int)So;
     }
     if (residual) { io.R1 = io.X; io.r_bf16 = act_bf16; }
+    if (residual && (flags & 16) && act_bf16) {               // residual in its own buffer (as in the generator: x, not the conv's input h)
+        bf16* r16 = nullptr; CUDA_OK(cudaMalloc(&r16, (size_t)B * T * Cin * 2)); c->owned.push_back(r16);
+        CUDA_OK(cudaMemcpyAsync(r16, x16, (size_t)B * T * Cin * 2, cudaMemcpyDeviceToDevice, s));
+        io.R1 = r16;
+    }
     if (in_lrelu_slope != 0.f) { io.in_act = ACT_LRELU; io.in_slope = in_lrelu_slope; }
     launch_conv(c, s, d, io);                                  // warm-up / result
     cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));

@@ -74,6 +74,7 @@ struct TcArgs {
     int in_act; float in_slope; int out_act; float out_slope;
     const void* R1; const void* R2; int r_bf16; float out_scale; float post_slope;
     int w_resident;                                    // the whole weight set is one stage, loaded once per CTA
+    int res_pf;                                        // copy warp prefetches the tile's residual rows into L2 (MASG_TC_RESPF, default on)
     int w_stages;                                      // weight ring depth (3 with 32 KB stages, else 4 with 16 KB stages)
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
@@ -550,6 +551,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const bool tr = (a.dbg & 32) && blockIdx.x == 0 && lane == 0;
             const int cgpc = a.KC >> 3;
             const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
+            const bool res_pf = a.res_pf && a.y_planar && a.R1 != nullptr && a.r_bf16 && a.up == 1 && a.up_pad == 0;
             for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
@@ -585,6 +587,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     }
                     if (kc == 0) TRACE(tr, 0, it, 2);
                     if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
+                }
+                if (res_pf) {
+                    // residual rows of this tile -> L2, one run per 8-channel group, a few tiles before the epilogue warps read them.
+                    // The activation copies above keep ~100 KB per SM (15 MB chip-wide) queued at the memory controllers, so a
+                    // residual load that has to go to DRAM waits 2.5-5 us behind them and the epilogue's two load rounds per tile
+                    // (16.8 kcycles at C = 64 k = 11) outlast the tile's MMAs (12.5 kcycles); from L2 they do not.
+                    const int nt = tile % a.n_ntiles, q0 = rt * a.msub * 128;
+                    const int rows = min(a.msub * 128, min(a.Q, a.y_T) - q0);
+                    if (rows > 0) {
+                        const long gs = (long)a.y_T * 8;
+                        const long off = (long)b * a.y_bs + (long)((nt * NT) >> 3) * gs + (long)q0 * 8;
+                        for (int g = lane; g < NT / 8; g += 32) {
+                            bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R1) + off + (long)g * gs, (uint32_t)rows * 16u);
+                            if (a.R2) bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R2) + off + (long)g * gs, (uint32_t)rows * 16u);
+                        }
+                    }
                 }
             }
         }
@@ -962,6 +980,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale; a.post_slope = io.post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
+    { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
     a.y_planar = io.y_planar;
     if (io.y_planar) {
         MASG_CHECK(io.Y16 != nullptr && io.Y == nullptr && io.y_T > 0, "conv_tc: planar output is bf16 only and needs y_T");

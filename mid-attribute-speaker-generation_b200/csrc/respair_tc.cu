@@ -44,7 +44,7 @@ struct RpArgs {
     const bf16* W1; const bf16* W2; const float* b1; const float* b2;
     int B, T, dil, tiles_per_b, total_tiles, Rx, r_out, p1, p2;
     float slope, out_scale, post_slope;
-    int dbg;
+    int dbg, res_pf;
 };
 
 // MASG_TC_DEBUG & 32: timeline of CTA 0 (clock64 at the hand-over points of its first RP_TRACE_TILES tiles).
@@ -169,6 +169,11 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
             if (run && lane < CG) {
                 const uint8_t* src = X8 + (((size_t)b * CG + lane) * a.T + lo) * 16;
                 bulk_g2s(dst + (uint32_t)((lane * a.Rx + (lo - t0)) * 16), src, run, bar);
+            }
+            if (a.R2 != nullptr && a.res_pf && lane < CG) {
+                // MRF accumulator rows of this tile -> L2 ahead of the E2 warps (see conv_tc.cu: DRAM loads queue behind the copies)
+                const int q0 = i * a.r_out, rows = min(a.r_out, a.T - q0);
+                if (rows > 0) bulk_prefetch_l2(a.R2 + (((size_t)b * CG + lane) * a.T + q0) * 8, (uint32_t)rows * 16u);
             }
             RP_TRACE(trace && lane == 0, 0, it, 2);
         }
@@ -426,6 +431,7 @@ void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const Co
     a.tiles_per_b = (T + a.r_out - 1) / a.r_out; a.total_tiles = B * a.tiles_per_b;
     a.slope = 0.1f; a.out_scale = out_scale; a.post_slope = post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
+    { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
     static int n_sm = 0;
     if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
     const dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);

@@ -44,6 +44,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// L2 prefetch of one contiguous run (no shared-memory destination, no barrier): the rows arrive in L2 ahead of the loads that use them
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 // one lane of the (converged) warp; the same lane every time, so MMAs and their commits come from one thread
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;

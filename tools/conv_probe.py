@@ -31,6 +31,11 @@ CASES = [
     ("fs2 dec fc (fp16)", 64, 600, 256, 256, 1, 1, 0, 0.0, 8),
     ("postnet 512 k5 (fp16)", 64, 600, 512, 512, 5, 1, 0, 0.0, 8),
     ("hg s2 c2 k3 +res", 64, 38400, 128, 128, 3, 1, 0, 0.1, 6),
+    ("hg s3 c1 k11 d5", 64, 76800, 64, 64, 11, 5, 0, 0.1, 2),
+    ("hg s3 c1 k11 d1", 64, 76800, 64, 64, 11, 1, 0, 0.1, 2),
+    ("hg s3 c2 k11 +res (own buffer)", 64, 76800, 64, 64, 11, 1, 0, 0.1, 22),
+    ("hg s2 c2 k7 +res (own buffer)", 64, 38400, 128, 128, 7, 1, 0, 0.1, 22),
+    ("hg s2 c2 k3 +res (own buffer)", 64, 38400, 128, 128, 3, 1, 0, 0.1, 22),
 ]
 
 def main():
@@ -57,7 +62,7 @@ def main():
         flops = 2.0 * B * T * taps * Cin * N
         esz = 2 if (flags & 2) else 4
         byts = B * T * Cin * esz * (2 if flags & 4 else 1) + B * So * Cout * esz
-        print("%2d %-24s %8.3f ms  %7.1f TFLOP/s  %7.1f GB/s" % (i, name, ms.value, flops / ms.value / 1e9, byts / ms.value / 1e6), flush=True)
+        print("%2d %-32s %8.3f ms  %7.1f TFLOP/s  %7.1f GB/s" % (i, name, ms.value, flops / ms.value / 1e9, byts / ms.value / 1e6), flush=True)
         del x, y
 
 if __name__ == "__main__":
