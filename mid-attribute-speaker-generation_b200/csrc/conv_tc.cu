@@ -892,6 +892,16 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     int msub = 1;
     while (msub * 2 * NT <= 256 && msub * 128 < io.Q) msub *= 2;
     if (d.split) msub = std::min(msub, 2);
+    {
+        // k = 1 layers (QKV / fc / w_2, flattened over the batch rows): 128-row tiles.  Their A block is the whole K extent
+        // (256 rows x 256..1024 channels = 4-16 chunks for 3 slots), so a 256-row tile cannot be prefetched across the tile
+        // boundary and every tile starts with an exposed load latency; at 128 rows the chunks are half as long and the tile
+        // count doubles (4.05 -> 8.1 waves for fc / w_2): QKV / fc / w_2 8-10 % faster in isolation, -0.1 ms per step (launch list)
+        // (MASG_TC_MSUB_K1: cap on the sub-tiles per tile, 0 = none)
+        static int cap = -1;
+        if (cap < 0) { const char* e = getenv("MASG_TC_MSUB_K1"); cap = e ? atoi(e) : 1; }
+        if (cap > 0 && d.taps == 1) msub = std::min(msub, cap);
+    }
     const int ntiles_n = d.N / NT;
     while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub /= 2;
     int KC = 0;
