@@ -157,3 +157,22 @@ def test_speaker_embedding_artefacts_round_trip(tmp_path):
     assert back.shape == (3, 256) and torch.equal(back, embs)
     np.save(tmp_path / "flat.npy", embs[0].numpy())                            # a [256] array is accepted too
     assert torch.equal(synth.load_speaker_embeddings([tmp_path / "flat.npy"])[0], embs[0])
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference (the CPU oracle port timed on the host cores) prints one JSON line with the driver's keys;
+    the sharded workloads are selectable without a GPU being touched at argument-parsing time."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "audio-s/s" and line["higher_is_better"] is True
+    assert line["value"] > 0 and line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert line["gpu_launches"] == 0 and "C3" in line["config"]["workload"]
+    helptext = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--help"], capture_output=True, text=True, timeout=600, cwd=root).stdout
+    assert "--workload" in helptext and "c4" in helptext and "c5" in helptext
