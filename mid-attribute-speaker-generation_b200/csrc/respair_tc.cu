@@ -54,19 +54,21 @@ constexpr int RP_TRACE_TILES = 96, RP_TRACE_EVTS = 4, RP_TRACE_ROLES = 5;
 __device__ long long g_rp_trace[RP_TRACE_ROLES * RP_TRACE_TILES * RP_TRACE_EVTS];
 #define RP_TRACE(on, role, it, evt) do { if ((on) && (it) < RP_TRACE_TILES) g_rp_trace[((role) * RP_TRACE_TILES + (it)) * RP_TRACE_EVTS + (evt)] = clock64(); } while (0)
 
+constexpr int RP_MAX_XS = 6;                // activation slots the barrier block has room for
 struct RpBars {
     uint32_t base;
     __device__ uint32_t x_raw(int i) const { return base + 8u * i; }
-    __device__ uint32_t x_full(int i) const { return base + 8u * (3 + i); }
-    __device__ uint32_t x_empty(int i) const { return base + 8u * (6 + i); }
-    __device__ uint32_t acc1_full(int i) const { return base + 8u * (9 + i); }
-    __device__ uint32_t acc1_empty(int i) const { return base + 8u * (11 + i); }
-    __device__ uint32_t h_full(int i) const { return base + 8u * (13 + i); }
-    __device__ uint32_t h_empty(int i) const { return base + 8u * (15 + i); }
-    __device__ uint32_t acc2_full(int i) const { return base + 8u * (17 + i); }
-    __device__ uint32_t acc2_empty(int i) const { return base + 8u * (19 + i); }
-    __device__ uint32_t w_ready() const { return base + 8u * 21; }
+    __device__ uint32_t x_full(int i) const { return base + 8u * (RP_MAX_XS + i); }
+    __device__ uint32_t x_empty(int i) const { return base + 8u * (2 * RP_MAX_XS + i); }
+    __device__ uint32_t acc1_full(int i) const { return base + 8u * (3 * RP_MAX_XS + i); }
+    __device__ uint32_t acc1_empty(int i) const { return base + 8u * (3 * RP_MAX_XS + 2 + i); }
+    __device__ uint32_t h_full(int i) const { return base + 8u * (3 * RP_MAX_XS + 4 + i); }
+    __device__ uint32_t h_empty(int i) const { return base + 8u * (3 * RP_MAX_XS + 6 + i); }
+    __device__ uint32_t acc2_full(int i) const { return base + 8u * (3 * RP_MAX_XS + 8 + i); }
+    __device__ uint32_t acc2_empty(int i) const { return base + 8u * (3 * RP_MAX_XS + 10 + i); }
+    __device__ uint32_t w_ready() const { return base + 8u * (3 * RP_MAX_XS + 12); }
 };
+static_assert(8 * (3 * RP_MAX_XS + 13) <= 256, "barrier block overlaps the TMEM slot");
 
 // XS activation slots, NH buffers of h (3 / 2 when shared memory allows, else 2 / 1)
 template <int C, int K, int XS, int NH>
@@ -128,10 +130,18 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
             mbar_wait_relaxed(bars.x_raw(slot), u & 1);
             RP_TRACE(trace && tid == 0, 1, it, 0);
             uint4* p = reinterpret_cast<uint4*>(Xs + (size_t)slot * x_bytes);
-            for (int i = tid; i < pieces && !(a.dbg & 128); i += RP_WORK_THREADS) {   // dbg 128: what-if, no leaky-relu pass
-                uint4 v = p[i];
-                v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl); v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
-                p[i] = v;
+            // four pieces per thread in flight (the one-piece loop serialised a shared-memory round trip per piece and, once six
+            // activation slots had removed the slot wait, this pass set the tile period at k = 3)
+            for (int i0 = tid; i0 < pieces && !(a.dbg & 128); i0 += 4 * RP_WORK_THREADS) {   // dbg 128: what-if, no leaky-relu pass
+                uint4 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { const int i = i0 + j * RP_WORK_THREADS; if (i < pieces) v[j] = p[i]; }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int i = i0 + j * RP_WORK_THREADS;
+                    v[j].x = lrelu_bf16x2(v[j].x, sl); v[j].y = lrelu_bf16x2(v[j].y, sl); v[j].z = lrelu_bf16x2(v[j].z, sl); v[j].w = lrelu_bf16x2(v[j].w, sl);
+                    if (i < pieces) p[i] = v[j];
+                }
             }
             fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(bars.x_full(slot));
@@ -385,9 +395,15 @@ void launch_rp(const RpArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
 size_t rp_smem(int C, int K, int Rx, int xs, int nh) {
     return (size_t)RP_HDR + (size_t)xs * (C / 8) * Rx * 16 + (size_t)nh * (C / 8) * RP_HROWS * 16 + 2 * (size_t)K * C * C * 2;
 }
-// 3 activation slots + 2 h buffers when they fit beside the resident weights, else 2 + 1 (C = 64, k = 7); false: no fit
+// C = 32: 6 activation slots + 2 h buffers (the slot cycle — copy issue 1.5 k + copy latency 2.8 k + leaky-relu pass 2.4 k + conv 1 —
+// is ~7.6 kcycles, so 3 slots capped the tile period at 2.6 kcycles whatever k; MASG_RP_XS overrides); C = 64: 3 + 2 when they
+// fit beside the resident weights, else 2 + 1 (k = 7); false: no fit
 bool rp_config(int C, int K, int Rx, int& xs, int& nh) {
-    xs = 3; nh = 2;
+    static int want = -1;
+    if (want < 0) { const char* e = getenv("MASG_RP_XS"); want = e ? atoi(e) : RP_MAX_XS; }
+    xs = (C == 32 && want == RP_MAX_XS) ? RP_MAX_XS : 3; nh = 2;
+    if (rp_smem(C, K, Rx, xs, nh) <= (size_t)RP_MAX_SMEM) return true;
+    xs = 3;
     if (rp_smem(C, K, Rx, xs, nh) <= (size_t)RP_MAX_SMEM) return true;
     xs = 2; nh = 1;
     return rp_smem(C, K, Rx, xs, nh) <= (size_t)RP_MAX_SMEM;
@@ -446,6 +462,7 @@ void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const Co
     }
 #define RP_CASE(CV, KV, XV, NV) if (C == CV && K == KV && xs == XV && nh == NV) launch_rp<CV, KV, XV, NV>(a, grid, smem, s);
     RP_CASE(32, 3, 3, 2) RP_CASE(32, 7, 3, 2) RP_CASE(32, 11, 3, 2) RP_CASE(64, 3, 3, 2) RP_CASE(64, 7, 2, 1)
+    RP_CASE(32, 3, 6, 2) RP_CASE(32, 7, 6, 2) RP_CASE(32, 11, 6, 2)
 #undef RP_CASE
     CUDA_OK(cudaGetLastError());
     c->launches++;
