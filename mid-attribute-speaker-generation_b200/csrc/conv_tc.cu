@@ -480,17 +480,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                         STAT_WAIT((a.dbg & 16) && tid == 0, 8, mbar_wait_relaxed(bars.a_raw(slot), phase));
                         if (kc == 0) TRACE(tr, 1, it, 0);
                         uint4* p = reinterpret_cast<uint4*>(A_smem + (size_t)slot * a.a_bytes);
-                        for (int i0 = tid; i0 < pieces; i0 += 4 * A_THREADS) {          // four pieces per thread in flight
-                            uint4 v[4];
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) { const int i = i0 + j * A_THREADS; if (i < pieces) v[j] = p[i]; }
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const int i = i0 + j * A_THREADS;
-                                v[j].x = lrelu_bf16x2(v[j].x, sl); v[j].y = lrelu_bf16x2(v[j].y, sl);
-                                v[j].z = lrelu_bf16x2(v[j].z, sl); v[j].w = lrelu_bf16x2(v[j].w, sl);
-                                if (i < pieces) p[i] = v[j];
-                            }
+                        for (int i = tid; i < pieces; i += A_THREADS) {                // one piece per trip on purpose (respair_tc.cu)
+                            uint4 v = p[i];
+                            v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl);
+                            v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
+                            p[i] = v;
                         }
                         fence_proxy_async();                  // generic-proxy stores -> visible to the tensor core (async proxy)
                         mbar_arrive(bars.a_full(slot));

@@ -130,18 +130,13 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
             mbar_wait_relaxed(bars.x_raw(slot), u & 1);
             RP_TRACE(trace && tid == 0, 1, it, 0);
             uint4* p = reinterpret_cast<uint4*>(Xs + (size_t)slot * x_bytes);
-            // four pieces per thread in flight (the one-piece loop serialised a shared-memory round trip per piece and, once six
-            // activation slots had removed the slot wait, this pass set the tile period at k = 3)
-            for (int i0 = tid; i0 < pieces && !(a.dbg & 128); i0 += 4 * RP_WORK_THREADS) {   // dbg 128: what-if, no leaky-relu pass
-                uint4 v[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) { const int i = i0 + j * RP_WORK_THREADS; if (i < pieces) v[j] = p[i]; }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int i = i0 + j * RP_WORK_THREADS;
-                    v[j].x = lrelu_bf16x2(v[j].x, sl); v[j].y = lrelu_bf16x2(v[j].y, sl); v[j].z = lrelu_bf16x2(v[j].z, sl); v[j].w = lrelu_bf16x2(v[j].w, sl);
-                    if (i < pieces) p[i] = v[j];
-                }
+            // one piece per thread per trip, on purpose: four pieces in flight shortened this pass from ~2000 to ~1250 cycles but the
+            // bursts compete with the MMAs' operand reads for the shared-memory pipe (k = 7 0.401 -> 0.425 ms, and the MMA-bound
+            // stage-2 convs of conv_tc, which share the loop shape, +4 %)
+            for (int i = tid; i < pieces && !(a.dbg & 128); i += RP_WORK_THREADS) {   // dbg 128: what-if, no leaky-relu pass
+                uint4 v = p[i];
+                v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl); v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
+                p[i] = v;
             }
             fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(bars.x_full(slot));
@@ -401,6 +396,11 @@ size_t rp_smem(int C, int K, int Rx, int xs, int nh) {
 bool rp_config(int C, int K, int Rx, int& xs, int& nh) {
     static int want = -1;
     if (want < 0) { const char* e = getenv("MASG_RP_XS"); want = e ? atoi(e) : RP_MAX_XS; }
+    {   // C = 64, k = 3: experiment switch MASG_RP_C64K3=41 -> 4 activation slots + 1 h buffer instead of 3 + 2
+        static int alt = -1;
+        if (alt < 0) { const char* e = getenv("MASG_RP_C64K3"); alt = e ? atoi(e) : 0; }
+        if (C == 64 && K == 3 && alt == 41 && rp_smem(C, K, Rx, 4, 1) <= (size_t)RP_MAX_SMEM) { xs = 4; nh = 1; return true; }
+    }
     xs = (C == 32 && want == RP_MAX_XS) ? RP_MAX_XS : 3; nh = 2;
     if (rp_smem(C, K, Rx, xs, nh) <= (size_t)RP_MAX_SMEM) return true;
     xs = 3;
@@ -462,7 +462,7 @@ void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const Co
     }
 #define RP_CASE(CV, KV, XV, NV) if (C == CV && K == KV && xs == XV && nh == NV) launch_rp<CV, KV, XV, NV>(a, grid, smem, s);
     RP_CASE(32, 3, 3, 2) RP_CASE(32, 7, 3, 2) RP_CASE(32, 11, 3, 2) RP_CASE(64, 3, 3, 2) RP_CASE(64, 7, 2, 1)
-    RP_CASE(32, 3, 6, 2) RP_CASE(32, 7, 6, 2) RP_CASE(32, 11, 6, 2)
+    RP_CASE(32, 3, 6, 2) RP_CASE(32, 7, 6, 2) RP_CASE(32, 11, 6, 2) RP_CASE(64, 3, 4, 1)
 #undef RP_CASE
     CUDA_OK(cudaGetLastError());
     c->launches++;
