@@ -50,7 +50,8 @@ def _ncu_traffic():
     """DRAM bytes (read + written) per k_conv_tc / k_respair_tc launch, from the newest committed `ncu --set full` capture of one C3 step
     (profiles/r*_ncu_full_conv_tc_*.csv, written by tools/ncu_summary.py).  A profiler number, reported beside the live ones."""
     import csv, glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv_tc_*.csv")))
+    # r<round>_ncu_<full|dram>_conv_tc_<tag>.csv: `--set full` captures and the cheaper DRAM / tensor-pipe metric captures; newest tag wins
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_*_conv_tc_*.csv")), key=lambda f: os.path.basename(f).rsplit("_", 1)[1])
     if not files:
         return None, None
     rows = list(csv.DictReader(open(files[-1])))
