@@ -369,9 +369,9 @@ def run_ours(args):
     # ---- CPU baseline (oracle port) on this box's host cores, bounded sample, N = 1 only ----------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        audio, times, cores = cpu_reference_run(2, L, 1)
+        audio, times, cores = cpu_reference_run(8, L, 1)
         cpu = {"value": audio / times[-1], "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "2 of the 64 C3 utterances (200 phonemes, 600 frames each), one pass after a tiny warm-up, fp32 PyTorch CPU ops"}
+               "sample": "8 of the 64 C3 utterances (200 phonemes, 600 frames each; 55.7 s of audio), one pass after a tiny warm-up, fp32 PyTorch CPU ops"}
     ach = k_flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
