@@ -128,54 +128,184 @@ def _dist_setup(n_gpus):
 
 
 # ----------------------------------------------------------------------------------------------------------
-# reference arm / CPU baseline: the oracle port on the host cores (the only place bench.py executes oracle/)
+# reference arm / CPU baseline / eager-GPU baseline: the UNMODIFIED reference (oracle/_ref staged by oracle/make_ref.py, or
+# /root/reference in the build container) through its own public API, else the oracle port.  The only place bench.py
+# executes oracle/.
 # ----------------------------------------------------------------------------------------------------------
-def cpu_reference_run(n_utts, L, reps, warm=True):
-    import torch
-    import masg_b200  # noqa: F401
-    from masg_b200 import synthetic as syn
-    from oracle import restate
-    torch.set_num_threads(os.cpu_count() or 1)
-    sd = syn.make_fs2_state_dict(seed=1234, duration_mode="fixed3")
-    hsd = restate.fold_weight_norm(syn.make_hifigan_state_dict(seed=4321))
+N_REF_SAMPLE = 8            # utterances of the C3 batch per reference step (55.7 s of audio; ~4 s of CPU work on 16 threads)
 
-    def run(b, emb):
-        out = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], b["max_src_len"], emb)
-        wav = restate.hifigan_forward(hsd, out[1].transpose(1, 2))
-        restate.wav_to_int16(wav.squeeze(1))
+
+def c3_config(world):
+    """The `config` object of the bench line — identical in both arms (the reference arm runs on OUR arm's config)."""
+    return {"workload": WORKLOAD, "global_batch": B_C3 * world, "phonemes": L_C3, "frames_per_utt": 3 * L_C3, "parallelism": "dp%d" % world,
+            "weights": "seeded random init (no checkpoint in the reference tree)",
+            "l2": "256 MiB flush buffer written before every timed step; activations (GBs per step) far exceed the 126 MB L2"}
+
+
+class ReferencePath:
+    """FastSpeech2 + speaker prior + HiFi-GAN of the reference on `device` ("cpu" or "cuda"): the unmodified modules driven the
+    way examples_gen.py:114-140 + utils/tools.py:264-270 drive them (synthesize_from_speaker_emb -> vocoder_infer), or the oracle
+    port (oracle/restate.py) when no reference tree is present."""
+
+    def __init__(self, device="cpu"):
+        import torch
+        import masg_b200  # noqa: F401
+        from masg_b200 import synthetic as syn
+        from oracle import ref_import, restate
+        self.torch, self.syn, self.restate, self.device = torch, syn, restate, device
+        self.sd = syn.make_fs2_state_dict(seed=1234, duration_mode="fixed3")
+        hsd = syn.make_hifigan_state_dict(seed=4321)
+        self.kind = "reference" if ref_import.available() else "port"
+        self.source = ref_import.kind()
+        if self.kind == "reference":
+            self.ns = ref_import.load()
+            self.pre, self.mod = ref_import.load_configs()
+            self.fs2 = ref_import.build_fs2(self.sd, syn.speakers_json(), syn.STATS_JSON).to(device)
+            self.voc = ref_import.build_hifigan(hsd).to(device)
+            metas = torch.tensor(syn.META_COMBOS, dtype=torch.float32, device=device)
+            with torch.no_grad():
+                d = [self.fs2.speaker_distribution(metas[i:i + 1]) for i in (0, 3)]
+            t0 = time.perf_counter()
+            self.interp = self.ns.InterpolateGMM(d[0], d[1])          # scipy sqrtm/inv on 256x256 matrices: seconds (SURVEY a19)
+            self.interp_build_s = time.perf_counter() - t0
+        else:
+            self.hsd = restate.fold_weight_norm(hsd)
+
+    def embeddings(self, n, seed):
+        """n speaker embeddings the way config 3 draws them: half from speaker_gen, half from an InterpolateGMM prior."""
+        torch = self.torch
+        torch.manual_seed(seed)
+        if self.kind != "reference":
+            return torch.randn(n, 256) * 0.5
+        meta = torch.tensor([self.syn.META_COMBOS[i % 4] for i in range(n - n // 2)], dtype=torch.float32, device=self.device)
+        with torch.no_grad():
+            embs = [self.fs2.speaker_gen(meta)] + [self.interp.sample().to(self.device) for _ in range(n // 2)]
+        return torch.cat(embs, 0).float()
+
+    def run(self, b, emb, vocoder=True):
+        """One pass: ids -> mel (-> int16 waveforms cut to length).  Returns audio seconds produced."""
+        torch, syn = self.torch, self.syn
+        if self.kind == "reference":
+            dev = self.device
+            with torch.no_grad():
+                out = self.fs2.synthesize_from_speaker_emb(None, b["texts"].to(dev), b["src_lens"].to(dev), b["max_src_len"],
+                                                           accents=b["accents"].to(dev), speaker_emb=emb.to(dev))
+                if vocoder:
+                    lengths = out[9] * self.pre["stft"]["hop_length"]
+                    self.ns.vocoder_infer(out[1].transpose(1, 2), self.voc, self.mod, self.pre, lengths=lengths)
+                elif dev != "cpu":
+                    out[1].cpu()
+        else:
+            out = self.restate.fs2_forward(self.sd, b["texts"], b["accents"], b["src_lens"], b["max_src_len"], emb)
+            if vocoder:
+                self.restate.wav_to_int16(self.restate.hifigan_forward(self.hsd, out[1].transpose(1, 2)).squeeze(1))
         return float(out[9].sum()) * syn.HOP / syn.SAMPLING_RATE
 
-    g = torch.Generator().manual_seed(1)
-    if warm:
-        run(syn.make_batch(1, 16, seed=3), torch.randn(1, 256, generator=g) * 0.5)
-    b = syn.make_batch(n_utts, L, seed=1234 + 2)
-    emb = torch.randn(n_utts, 256, generator=g) * 0.5
-    times, audio = [], 0.0
-    for _ in range(reps):
-        t0 = time.perf_counter()
-        audio = run(b, emb)
-        times.append(time.perf_counter() - t0)
-    return audio, times, torch.get_num_threads()
+
+def _p50(xs):
+    xs = sorted(xs)
+    return xs[len(xs) // 2]
 
 
 def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores (all threads), each step
+    a bounded sample (N_REF_SAMPLE of the 64 utterances) of our arm's workload.  CUDA is hidden from this process so the
+    reference's module-level `device` globals (model/modules.py:14, utils/tools.py:15) resolve to the CPU."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    n_utts = 2
-    audio, times, cores = cpu_reference_run(n_utts, L_C3, args.warmup + args.steps)
+    import torch
+    torch.set_num_threads(os.cpu_count() or 1)
+    cores = torch.get_num_threads()
+    ref = ReferencePath("cpu")
+    syn = ref.syn
+    n_utts = N_REF_SAMPLE
+    ref.run(syn.make_batch(1, 16, seed=3), ref.embeddings(1, 0))               # tiny warm-up (thread pools, oneDNN primitives)
+    b = syn.make_batch(B_C3, L_C3, seed=1234 + 2)
+    b = {k: (v[:n_utts] if torch.is_tensor(v) else v) for k, v in b.items()}
+    times, audio = [], 0.0
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        emb = ref.embeddings(n_utts, 77 + i)
+        audio = ref.run(b, emb)
+        times.append(time.perf_counter() - t0)
     timed = times[args.warmup:]
     sec = sum(timed) / len(timed)
     val = audio / sec
-    sample = "%d of the 64 utterances of the C3 batch per step (200 phonemes, 600 frames each), fp32 PyTorch CPU ops, %d threads" % (n_utts, cores)
+    # BASELINE.json config 1 (B = 1, L = 50, mel only, CPU) and config 2 (+ HiFi-GAN) latencies on the same cores
+    b1 = syn.make_batch(1, 50, seed=1235, accents_const=4)
+    e1 = ref.embeddings(1, 5)
+    lat1, lat2 = [], []
+    for i in range(1 + args.latency_reps):
+        t0 = time.perf_counter(); ref.run(b1, e1, vocoder=False); lat1.append((time.perf_counter() - t0) * 1e3)
+        t0 = time.perf_counter(); ref.run(b1, e1, vocoder=True); lat2.append((time.perf_counter() - t0) * 1e3)
+    what = ("the unmodified reference modules (%s copy), synthesize_from_speaker_emb + vocoder_infer" % ref.source) if ref.kind == "reference" \
+        else "oracle/restate.py (CPU port of the reference's algorithm; no reference tree on this box)"
+    sample = "%d of the 64 utterances of the C3 batch per step (200 phonemes, 600 frames each; %.1f s of audio), %s, fp32 PyTorch CPU ops, %d threads" % (
+        n_utts, audio, what, cores)
+    cpu = {"value": val, "unit": UNIT, "cores": cores, "kind": ref.kind, "sample": sample,
+           "c1_latency_p50_ms": {"value": _p50(lat1[1:]), "config": "C1: batch 1, 50 phonemes, mel only, CPU, p50 of %d runs after 1 warm-up" % args.latency_reps},
+           "c2_latency_p50_ms": {"value": _p50(lat2[1:]), "config": "C2 on the CPU: batch 1, 50 phonemes, FastSpeech2 + HiFi-GAN -> int16, p50 of %d runs" % args.latency_reps}}
+    if ref.kind == "reference":
+        cpu["interpolate_gmm_build_s"] = ref.interp_build_s
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": sample},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "config": c3_config(args.gpus),
+            "cpu_baseline": cpu,
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
     return 0
+
+
+def cpu_baseline_subprocess():
+    """cpu_baseline leg of our arm: the reference arm above in a child process with CUDA hidden (one warm-up + one timed step)."""
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "2", "--warmup", "1", "--latency-reps", "5"],
+                           capture_output=True, text=True, env=env, timeout=900)
+        for ln in reversed(r.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)["cpu_baseline"]
+        return {"error": (r.stderr or r.stdout)[-400:]}
+    except Exception as e:                                                   # noqa: BLE001 - a missing baseline must not lose the bench line
+        return {"error": repr(e)[:400]}
+
+
+def gpu_eager_baseline(dev, steps=3):
+    """The unmodified reference modules on the B200 through PyTorch eager (fp32; TF32 off and on), full C3 batch — SURVEY §8(d)
+    'reference GPU path': not a published number, the honest thing to beat.  Same call sequence as the CPU arm."""
+    import torch
+    from oracle import ref_import
+    if not ref_import.available():
+        return {"unavailable": "no reference tree on this box (oracle/_ref not staged)"}
+    out = {}
+    try:
+        ref = ReferencePath(str(dev))
+        b = ref.syn.make_batch(B_C3, L_C3, seed=1234 + 2)
+        audio = 0.0
+        old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+        for name, tf32 in (("fp32_tf32_off", False), ("fp32_tf32_on", True)):
+            torch.backends.cudnn.allow_tf32 = tf32
+            torch.backends.cuda.matmul.allow_tf32 = tf32
+            ts = []
+            for i in range(1 + steps):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                audio = ref.run(b, ref.embeddings(B_C3, 77 + i))              # ends with the int16 audio on the host (vocoder_infer .cpu())
+                torch.cuda.synchronize()
+                ts.append(time.perf_counter() - t0)
+            sec = sum(ts[1:]) / steps
+            out[name] = {"value": audio / sec, "unit": UNIT, "ms_per_step": sec * 1e3}
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+        out["config"] = "the unmodified reference modules on cuda:0 (PyTorch eager), full C3 batch of 64, host ids -> int16 audio on the host, %d timed steps after 1 warm-up" % steps
+        del ref
+        torch.cuda.empty_cache()
+    except Exception as e:                                                   # noqa: BLE001
+        out["error"] = repr(e)[:400]
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -367,20 +497,17 @@ def run_ours(args):
     if rank != 0:
         return 0
     # ---- CPU baseline (oracle port) on this box's host cores, bounded sample, N = 1 only ----------------
-    cpu = None
+    cpu = eager = None
     if world == 1 and not args.no_cpu_baseline:
-        audio, times, cores = cpu_reference_run(8, L, 1)
-        cpu = {"value": audio / times[-1], "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "8 of the 64 C3 utterances (200 phonemes, 600 frames each; 55.7 s of audio), one pass after a tiny warm-up, fp32 PyTorch CPU ops"}
+        cpu = cpu_baseline_subprocess()
+        eager = gpu_eager_baseline(dev)
     ach = k_flops / (k_ms / 1e3) / 1e12 if k_ms > 0 else 0.0
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "global_batch": B * world, "phonemes": L, "frames_per_utt": 3 * L, "parallelism": "dp%d" % world,
-                   "precision": args.precision + (" (HiFi-GAN bf16; FastSpeech2 encoder + variance predictors split-bf16 hi/lo, 3 MMAs per K step; decoder, mel_linear, PostNet fp16 operands; fp32 accumulation everywhere)" if args.precision == "bf16" else ""),
-                   "weights": "seeded random init (no checkpoint in the reference tree)",
-                   "l2": "256 MiB flush buffer written before every timed step; activations (GBs per step) far exceed the 126 MB L2"},
+        "config": c3_config(world),
+        "precision": args.precision + (" (HiFi-GAN bf16; FastSpeech2 encoder + variance predictors split-bf16 hi/lo, 3 MMAs per K step; decoder, mel_linear, PostNet fp16 operands; fp32 accumulation everywhere)" if args.precision == "bf16" else ""),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "clocks": clk,
@@ -391,6 +518,7 @@ def run_ours(args):
                      "share_of_step": k_ms / step_ms_plain if step_ms_plain else None,
                      "how": "per-launch CUDA events on the launching stream over one extra identical step; algorithmic FLOPs = 2*rows*K*N per conv (both convs of a fused pair)"},
         "cpu_baseline": cpu,
+        "gpu_eager_baseline": eager,
         "latency_p50_ms": {"value": lat[len(lat) // 2], "config": "C2: batch 1, 50 phonemes, host ids -> int16 audio on host (masg_synthesize_host), 200 timed runs after 20 warm-ups"},
     }
     print(json.dumps(line))
@@ -550,12 +678,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline and gpu_eager_baseline legs")
+    ap.add_argument("--latency-reps", type=int, default=5, help="reference arm: timed runs of the C1 / C2 CPU latency")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"], help="c3 = the headline configuration (default); c4 / c5 = the sharded configurations of BASELINE.json")
     ap.add_argument("--frame-budget", type=int, default=40000, help="c4: padded frames per batch")
     ap.add_argument("--max-batch", type=int, default=64, help="c4: utterances per batch")
     ap.add_argument("--profile-range", action="store_true", help="warm up, then run ONE step inside cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
+    if args.impl == "reference":
+        os.environ["CUDA_VISIBLE_DEVICES"] = ""        # the CPU arm: the reference's `device` globals must resolve to the CPU
+        if int(os.environ.get("RANK", "0")) != 0:
+            return 0                                   # under torchrun rank 0 alone runs it
     import __graft_entry__
     __graft_entry__.build_if_needed()
     if args.impl == "reference":

@@ -70,7 +70,28 @@ def main():
     rec["scale_025"] = ig.component_distribution.base_dist.scale[0].numpy()
     np.savez_compressed(os.path.join(OUT, "gmm_prior.npz"), weights_seed=1234, **rec)
     print("gmm weights", rec["weights"])
+    barycenter(ref)
+
+
+BARY_RATE = [0.5, 0.25, 0.125, 0.125]      # sums to 1 exactly in floating point (distributions.py:112 asserts equality)
+
+
+def barycenter(ref=None):
+    """tests/golden/barycenter.npz: BarycenterGMM run by the reference's own methods (ref_import.run_barycenter) at the
+    default uniform rate and at BARY_RATE."""
+    if ref is None:
+        ref = ref_import.build_fs2(syn.make_fs2_state_dict(seed=1234), syn.speakers_json(), syn.STATS_JSON)
+    rec = {}
+    with torch.no_grad():
+        for tag, rate in (("uniform", None), ("rate", BARY_RATE)):
+            probs, mean, std, _ = ref_import.run_barycenter(ref, rate)
+            rec["probs_" + tag], rec["mean_" + tag], rec["std_" + tag] = probs.numpy(), mean.numpy(), std.numpy()
+            print("barycenter", tag, "components", probs.shape[0], "probs", probs.numpy().round(4))
+    np.savez_compressed(os.path.join(OUT, "barycenter.npz"), weights_seed=1234, rate=np.array(BARY_RATE), **rec)
 
 
 if __name__ == "__main__":
-    main()
+    if "--barycenter" in sys.argv:
+        barycenter()
+    else:
+        main()

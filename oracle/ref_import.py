@@ -1,6 +1,6 @@
-"""Import the *unmodified* reference (/root/reference) read-only, on CPU, with the five absent
-third-party modules stubbed.  Exists only in the build container: nothing run
-on the GPU box may call this (``available()`` is False there).
+"""Import the *unmodified* reference read-only with the five absent third-party modules stubbed:
+from /root/reference in the build container, or from the byte-for-byte staged copy ``oracle/_ref`` (written by
+oracle/make_ref.py, git-ignored, shipped with the snapshot) on the GPU box, where /root/reference does not exist.
 
 TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).
 """
@@ -11,12 +11,31 @@ import sys
 import tempfile
 import types
 
-REF_ROOT = os.environ.get("MASG_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_STAGED = os.path.join(_HERE, "_ref")            # oracle/make_ref.py: byte-for-byte staged copy that travels to the GPU box
 _CFG_REL = "config/JVS-VCTK_langemb_configs/JVS-VCTK_1"
+
+
+def _resolve_root():
+    env = os.environ.get("MASG_REFERENCE_ROOT")
+    for cand in ([env] if env else []) + ["/root/reference", _STAGED]:
+        if cand and os.path.isfile(os.path.join(cand, "model", "fastspeech2.py")):
+            return cand
+    return env or "/root/reference"
+
+
+REF_ROOT = _resolve_root()
 
 
 def available() -> bool:
     return os.path.isfile(os.path.join(REF_ROOT, "model", "fastspeech2.py"))
+
+
+def kind() -> str:
+    """'live' = /root/reference itself (build container), 'staged' = oracle/_ref (GPU box), 'absent'."""
+    if not available():
+        return "absent"
+    return "staged" if os.path.abspath(REF_ROOT) == os.path.abspath(_STAGED) else "live"
 
 
 def _stub(name, **attrs):
@@ -116,3 +135,28 @@ def build_hifigan(state_dict_weight_normed):
     with contextlib.redirect_stdout(io.StringIO()):
         g.remove_weight_norm()
     return g
+
+
+def run_barycenter(model, rate=None):
+    """The reference's BarycenterGMM (model/distributions.py:79-192) on `model`, executed by the reference's own code.
+
+    As written the constructor raises TypeError: :92 calls ``self._barycenter_gaussians(_print=False)`` while :136 defines
+    ``_barycenter_gaussians(self)``.  The subclass below overrides that ONE method to swallow the
+    keyword and forward to the reference's implementation; ``__init__``, ``_product``, ``_one_barycenter_gaussian``,
+    ``_determine_pi``, ``_w2sq`` and ``barycenter_rate`` all run unmodified.  This is what pins a20.
+    Returns (probs [n], mean [n, D], std [n, D], used positions) of the resulting mixture."""
+    import contextlib
+    import io
+    import tqdm as _tqdm
+    ns = load()
+
+    class _Runnable(ns.BarycenterGMM):
+        def _barycenter_gaussians(self, _print=True):
+            return ns.BarycenterGMM._barycenter_gaussians(self)
+
+    with contextlib.redirect_stdout(io.StringIO()), contextlib.redirect_stderr(io.StringIO()):
+        bg = _Runnable(model)
+        if rate is not None:
+            bg.barycenter_rate(list(rate), _print=False)
+    comp = bg.component_distribution.base_dist
+    return bg.mixture_distribution.probs[0], comp.loc[0], comp.scale[0], bg

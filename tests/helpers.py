@@ -61,3 +61,22 @@ def snr_db(ref, out):
 
 def to_gpu(batch):
     return {k: (v.to("cuda:0") if torch.is_tensor(v) else v) for k, v in batch.items()}
+
+
+def check_unforced_durations(out_log_d, ref_log_d, out_d, ref_d, tag=""):
+    """Un-forced duration parity (north_star: durations bit-exact given identical predictor outputs).  The predictor outputs
+    of a reduced-precision mode are not identical, so: the integer durations must still be EQUAL, except at positions where
+    the reference's own exp(log_d) - 1 sits on a half-integer rounding boundary to within twice the measured log_d error
+    (there the reference's decision is itself an accident of rounding).  Returns the number of such boundary flips."""
+    out_log_d, ref_log_d = out_log_d.detach().cpu().double(), torch.as_tensor(ref_log_d).double()
+    out_d, ref_d = out_d.detach().cpu(), torch.as_tensor(ref_d)
+    err = (out_log_d - ref_log_d).abs().max().item()
+    flips = out_d != ref_d
+    n = int(flips.sum())
+    print("un-forced durations %s: log_d max-abs err %.2e, flips %d of %d" % (tag, err, n, flips.numel()))
+    if n:
+        d = torch.exp(ref_log_d) - 1
+        dist = ((d - torch.floor(d)) - 0.5).abs()[flips]
+        assert (dist <= 2 * err * torch.exp(ref_log_d)[flips] + 1e-7).all(), \
+            "%s: duration flip away from a rounding boundary (boundary distances %s, log_d err %.2e)" % (tag, dist.tolist()[:8], err)
+    return n

@@ -79,12 +79,22 @@ def test_duration_rounding_bit_exact(ctx, d_ctl):
     log_dg = log_d.to(DEV)                                                            # keep alive across the call
     ctx.check(ctx.lib.masg_duration_round(ctx.h, ctx.stream(), P(log_dg), d_ctl, log_d.numel(), P(out)), "dur")
     out = out.cpu()
-    # identical except where a 1-ulp difference in exp() straddles a rounding boundary (none expected on
-    # the random part; the engineered .5 cases depend on the CPU libm and are allowed to differ by one step)
+    # The kernel evaluates exp in double and rounds it to fp32 (k_duration), i.e. it implements the duration rule with a
+    # correctly rounded fp32 exp.  That is bit-exact on EVERY input against the same rule evaluated through a float64 exp
+    # (numpy), including the 39 engineered inputs whose exp(x) - 1 lands within an ulp of a .5 rounding boundary ...
+    e32 = np.exp(log_d.numpy().astype(np.float64)).astype(np.float32)
+    want_cr = np.maximum(np.rint(e32 - np.float32(1.0)).astype(np.float32) * np.float32(d_ctl), np.float32(0.0))
+    assert np.array_equal(out.numpy(), want_cr)
+    # ... and against torch's own CPU fp32 exp (SLEEF, <= 1 ulp, not correctly rounded) wherever that exp is not itself
+    # on a boundary: all 20000 random inputs and the special values.  On the engineered boundary inputs torch CPU, torch
+    # CUDA (expf, 2 ulp) and a correctly rounded exp can legitimately disagree by one rounding step: the reference's result
+    # there depends on its libm, so the correctly rounded value above is the pinned one.
     n_rand = 20000
     assert torch.equal(out[:n_rand], want[:n_rand])
-    assert (out[n_rand:] - want[n_rand:]).abs().max() <= d_ctl + 1e-6
     assert torch.equal(out[-4:], want[-4:])
+    n_diff = int((out[n_rand:-4] != want[n_rand:-4]).sum())
+    print("engineered .5-boundary inputs where torch's CPU expf rounds the other way: %d of 39" % n_diff)
+    assert (out[n_rand:] - want[n_rand:]).abs().max() <= d_ctl + 1e-6
 
 
 def test_bucketize_embedding_bit_exact(ctx):
@@ -130,11 +140,11 @@ def test_fs2_matches_oracle_ragged_batch(precision):
     assert (enc - taps["encoder_out"]).abs().max() <= tol * 2
     for i, name in ((2, "pitch"), (3, "energy"), (4, "log_d")):
         assert (out[i].cpu() - ref[i]).abs().max() <= tol * 4, name
-    flips = int((out[5].cpu() != ref[5]).sum())
-    print("un-forced duration flips (%s): %d of %d" % (precision, flips, ref[5].numel()))
     assert torch.equal(out[6].cpu(), ref[6]) and torch.equal(out[8].cpu(), b["src_lens"])
-    if precision == "fp32":
-        assert flips == 0
+    # un-forced integer durations: equal in BOTH precisions (a flip only on an exact rounding boundary of the reference itself)
+    flips = helpers.check_unforced_durations(out[4], ref[4] , out[5] / 1.2, ref[5] / 1.2, precision)
+    if precision == "fp32" or flips == 0:
+        assert flips == 0 and torch.equal(out[9].cpu(), ref[9])
     # mel parity on the same padded batch with the oracle's durations teacher-forced
     ref_t = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 40, emb, p_control=0.9, d_control=1.2, d_target=ref[5])
     out_t = _run_fs2(model, b, emb, p_control=0.9, d_control=1.2, d_targets=ref[5].to(DEV))
@@ -152,11 +162,19 @@ def test_fs2_matches_reference_golden(golden_dir, precision, name):
     g = np.load(os.path.join(golden_dir, name + ".npz"))
     model, sd = helpers.fs2_on_gpu(int(g["weights_seed"]), str(g["duration_mode"]), precision)
     texts = torch.from_numpy(g["texts"]).to(DEV)
-    out = model.synthesize_from_speaker_emb(
-        ["raw text is ignored"], texts, torch.from_numpy(g["src_lens"]).to(DEV), texts.shape[1],
-        accents=torch.from_numpy(g["accents"]).to(DEV), speaker_emb=torch.from_numpy(g["speaker_emb"]).to(DEV),
-        p_control=float(g["p_control"]), d_control=float(g["d_control"]),
-        d_targets=None if precision == "fp32" else torch.from_numpy(g["d_rounded"]).to(DEV))
+    args = dict(accents=torch.from_numpy(g["accents"]).to(DEV), speaker_emb=torch.from_numpy(g["speaker_emb"]).to(DEV),
+                p_control=float(g["p_control"]), d_control=float(g["d_control"]))
+    lens = torch.from_numpy(g["src_lens"]).to(DEV)
+    # un-forced in both precisions: the integer durations of the bf16 mode (split-bf16 encoder + predictors) must equal the
+    # reference's own; teacher forcing is only the fallback for a flip on an exact rounding boundary of the reference
+    out = model.synthesize_from_speaker_emb(["raw text is ignored"], texts, lens, texts.shape[1], **args)
+    dc = float(g["d_control"])
+    flips = helpers.check_unforced_durations(out[4], g["log_d"], out[5] / dc, torch.from_numpy(g["d_rounded"]) / dc, "%s %s" % (name, precision))
+    if precision == "fp32":
+        assert flips == 0
+    if flips:
+        out = model.synthesize_from_speaker_emb(["raw text is ignored"], texts, lens, texts.shape[1],
+                                                d_targets=torch.from_numpy(g["d_rounded"]).to(DEV), **args)
     assert torch.equal(out[9].cpu(), torch.from_numpy(g["mel_lens"]))
     assert torch.equal(out[5].cpu(), torch.from_numpy(g["d_rounded"]))
     tol = MEL_TOL[precision]
@@ -295,9 +313,20 @@ def test_gmm_params_sampling_and_interpolation(golden_dir):
     buf = io.BytesIO(); torch.save(ig, buf); buf.seek(0)
     ig2 = torch.load(buf, weights_only=False)
     assert torch.equal(ig2.component_distribution.base_dist.loc, ig.component_distribution.base_dist.loc)
-    # BarycenterGMM against the oracle's restatement of the maths
+    # BarycenterGMM against the fixture written by the reference's OWN methods (oracle/ref_import.run_barycenter runs
+    # model/distributions.py:79-192 unmodified apart from the one keyword that makes the constructor raise) ...
+    gb = np.load(os.path.join(golden_dir, "barycenter.npz"))
     bg = BarycenterGMM(model)
-    w, bm, bs, keys = restate.barycenter_gmm([p for p in pi.cpu()], [m for m in mu.cpu()], [s_ for s_ in sigma.cpu()])
+    for tag in ("uniform", "rate"):
+        if tag == "rate":
+            bg.barycenter_rate([float(r) for r in gb["rate"]], _print=False)
+        assert bg.mixture_distribution.probs.shape[-1] == gb["probs_" + tag].shape[0]
+        assert np.abs(bg.mixture_distribution.probs[0].cpu().numpy() - gb["probs_" + tag]).max() < 1e-5
+        assert np.abs(bg.component_distribution.base_dist.loc[0].cpu().numpy() - gb["mean_" + tag]).max() < 1e-5
+        assert np.abs(bg.component_distribution.base_dist.scale[0].cpu().numpy() - gb["std_" + tag]).max() < 1e-5
+    # ... and against the oracle's restatement of the same maths
+    w, bm, bs, keys = restate.barycenter_gmm([p for p in pi.cpu()], [m for m in mu.cpu()], [s_ for s_ in sigma.cpu()],
+                                             [float(r) for r in gb["rate"]])
     assert bg.mixture_distribution.probs.shape[-1] == len(keys)
     assert (bg.mixture_distribution.probs[0].cpu() - w / w.sum()).abs().max() < 1e-5
     assert (bg.component_distribution.base_dist.loc[0].cpu() - bm).abs().max() < 1e-5
