@@ -160,14 +160,17 @@ class ReferencePath:
         if self.kind == "reference":
             self.ns = ref_import.load()
             self.pre, self.mod = ref_import.load_configs()
-            self.fs2 = ref_import.build_fs2(self.sd, syn.speakers_json(), syn.STATS_JSON).to(device)
-            self.voc = ref_import.build_hifigan(hsd).to(device)
-            metas = torch.tensor(syn.META_COMBOS, dtype=torch.float32, device=device)
+            fs2 = ref_import.build_fs2(self.sd, syn.speakers_json(), syn.STATS_JSON)
+            # the mid-attribute prior is built on the CPU as the reference does (model/distributions.py mixes numpy / CPU tensors
+            # into the components, so an InterpolateGMM of CUDA distributions cannot be sampled); it is sampled on the CPU too
+            metas = torch.tensor(syn.META_COMBOS, dtype=torch.float32)
             with torch.no_grad():
-                d = [self.fs2.speaker_distribution(metas[i:i + 1]) for i in (0, 3)]
+                d = [fs2.speaker_distribution(metas[i:i + 1]) for i in (0, 3)]
             t0 = time.perf_counter()
-            self.interp = self.ns.InterpolateGMM(d[0], d[1])          # scipy sqrtm/inv on 256x256 matrices: seconds
+            self.interp = self.ns.InterpolateGMM(d[0], d[1])          # scipy sqrtm/inv on 256x256 matrices
             self.interp_build_s = time.perf_counter() - t0
+            self.fs2 = fs2.to(device)
+            self.voc = ref_import.build_hifigan(hsd).to(device)
         else:
             self.hsd = restate.fold_weight_norm(hsd)
 
@@ -219,7 +222,7 @@ def run_reference(args):
     cores = torch.get_num_threads()
     ref = ReferencePath("cpu")
     syn = ref.syn
-    n_utts = N_REF_SAMPLE
+    n_utts = max(1, min(B_C3, args.ref_sample))
     ref.run(syn.make_batch(1, 16, seed=3), ref.embeddings(1, 0))               # tiny warm-up (thread pools, oneDNN primitives)
     b = syn.make_batch(B_C3, L_C3, seed=1234 + 2)
     b = {k: (v[:n_utts] if torch.is_tensor(v) else v) for k, v in b.items()}
@@ -679,6 +682,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline and gpu_eager_baseline legs")
+    ap.add_argument("--ref-sample", type=int, default=N_REF_SAMPLE, help="reference arm: utterances of the C3 batch per step")
     ap.add_argument("--latency-reps", type=int, default=5, help="reference arm: timed runs of the C1 / C2 CPU latency")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"], help="c3 = the headline configuration (default); c4 / c5 = the sharded configurations of BASELINE.json")
     ap.add_argument("--frame-budget", type=int, default=40000, help="c4: padded frames per batch")

@@ -64,11 +64,14 @@ int masg_hifigan_commit(masg_ctx* ctx, void* stream);
  *   p_ctl, e_ctl, d_ctl: controls; e_ctl is accepted and IGNORED, energy is scaled by p_ctl exactly
  *                        as model/modules.py:123-125 does.
  *   d_target       : nullable fp32 [B, L]: teacher-forced durations (modules.py:128-130)
+ *   p_target, e_target: nullable fp32 [B, L]: teacher-forced pitch / energy — the embedding is then looked up from
+ *                        bucketize(target) and the prediction is returned unscaled (modules.py:80-100)
  *   out: pitch, energy, log_d, d_rounded fp32 [B, L]; mel_lens int64 [B]; src_mask uint8 [B, L]
  *        (1 = pad). */
 int masg_fs2_phase_a(masg_ctx* ctx, void* stream, const int64_t* texts, const int64_t* accents,
                      int accents_is_1d, const int64_t* src_lens, int B, int L, const float* spk_emb,
                      float p_ctl, float e_ctl, float d_ctl, const float* d_target,
+                     const float* p_target, const float* e_target,
                      float* pitch, float* energy, float* log_d, float* d_rounded, int64_t* mel_lens,
                      uint8_t* src_mask, int64_t* h_tmax);
 
@@ -181,6 +184,25 @@ int64_t masg_launch_count(masg_ctx* ctx, int reset);
 /* Intermediate tap for parity tests: copies a named internal fp32 buffer of the last forward
  * ("encoder_out" [B,L,256], "lr_out" [B,T,256], "decoder_out" [B,T,256]) into dst (device, fp32). */
 int masg_debug_tap(masg_ctx* ctx, void* stream, const char* name, float* dst, int64_t n_elems);
+
+/* ---- text front-end (host only, no device work): the Japanese branch of the reference's tokenisation, batched ----
+ * prepare_tg_accent_jsut.py:18-70 pp_symbols (HTS full-context label -> phoneme + accent mark), convert_label.py:52-59
+ * openjtalk2julius, and the id lookups of synthesize.py:217-218 ({s: i for i, s in enumerate(symbols)} — the LAST occurrence
+ * of a duplicated symbol wins — and {'0':0, '[':1, ']':2, '#':3}).
+ * masg_frontend_create: `symbols` = the model's symbol inventory (text/symbols.py:25-36), index = id.
+ * masg_frontend_tokenize: `blob` holds one label per '\n'-separated line for all utterances back to back,
+ * labels_per_utt[u] lines each; writes texts / accents int64 [n_utts, L_cap] (zero padded, caller-owned HOST memory,
+ * typically pinned) and src_lens int64 [n_utts].  n_threads host threads split the utterances.
+ * Errors (non-zero, message via masg_frontend_last_error): 11 = 'sil' inside an utterance (the reference asserts),
+ * 12 = symbol not in the inventory (KeyError in the reference), 13 = malformed label / no trailing 'sil' (IndexError),
+ * 14 = utterance longer than L_cap. */
+typedef struct masg_frontend masg_frontend;
+int  masg_frontend_create(const char* const* symbols, int n_symbols, masg_frontend** out);
+void masg_frontend_destroy(masg_frontend* fe);
+const char* masg_frontend_last_error(masg_frontend* fe);      /* fe may be NULL */
+int  masg_frontend_tokenize(masg_frontend* fe, const char* blob, int64_t blob_bytes, const int64_t* labels_per_utt, int n_utts,
+                            int L_cap, int drop_unvoiced_vowels, int n_threads, int64_t* texts, int64_t* accents,
+                            int64_t* src_lens);
 
 #ifdef __cplusplus
 }

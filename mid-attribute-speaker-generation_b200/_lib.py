@@ -25,7 +25,7 @@ SIGNATURES = {
     "masg_load_tensor": (c_int, [P, c_char_p, c_char_p, P, c_int, ctypes.POINTER(c_i64)]),
     "masg_fs2_commit": (c_int, [P, P]),
     "masg_hifigan_commit": (c_int, [P, P]),
-    "masg_fs2_phase_a": (c_int, [P, P, P, P, c_int, P, c_int, c_int, P, c_float, c_float, c_float, P,
+    "masg_fs2_phase_a": (c_int, [P, P, P, P, c_int, P, c_int, c_int, P, c_float, c_float, c_float, P, P, P,
                                  P, P, P, P, P, P, ctypes.POINTER(c_i64)]),
     "masg_fs2_phase_b": (c_int, [P, P, c_int, P, P, P]),
     "masg_duration_round": (c_int, [P, P, P, c_float, c_i64, P]),
@@ -48,6 +48,10 @@ SIGNATURES = {
     "masg_profile_read": (c_int, [P, P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64)]),
     "masg_launch_count": (c_i64, [P, c_int]),
     "masg_debug_tap": (c_int, [P, P, c_char_p, P, c_i64]),
+    "masg_frontend_create": (c_int, [ctypes.POINTER(c_char_p), c_int, ctypes.POINTER(P)]),
+    "masg_frontend_destroy": (None, [P]),
+    "masg_frontend_last_error": (c_char_p, [P]),
+    "masg_frontend_tokenize": (c_int, [P, c_char_p, c_i64, P, c_int, c_int, c_int, c_int, P, P, P]),
 }
 
 _lib = None

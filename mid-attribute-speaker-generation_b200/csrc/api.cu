@@ -90,12 +90,12 @@ int masg_hifigan_commit(masg_ctx* c, void* stream) {
 
 int masg_fs2_phase_a(masg_ctx* c, void* stream, const int64_t* texts, const int64_t* accents, int accents_is_1d,
                      const int64_t* src_lens, int B, int L, const float* spk_emb, float p_ctl, float e_ctl, float d_ctl,
-                     const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded, int64_t* mel_lens,
-                     uint8_t* src_mask, int64_t* h_tmax) {
+                     const float* d_target, const float* p_target, const float* e_target, float* pitch, float* energy, float* log_d,
+                     float* d_rounded, int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax) {
     API_BEGIN(c)
     MASG_CHECK(texts && src_lens && spk_emb && pitch && energy && log_d, "null argument");
     fs2_phase_a(c, (cudaStream_t)stream, texts, accents, accents_is_1d, src_lens, B, L, spk_emb, p_ctl, e_ctl, d_ctl, d_target,
-                pitch, energy, log_d, d_rounded, mel_lens, src_mask, h_tmax);
+                p_target, e_target, pitch, energy, log_d, d_rounded, mel_lens, src_mask, h_tmax);
     API_END(c)
 }
 int masg_fs2_phase_b(masg_ctx* c, void* stream, int T, float* mel, float* postnet_mel, uint8_t* mel_mask) {
@@ -279,7 +279,7 @@ int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, cons
     CUDA_OK(cudaMemcpyAsync(lens, h_src_lens, B * 8, cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaMemcpyAsync(spk, h_spk_emb, (size_t)B * 256 * 4, cudaMemcpyHostToDevice, s));
     int64_t tmax = 0;
-    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, pitch, energy, logd, drnd, mel_lens, nullptr, &tmax);
+    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens, nullptr, &tmax);
     MASG_CHECK(tmax > 0, "no frames to synthesise (all durations are zero)");
     MASG_CHECK(tmax <= t_cap, "T_max=%lld exceeds t_cap=%d", (long long)tmax, t_cap);
     int T = (int)tmax;

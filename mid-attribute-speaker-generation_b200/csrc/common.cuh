@@ -184,7 +184,7 @@ void fs2_commit(masg_ctx* c, cudaStream_t s);
 void hifigan_commit(masg_ctx* c, cudaStream_t s);
 void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
                  const int64_t* src_lens, int B, int L, const float* spk, float p_ctl, float e_ctl, float d_ctl,
-                 const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded,
-                 int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax);
+                 const float* d_target, const float* p_target, const float* e_target, float* pitch, float* energy, float* log_d,
+                 float* d_rounded, int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax);
 void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, uint8_t* mel_mask);
 void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16);

@@ -261,8 +261,8 @@ static void predictor_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const Predicto
 
 void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
                  const int64_t* src_lens, int B, int L, const float* spk, float p_ctl, float e_ctl, float d_ctl,
-                 const float* d_target, float* pitch, float* energy, float* log_d, float* d_rounded,
-                 int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax) {
+                 const float* d_target, const float* p_target, const float* e_target, float* pitch, float* energy, float* log_d,
+                 float* d_rounded, int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax) {
     MASG_CHECK(c->fs2_ready, "FastSpeech2 weights not committed (call masg_fs2_commit)");
     MASG_CHECK(B > 0 && L > 0, "empty batch B=%d L=%d", B, L);
     MASG_CHECK(accents != nullptr, "accents is required (transformer/Models.py:101 would raise on None)");
@@ -290,10 +290,11 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
         predictor_f32(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
     };
     predict(0, 1.0f, log_d);
-    predict(1, p_ctl, pitch);
-    launch_bucket_add(c, s, pitch, c->pitch_bins, 255, c->pitch_emb, (int64_t)rows, 256, x, nullptr);
-    predict(2, p_ctl, energy);                                                  // p_control, sic (modules.py:123-125)
-    launch_bucket_add(c, s, energy, c->energy_bins, 255, c->energy_emb, (int64_t)rows, 256, x, nullptr);
+    // with a target the embedding comes from bucketize(target) and the prediction is returned unscaled (modules.py:80-100)
+    predict(1, p_target ? 1.0f : p_ctl, pitch);
+    launch_bucket_add(c, s, p_target ? p_target : pitch, c->pitch_bins, 255, c->pitch_emb, (int64_t)rows, 256, x, nullptr);
+    predict(2, e_target ? 1.0f : p_ctl, energy);                                // p_control, sic (modules.py:123-125)
+    launch_bucket_add(c, s, e_target ? e_target : energy, c->energy_bins, 255, c->energy_emb, (int64_t)rows, 256, x, nullptr);
     if (d_target) CUDA_OK(cudaMemcpyAsync(c->d_rounded_dev, d_target, rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
     else launch_duration(c, s, log_d, d_ctl, (int64_t)rows, c->d_rounded_dev);
     if (d_rounded) CUDA_OK(cudaMemcpyAsync(d_rounded, c->d_rounded_dev, rows * sizeof(float), cudaMemcpyDeviceToDevice, s));

@@ -220,8 +220,8 @@ class FastSpeech2(nn.Module):
     # ---- the hot path -----------------------------------------------------------------------------
     def _synth(self, texts, src_lens, max_src_len, speaker_emb, accents, p_control, e_control, d_control, d_targets,
                max_mel_len, mels, p_targets, e_targets):
-        if mels is not None or p_targets is not None or e_targets is not None:
-            raise NotImplementedError("teacher-forced mels/pitch/energy targets are training-path inputs (out of scope)")
+        if mels is not None:
+            raise NotImplementedError("ground-truth mels are a training-path input (out of scope)")
         if self.training:
             raise RuntimeError("training mode is not supported (inference-only path); call .eval()")
         ctx = self._context()
@@ -246,13 +246,20 @@ class FastSpeech2(nn.Module):
         log_d = torch.empty(B, L, **f32); d_rounded = torch.empty(B, L, **f32)
         mel_lens = torch.empty(B, dtype=torch.int64, device=dev)
         src_mask = torch.empty(B, L, dtype=torch.uint8, device=dev)
-        d_t = None
+        d_t = p_t = e_t = None
         if d_targets is not None:
             d_t = d_targets.to(**f32).contiguous()
+        if p_targets is not None:                     # teacher-forced pitch / energy (model/modules.py:80-100)
+            p_t = p_targets.to(**f32).contiguous()
+        if e_targets is not None:
+            e_t = e_targets.to(**f32).contiguous()
+        for t_ in (d_t, p_t, e_t):
+            if t_ is not None and tuple(t_.shape) != (B, L):
+                raise ValueError("duration / pitch / energy targets must be [B, L] (phoneme level)")
         tmax = ctypes.c_int64(0)
         ctx.check(ctx.lib.masg_fs2_phase_a(
             ctx.h, ctx.stream(), _lib.ptr(texts), _lib.ptr(accents), acc1d, _lib.ptr(lens), B, L, _lib.ptr(spk),
-            float(p_control), float(e_control), float(d_control), _lib.ptr(d_t), _lib.ptr(pitch), _lib.ptr(energy),
+            float(p_control), float(e_control), float(d_control), _lib.ptr(d_t), _lib.ptr(p_t), _lib.ptr(e_t), _lib.ptr(pitch), _lib.ptr(energy),
             _lib.ptr(log_d), _lib.ptr(d_rounded), _lib.ptr(mel_lens), _lib.ptr(src_mask), ctypes.byref(tmax)), "masg_fs2_phase_a")
         T = int(max_mel_len) if max_mel_len is not None else int(tmax.value)
         if T <= 0:

@@ -73,6 +73,50 @@ def main():
     barycenter(ref)
 
 
+def frontend_fixture():
+    """tests/golden/frontend_jsut.npz: the reference's own tokenisation (pp_symbols -> openjtalk2julius -> symbol_to_id /
+    accent_to_id, synthesize.py:96-101,215-234) of every 80th utterance of the vendored jsut-lab full-context labels
+    (MIT-licensed label data, jsut-lab/LICENSE.md), with the symbol inventory (text/symbols.py) it was run with; and
+    tests/golden/fs2_jsut.npz: the reference FastSpeech2 on a ragged batch of four of those real (phoneme, accent) sequences."""
+    import glob
+    ref_import.load()
+    from prepare_tg_accent_jsut import pp_symbols
+    from convert_label import openjtalk2julius
+    from text import symbols
+    files = sorted(glob.glob(os.path.join(ref_import.REF_ROOT, "jsut-lab", "*", "lab", "*.lab")))[::80]
+    sym2id = {s_: i for i, s_ in enumerate(symbols)}
+    acc2id = {"0": 0, "[": 1, "]": 2, "#": 3}
+    labels, ids, accs, names = [], [], [], []
+    for f in files:
+        lab = [ln.strip().rsplit(None, 1)[-1] for ln in open(f) if ln.strip()]
+        ph, ac = pp_symbols(lab)
+        ph = [openjtalk2julius(p_) for p_ in ph if p_ != ""]
+        labels.append("\n".join(lab)); names.append(os.path.basename(f))
+        ids.append(np.array([sym2id[p_] for p_ in ph], dtype=np.int64)); accs.append(np.array([acc2id[a] for a in ac], dtype=np.int64))
+    lens = np.array([len(x) for x in ids], dtype=np.int64)
+    L = int(lens.max())
+    pad = lambda rows: np.stack([np.pad(r, (0, L - len(r))) for r in rows])
+    np.savez_compressed(os.path.join(OUT, "frontend_jsut.npz"), symbols=np.array(symbols), names=np.array(names), labels=np.array(labels),
+                        texts=pad(ids), accents=pad(accs), src_lens=lens)
+    print("frontend fixture:", len(files), "utterances, lengths", lens.min(), "-", lens.max())
+    # FastSpeech2 on real sequences: the longest, the shortest and two mid-length utterances of the sample
+    order = np.argsort(-lens)
+    pick = [int(order[0]), int(order[len(order) // 3]), int(order[2 * len(order) // 3]), int(order[-1])]
+    texts = torch.from_numpy(pad(ids)[pick]); accents = torch.from_numpy(pad(accs)[pick]); src_lens = torch.from_numpy(lens[pick])
+    sd = syn.make_fs2_state_dict(seed=11, duration_mode="spread")
+    ref = ref_import.build_fs2(sd, syn.speakers_json(), syn.STATS_JSON)
+    torch.manual_seed(5)
+    meta = torch.tensor([syn.META_COMBOS[i % 4] for i in range(4)], dtype=torch.float32)
+    emb = ref.speaker_gen(meta)
+    with torch.no_grad():
+        out = ref.synthesize_from_speaker_emb(None, texts, src_lens, L, accents=accents, speaker_emb=emb)
+    np.savez_compressed(os.path.join(OUT, "fs2_jsut.npz"), texts=texts.numpy(), accents=accents.numpy(), src_lens=src_lens.numpy(),
+                        speaker_emb=emb.numpy(), p_control=1.0, d_control=1.0, weights_seed=11, duration_mode="spread", picked=np.array(pick),
+                        mel=out[0].numpy(), postnet_mel=out[1].numpy(), pitch=out[2].numpy(), energy=out[3].numpy(), log_d=out[4].numpy(),
+                        d_rounded=out[5].numpy(), src_mask=out[6].numpy(), mel_mask=out[7].numpy(), mel_lens=out[9].numpy())
+    print("fs2_jsut: lens", src_lens.tolist(), "T =", out[0].shape[1], "mel_lens", out[9].tolist())
+
+
 BARY_RATE = [0.5, 0.25, 0.125, 0.125]      # sums to 1 exactly in floating point (distributions.py:112 asserts equality)
 
 
@@ -93,5 +137,7 @@ def barycenter(ref=None):
 if __name__ == "__main__":
     if "--barycenter" in sys.argv:
         barycenter()
+    elif "--frontend" in sys.argv:
+        frontend_fixture()
     else:
         main()

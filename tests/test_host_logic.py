@@ -160,19 +160,23 @@ def test_speaker_embedding_artefacts_round_trip(tmp_path):
 
 
 def test_bench_reference_arm_prints_the_contract_line():
-    """bench.py --impl reference (the CPU oracle port timed on the host cores) prints one JSON line with the driver's keys;
+    """bench.py --impl reference (the unmodified reference when a tree is present, else the CPU oracle port, timed on the host cores) prints one JSON line with the driver's keys;
     the sharded workloads are selectable without a GPU being touched at argument-parsing time."""
     import json
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--ref-sample", "1",
+                          "--latency-reps", "1"],
                          capture_output=True, text=True, timeout=600, cwd=root)
     assert out.returncode == 0, out.stderr[-2000:]
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["unit"] == "audio-s/s" and line["higher_is_better"] is True
-    assert line["value"] > 0 and line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["value"] > 0 and line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert line["gpu_launches"] == 0 and "C3" in line["config"]["workload"]
+    import bench
+    assert line["config"] == bench.c3_config(1)                              # the reference arm runs on OUR arm's config object
+    assert line["cpu_baseline"]["c1_latency_p50_ms"]["value"] > 0 and line["cpu_baseline"]["c2_latency_p50_ms"]["value"] > 0
     helptext = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--help"], capture_output=True, text=True, timeout=600, cwd=root).stdout
     assert "--workload" in helptext and "c4" in helptext and "c5" in helptext

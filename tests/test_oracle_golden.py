@@ -113,3 +113,18 @@ def test_restatement_matches_live_reference():
     from transformer.Models import get_sinusoid_encoding_table
     assert torch.equal(get_sinusoid_encoding_table(1200, 256), restate.sinusoid_table(1200))
     assert torch.equal(get_sinusoid_encoding_table(1200, 256), syn.sinusoid_table(1200))
+
+
+def test_fs2_restatement_matches_reference_golden_on_real_sequences(golden_dir):
+    """fs2_jsut.npz: the reference on four real (phoneme, accent) sequences tokenised from the vendored jsut-lab labels."""
+    g = _load(golden_dir, "fs2_jsut")
+    sd = syn.make_fs2_state_dict(seed=int(g["weights_seed"]), duration_mode=str(g["duration_mode"]))
+    texts, acc, lens = (torch.from_numpy(g[k]) for k in ("texts", "accents", "src_lens"))
+    out = restate.fs2_forward(sd, texts, acc, lens, texts.shape[1], torch.from_numpy(g["speaker_emb"]))
+    assert torch.equal(out[9], torch.from_numpy(g["mel_lens"])) and torch.equal(out[5], torch.from_numpy(g["d_rounded"]))
+    for i, key in ((0, "mel"), (1, "postnet_mel"), (2, "pitch"), (3, "energy"), (4, "log_d")):
+        np.testing.assert_allclose(out[i].numpy(), g[key], atol=3e-5, rtol=0)
+    # teacher-forced targets restated as the reference does (modules.py:80-100): forcing the reference's own outputs changes nothing
+    out_f = restate.fs2_forward(sd, texts, acc, lens, texts.shape[1], torch.from_numpy(g["speaker_emb"]), p_target=torch.from_numpy(g["pitch"]),
+                                e_target=torch.from_numpy(g["energy"]), d_target=torch.from_numpy(g["d_rounded"]))
+    np.testing.assert_allclose(out_f[1].numpy(), g["postnet_mel"], atol=3e-5, rtol=0)
