@@ -112,6 +112,14 @@ int masg_attention_planar(masg_ctx* ctx, void* stream, const void* qkv16, const 
 int masg_hifigan_forward(masg_ctx* ctx, void* stream, const float* mel, int mel_is_channels_last, int B, int T,
                          float* wav, int16_t* wav_i16);
 
+/* hifigan.Generator.forward + vocoder_infer's int16 cast AND its per-utterance trim (utils/model.py:82-90), fused into the
+ * generator's last kernel: row b keeps its first mel_lens[b] * hop samples and the rows are written back to back.
+ * mel_lens: device int64 [B]; offsets: device int64 [B + 1] out (offsets[b] = first sample of row b, offsets[B] = total);
+ * wav_packed: device int16 with room for hop * sum(mel_lens) samples.  One D2H copy of offsets[B] samples then moves
+ * exactly the valid audio. */
+int masg_hifigan_forward_packed(masg_ctx* ctx, void* stream, const float* mel, int mel_is_channels_last, int B, int T,
+                                const int64_t* mel_lens, int hop, int16_t* wav_packed, int64_t* offsets);
+
 /* SpeakerMetaEncoder.forward (model/fastspeech2.py:332-341): meta fp32 [N,4] → pi [N,3], mu/sigma [N,3,256]. */
 int masg_gmm_params(masg_ctx* ctx, void* stream, const float* meta, int N, float* pi, float* mu, float* sigma);
 /* MixtureSameFamily.sample() (model/fastspeech2.py:176-180, distributions.py .sample()): per row n draw
@@ -144,6 +152,14 @@ int masg_synthesize_host(masg_ctx* ctx, void* stream, const int64_t* h_texts, co
                          const int64_t* h_src_lens, int B, int L, const float* h_spk_emb,
                          float p_ctl, float e_ctl, float d_ctl, int t_cap,
                          int16_t* h_wav_i16, int64_t* h_mel_lens, int64_t* h_tmax);
+
+/* The same with the trim of utils/model.py:88-90 done on the device: h_wav_packed receives the utterances back to back (row b =
+ * h_mel_lens[b] * 256 samples starting at h_offsets[b]; h_offsets has B + 1 entries, the last is the total) in ONE D2H copy of
+ * exactly the valid samples; cap_samples = capacity of h_wav_packed in samples (error if the batch produces more). */
+int masg_synthesize_host_packed(masg_ctx* ctx, void* stream, const int64_t* h_texts, const int64_t* h_accents,
+                                const int64_t* h_src_lens, int B, int L, const float* h_spk_emb,
+                                float p_ctl, float e_ctl, float d_ctl, int64_t cap_samples,
+                                int16_t* h_wav_packed, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax);
 
 /* One Conv1d (torch.nn.Conv1d as used throughout transformer/SubLayers.py:72-83, model/modules.py:253-296,
  * hifigan/models.py:24-91) or, with stride_transposed = u > 0, one ConvTranspose1d(k = 2u, stride u,

@@ -10,7 +10,7 @@ _here = os.path.dirname(os.path.abspath(__file__))
 if _here not in sys.path:
     sys.path.insert(0, _here)
 _pkg = importlib.import_module(_REAL)
-for _sub in ("synthetic", "_lib", "fastspeech2", "hifigan", "distributions", "synth", "build", "frontend"):
+for _sub in ("synthetic", "_lib", "fastspeech2", "hifigan", "distributions", "wavio", "synth", "build", "frontend", "tools"):
     _m = importlib.import_module(_REAL + "." + _sub)
     sys.modules["masg_b200." + _sub] = _m
 sys.modules["masg_b200"] = _pkg

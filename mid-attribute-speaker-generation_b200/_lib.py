@@ -33,12 +33,15 @@ SIGNATURES = {
     "masg_length_regulate": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P, P, P]),
     "masg_bucketize_embed_add": (c_int, [P, P, P, P, c_int, P, c_i64, c_int, P, P]),
     "masg_hifigan_forward": (c_int, [P, P, P, c_int, c_int, c_int, P, P]),
+    "masg_hifigan_forward_packed": (c_int, [P, P, P, c_int, c_int, c_int, P, c_int, P, P]),
     "masg_gmm_params": (c_int, [P, P, P, c_int, P, P, P]),
     "masg_gmm_sample": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_u64, c_u64, P, P, P, P]),
     "masg_gmm_interpolate": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, P, P, P, P]),
     "masg_gmm_barycenter": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P]),
     "masg_synthesize_host": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_int, P, P,
                                      ctypes.POINTER(c_i64)]),
+    "masg_synthesize_host_packed": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_i64, P, P, P,
+                                            ctypes.POINTER(c_i64)]),
     "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, c_int, P,
                             ctypes.POINTER(c_float)]),
     "masg_attention": (c_int, [P, P, P, P, c_int, c_int, P]),

@@ -39,10 +39,12 @@ int masg_ctx_create(int device, int precision, masg_ctx** out) {
         CUDA_OK(cudaSetDevice(device));
         masg_ctx* c = new masg_ctx();
         c->device = device; c->precision = precision;
-        CUDA_OK(cudaMallocHost(&c->h_pinned, 64 * sizeof(int64_t)));
+        c->n_sm = prop.multiProcessorCount;
         *out = c;
         return 0;
     } catch (const MasgError& e) { g_err = e.msg; return 1; }
+      catch (const std::exception& e) { g_err = e.what(); return 2; }
+      catch (...) { g_err = "unknown exception in masg_ctx_create"; return 3; }
 }
 
 static void free_owned(masg_ctx* c) {
@@ -59,6 +61,7 @@ void masg_ctx_destroy(masg_ctx* c) {
     c->arena.release(); c->arena_b.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->io_buf) cudaFree(c->io_buf);
+    if (c->out_buf) cudaFree(c->out_buf);
     delete c;
 }
 
@@ -135,6 +138,22 @@ int masg_hifigan_forward(masg_ctx* c, void* stream, const float* mel, int mel_is
     API_BEGIN(c)
     MASG_CHECK(mel && (wav || wav_i16), "null argument");
     hifigan_forward(c, (cudaStream_t)stream, mel, mel_is_channels_last, B, T, wav, wav_i16);
+    API_END(c)
+}
+
+int masg_hifigan_forward_packed(masg_ctx* c, void* stream, const float* mel, int mel_is_channels_last, int B, int T,
+                                const int64_t* mel_lens, int hop, int16_t* wav_packed, int64_t* offsets) {
+    API_BEGIN(c)
+    MASG_CHECK(mel && mel_lens && wav_packed && offsets && hop > 0, "null argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    // offsets [B + 1] are the caller's; the per-row lengths live in the I/O staging buffer (the arenas are reset by the forward)
+    if (c->io_cap < (size_t)B * 8 + 256) {
+        if (c->io_buf) { CUDA_OK(cudaStreamSynchronize(s)); cudaFree(c->io_buf); c->io_buf = nullptr; c->io_cap = 0; }
+        CUDA_OK(cudaMalloc(&c->io_buf, (size_t)B * 8 + 4096)); c->io_cap = (size_t)B * 8 + 4096;
+    }
+    int64_t* len = (int64_t*)c->io_buf;
+    launch_wav_offsets(c, s, mel_lens, B, hop, offsets, len);
+    hifigan_forward(c, s, mel, mel_is_channels_last, B, T, nullptr, wav_packed, len, offsets);
     API_END(c)
 }
 
@@ -253,24 +272,28 @@ int masg_gmm_barycenter(masg_ctx* c, void* stream, const float* pi, const float*
     API_END(c)
 }
 
-int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
-                         int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int t_cap,
-                         int16_t* h_wav_i16, int64_t* h_mel_lens, int64_t* h_tmax) {
-    API_BEGIN(c)
-    cudaStream_t s = (cudaStream_t)stream;
-    MASG_CHECK(h_texts && h_accents && h_src_lens && h_spk_emb && h_wav_i16, "null argument");
-    // the I/O staging area is a growth-only buffer of its own (arena/arena_b are reset by the phases)
-    size_t rows = (size_t)B * L;
-    size_t need_in = rows * 8 * 2 + B * 8 * 2 + (size_t)B * 256 * 4 + rows * 4 * 4 + 4096;
-    size_t need = need_in + ((size_t)B * t_cap * 80 * 4) * 2 + (size_t)B * t_cap * 256 * 2 + 4096;
-    if (c->io_cap < need) {
-        if (c->io_buf) { CUDA_OK(cudaStreamSynchronize(s)); cudaFree(c->io_buf); c->io_buf = nullptr; }
-        CUDA_OK(cudaMalloc(&c->io_buf, need)); c->io_cap = need;
+// shared body of the two host-buffer entry points.  packed == 0: rows of stride 256 * t_cap in h_wav (every row is copied up to
+// T_max frames).  packed != 0: the vocoder's last kernel writes the trimmed rows back to back (row b = its mel_len[b] * 256
+// samples at h_offsets[b]) and ONE D2H copy moves exactly the valid samples.
+static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
+                            int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int packed, int64_t cap,
+                            int16_t* h_wav, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax) {
+    MASG_CHECK(h_texts && h_accents && h_src_lens && h_spk_emb && h_wav, "null argument");
+    MASG_CHECK(B > 0 && L > 0, "empty batch B=%d L=%d", B, L);
+    // two growth-only staging buffers of their own (arena / arena_b are reset by the phases): io_buf for the inputs and phase A's
+    // small outputs (sized by B and L, before anything is enqueued), out_buf for mel / postnet mel / audio (sized once T_max and
+    // the lengths are known, right after phase A's sync — growing it there costs no extra synchronisation)
+    const size_t rows = (size_t)B * L;
+    const size_t need_in = rows * 8 * 2 + (size_t)B * 8 * 4 + 8 + (size_t)B * 256 * 4 + rows * 4 * 4 + 8192;
+    if (c->io_cap < need_in) {
+        if (c->io_buf) { CUDA_OK(cudaStreamSynchronize(s)); cudaFree(c->io_buf); c->io_buf = nullptr; c->io_cap = 0; }
+        CUDA_OK(cudaMalloc(&c->io_buf, need_in * 2)); c->io_cap = need_in * 2;
     }
     char* p = (char*)c->io_buf;
     auto take = [&](size_t bytes) { void* r = p; p += (bytes + 255) & ~size_t(255); return r; };
     int64_t* texts = (int64_t*)take(rows * 8); int64_t* acc = (int64_t*)take(rows * 8);
     int64_t* lens = (int64_t*)take(B * 8); int64_t* mel_lens = (int64_t*)take(B * 8);
+    int64_t* woff = (int64_t*)take((size_t)(B + 1) * 8); int64_t* wlen = (int64_t*)take(B * 8);
     float* spk = (float*)take((size_t)B * 256 * 4);
     float* pitch = (float*)take(rows * 4); float* energy = (float*)take(rows * 4); float* logd = (float*)take(rows * 4);
     float* drnd = (float*)take(rows * 4);
@@ -279,18 +302,54 @@ int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, cons
     CUDA_OK(cudaMemcpyAsync(lens, h_src_lens, B * 8, cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaMemcpyAsync(spk, h_spk_emb, (size_t)B * 256 * 4, cudaMemcpyHostToDevice, s));
     int64_t tmax = 0;
-    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens, nullptr, &tmax);
+    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
+                nullptr, &tmax);
     MASG_CHECK(tmax > 0, "no frames to synthesise (all durations are zero)");
-    MASG_CHECK(tmax <= t_cap, "T_max=%lld exceeds t_cap=%d", (long long)tmax, t_cap);
-    int T = (int)tmax;
+    const int T = (int)tmax;
+    // phase A's single sync left [mel_lens | T_max] in the pinned scratch: the host knows every row's length from here on
+    int64_t total = 0;
+    for (int b = 0; b < B; ++b) { if (h_mel_lens) h_mel_lens[b] = c->h_pinned[b]; if (h_offsets) h_offsets[b] = total * 256; total += std::max<int64_t>(c->h_pinned[b], 0); }
+    if (h_offsets) h_offsets[B] = total * 256;
+    if (packed) MASG_CHECK(total * 256 <= cap, "the batch produces %lld samples, capacity is %lld", (long long)(total * 256), (long long)cap);
+    else MASG_CHECK(tmax <= cap, "T_max=%lld exceeds t_cap=%lld", (long long)tmax, (long long)cap);
+    const size_t out_bytes = ((size_t)B * T * 80 * 4 + 256) * 2 + (packed ? (size_t)total * 512 : (size_t)B * T * 512) + 1024;
+    if (c->out_cap < out_bytes) {                            // the stream is idle here (phase A just synchronised)
+        if (c->out_buf) { cudaFree(c->out_buf); c->out_buf = nullptr; c->out_cap = 0; }
+        CUDA_OK(cudaMalloc(&c->out_buf, out_bytes + out_bytes / 4)); c->out_cap = out_bytes + out_bytes / 4;
+    }
+    p = (char*)c->out_buf;
     float* mel = (float*)take((size_t)B * T * 80 * 4); float* post = (float*)take((size_t)B * T * 80 * 4);
-    int16_t* w16 = (int16_t*)take((size_t)B * T * 256 * 2);
     fs2_phase_b(c, s, T, mel, post, nullptr);
-    hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
-    CUDA_OK(cudaMemcpy2DAsync(h_wav_i16, (size_t)t_cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
-    if (h_mel_lens) CUDA_OK(cudaMemcpyAsync(h_mel_lens, mel_lens, B * 8, cudaMemcpyDeviceToHost, s));
+    if (packed) {
+        int16_t* w16 = (int16_t*)take((size_t)total * 512);
+        launch_wav_offsets(c, s, mel_lens, B, 256, woff, wlen);
+        hifigan_forward(c, s, post, 1, B, T, nullptr, w16, wlen, woff);
+        CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, s));
+    } else {
+        int16_t* w16 = (int16_t*)take((size_t)B * T * 256 * 2);
+        hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
+        CUDA_OK(cudaMemcpy2DAsync(h_wav, (size_t)cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
+    }
     CUDA_OK(cudaStreamSynchronize(s));
     if (h_tmax) *h_tmax = tmax;
+}
+
+int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
+                         int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int t_cap,
+                         int16_t* h_wav_i16, int64_t* h_mel_lens, int64_t* h_tmax) {
+    API_BEGIN(c)
+    synthesize_host(c, (cudaStream_t)stream, h_texts, h_accents, h_src_lens, B, L, h_spk_emb, p_ctl, e_ctl, d_ctl, 0, t_cap, h_wav_i16,
+                    nullptr, h_mel_lens, h_tmax);
+    API_END(c)
+}
+
+int masg_synthesize_host_packed(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
+                                int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int64_t cap_samples,
+                                int16_t* h_wav_packed, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax) {
+    API_BEGIN(c)
+    MASG_CHECK(h_offsets != nullptr, "null h_offsets");
+    synthesize_host(c, (cudaStream_t)stream, h_texts, h_accents, h_src_lens, B, L, h_spk_emb, p_ctl, e_ctl, d_ctl, 1, cap_samples,
+                    h_wav_packed, h_offsets, h_mel_lens, h_tmax);
     API_END(c)
 }
 
@@ -345,7 +404,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
     if (ms_out) *ms_out = ms / reps;
     if (getenv("MASG_TC_DEBUG") && (atoi(getenv("MASG_TC_DEBUG")) & 16)) {
         unsigned long long st[16]; tc_debug_stats(st, true);
-        const double n = 148.0 * (reps + 1);
+        const double n = (double)c->n_sm * (reps + 1);
         fprintf(stderr, "  [tc stats, kcycles per CTA per launch] issuer: wait acc_empty %.0f a_full %.0f w_full %.0f of total %.0f | epilogue: wait acc_full %.0f of %.0f | copy warp wait a_empty %.0f | weight warp wait w_empty %.0f | worker wait a_raw %.0f\n",
                 st[0] / n / 1e3, st[1] / n / 1e3, st[2] / n / 1e3, st[3] / n / 1e3, st[4] / n / 1e3, st[5] / n / 1e3, st[6] / n / 1e3, st[7] / n / 1e3, st[8] / n / 1e3);
     }

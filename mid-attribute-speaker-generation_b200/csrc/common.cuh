@@ -70,7 +70,7 @@ struct Predictor {
 };
 
 struct masg_ctx {
-    int device = 0, precision = 0;
+    int device = 0, precision = 0, n_sm = 148;
     std::string err;
     int64_t launches = 0;
     // per-launch device timing of the dense-contraction kernel (masg_profile): event pairs + algorithmic FLOPs
@@ -95,8 +95,9 @@ struct masg_ctx {
     const int64_t* src_lens_dev = nullptr;
     float* tap_enc = nullptr; float* tap_lr = nullptr; float* tap_dec = nullptr; int tap_T = 0;
     Arena arena_b;                    // phase-B / vocoder workspace (arena holds phase-A state)
-    int64_t* h_pinned = nullptr;      // pinned host scratch (T_max etc.)
-    void* io_buf = nullptr; size_t io_cap = 0;   // device staging of masg_synthesize_host
+    int64_t* h_pinned = nullptr; int h_pinned_n = 0;   // pinned host scratch: [mel_lens (B) | T_max] of the last phase A
+    void* io_buf = nullptr; size_t io_cap = 0;   // device staging of the host-buffer entry points: inputs + phase-A outputs
+    void* out_buf = nullptr; size_t out_cap = 0; // ... and mel / postnet mel / audio (sized after phase A)
     // ---- HiFi-GAN ----
     ConvDesc hg_pre, hg_ups[4], hg_c1[12][3], hg_c2[12][3];
     const float* hg_post_w = nullptr; float hg_post_b = 0.f;   // [7][32] fp32
@@ -148,8 +149,10 @@ void launch_attention_tc(masg_ctx* c, cudaStream_t s, const float* qkv, const in
 // planar fp16 in ([B][96][S][8]) and out ([B][32][S][8]): attn_f16p.cu
 void launch_attention_f16p(masg_ctx* c, cudaStream_t s, const void* qkv, const int64_t* lens, int B, int S, void* out);
 void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int B, int C, int T, float* out_btc);
+// row_len / row_off (nullable, device int64 [B]): store only the first row_len[b] samples of row b, at wav + row_off[b]
 void launch_conv_post(masg_ctx* c, cudaStream_t s, const void* x, int x_bf16, const float* w, float bias, int B, long S,
-                      float in_slope, float* wav, int16_t* wav16);
+                      float in_slope, float* wav, int16_t* wav16, const int64_t* row_len = nullptr, const int64_t* row_off = nullptr);
+void launch_wav_offsets(masg_ctx* c, cudaStream_t s, const int64_t* mel_lens, int B, int hop, int64_t* off /*[B+1]*/, int64_t* len /*[B], nullable*/);
 void launch_pos_table(masg_ctx* c, cudaStream_t s, int n, float* out);
 void launch_add2(masg_ctx* c, cudaStream_t s, const float* a, const float* b, float* out, int64_t n);
 void launch_gmm_params(masg_ctx* c, cudaStream_t s, const float* meta, int N, float* pi, float* mu, float* sigma);
@@ -187,4 +190,6 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
                  const float* d_target, const float* p_target, const float* e_target, float* pitch, float* energy, float* log_d,
                  float* d_rounded, int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax);
 void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, uint8_t* mel_mask);
-void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16);
+// row_len / row_off (nullable, device int64 [B]): per-utterance trim + packed placement of the output rows (launch_conv_post)
+void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16,
+                     const int64_t* row_len = nullptr, const int64_t* row_off = nullptr);

@@ -903,7 +903,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
         if (cap > 0 && d.taps == 1) msub = std::min(msub, cap);
     }
     const int ntiles_n = d.N / NT;
-    while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < 148) msub /= 2;
+    while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < c->n_sm) msub /= 2;
     int KC = 0;
     if (tma_in) {
         // one [KC/8][Rb][8] block per tile (its msub*128 rows + the halo); sub-tile ms starts 128 rows further down; every
@@ -1009,9 +1009,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)a.w_stages * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
     MASG_CHECK(!tma_in || ((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
-    static int n_sm = 0;
-    if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
-    dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
+    dim3 grid(std::min(a.total_tiles, c->n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
 #define MASG_TC_CASE(NTV)                                                                       \
     case NTV: if (tma_in) launch_inst<NTV, true>(a, grid, smem, s); else launch_inst<NTV, false>(a, grid, smem, s); break;
     switch (NT) {

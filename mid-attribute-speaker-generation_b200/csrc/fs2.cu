@@ -301,9 +301,16 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
     launch_mel_lens(c, s, c->d_rounded_dev, B, L, c->mel_lens_dev, c->mel_lens_dev + B);
     if (mel_lens) CUDA_OK(cudaMemcpyAsync(mel_lens, c->mel_lens_dev, B * sizeof(int64_t), cudaMemcpyDeviceToDevice, s));
     if (h_tmax) {
-        CUDA_OK(cudaMemcpyAsync(c->h_pinned, c->mel_lens_dev + B, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        if (c->h_pinned_n < B + 1) {
+            if (c->h_pinned) cudaFreeHost(c->h_pinned);
+            c->h_pinned = nullptr; c->h_pinned_n = 0;
+            CUDA_OK(cudaMallocHost(&c->h_pinned, (size_t)(B + 1 + 64) * sizeof(int64_t)));
+            c->h_pinned_n = B + 1 + 64;
+        }
+        // [mel_lens (B) | T_max] in one copy: the host-buffer entry points size their trimmed D2H from the lengths
+        CUDA_OK(cudaMemcpyAsync(c->h_pinned, c->mel_lens_dev, (size_t)(B + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaStreamSynchronize(s));                                      // the single documented sync
-        *h_tmax = c->h_pinned[0];
+        *h_tmax = c->h_pinned[B];
     }
 }
 

@@ -108,7 +108,8 @@ static void convP(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const void* X,
     launch_conv(c, s, d, io);
 }
 
-static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT, int B, int T, float* wav, int16_t* w16) {
+static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT, int B, int T, float* wav, int16_t* w16,
+                                 const int64_t* row_len, const int64_t* row_off) {
     Arena& ar = c->arena_b;
     long S = T;
     bf16* x = ar.get<bf16>((size_t)B * S * 512);
@@ -145,10 +146,11 @@ static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT,
         }
         x = xs; S = So;
     }
-    launch_conv_post(c, s, x, 1, c->hg_post_w, c->hg_post_b, B, S, 1.0f, wav, w16);   // the leaky-relu is already applied
+    launch_conv_post(c, s, x, 1, c->hg_post_w, c->hg_post_b, B, S, 1.0f, wav, w16, row_len, row_off);   // the leaky-relu is already applied
 }
 
-void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16) {
+void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16,
+                     const int64_t* row_len, const int64_t* row_off) {
     MASG_CHECK(c->hg_ready, "HiFi-GAN weights not committed (call masg_hifigan_commit)");
     MASG_CHECK(B > 0 && T > 0, "empty vocoder input B=%d T=%d", B, T);
     const bool bf = c->precision == MASG_PREC_BF16;
@@ -161,7 +163,7 @@ void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int 
         launch_transpose_mel(c, s, mel, B, 80, T, t);
         melT = t;
     }
-    if (bf) { hifigan_forward_bf16(c, s, melT, B, T, wav, w16); return; }
+    if (bf) { hifigan_forward_bf16(c, s, melT, B, T, wav, w16, row_len, row_off); return; }
     long S = T;
     char* x = (char*)ar.alloc((size_t)B * S * 512 * esz);
     convS(c, s, c->hg_pre, melT, false, B, S, x, S, 512, ACT_NONE, 0.f, nullptr, nullptr, 1.f, (int)S);
@@ -192,5 +194,5 @@ void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int 
         }
         x = xs; S = So;
     }
-    launch_conv_post(c, s, x, bf, c->hg_post_w, c->hg_post_b, B, S, 0.01f, wav, w16);   // F.leaky_relu default slope (models.py:161)
+    launch_conv_post(c, s, x, bf, c->hg_post_w, c->hg_post_b, B, S, 0.01f, wav, w16, row_len, row_off);   // F.leaky_relu default slope (models.py:161)
 }

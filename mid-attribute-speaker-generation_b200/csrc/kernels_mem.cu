@@ -449,11 +449,14 @@ void launch_transpose_mel(masg_ctx* c, cudaStream_t s, const float* mel_bct, int
 template <bool XBF>
 __global__ void __launch_bounds__(256)
 k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias, long S, float slope,
-            float* __restrict__ wav, int16_t* __restrict__ wav16) {
+            float* __restrict__ wav, int16_t* __restrict__ wav16, const int64_t* __restrict__ row_len, const int64_t* __restrict__ row_off) {
     constexpr int XS = 36;                                   // row stride in floats: 16-byte aligned rows, conflict-free 128-bit accesses
     __shared__ __align__(16) float xs[262 * XS];
     __shared__ __align__(16) float ws[7 * 32];
     int b = blockIdx.y; long s0 = (long)blockIdx.x * 256;
+    const long n_valid = row_len ? min((long)row_len[b], S) : S;          // vocoder_infer's trim (utils/model.py:88-90), fused
+    if (s0 >= n_valid) return;
+    const long obase = row_off ? (long)row_off[b] : (long)b * S;
     int tid = threadIdx.x;
     if (tid < 224) ws[tid] = w[tid];
     if (XBF) {
@@ -497,7 +500,7 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
     }
     __syncthreads();
     long sidx = s0 + tid;
-    if (sidx >= S) return;
+    if (sidx >= n_valid) return;
     float acc = bias;
 #pragma unroll
     for (int j = 0; j < 7; ++j) {
@@ -510,85 +513,130 @@ k_conv_post(const void* __restrict__ xv, const float* __restrict__ w, float bias
         }
     }
     float y = tanhf(acc);
-    if (wav) wav[(long)b * S + sidx] = y;
-    if (wav16) wav16[(long)b * S + sidx] = (int16_t)__float2int_rz(y * 32768.0f);
+    if (wav) wav[obase + sidx] = y;
+    if (wav16) wav16[obase + sidx] = (int16_t)__float2int_rz(y * 32768.0f);
 }
-// Planar bf16 input (the bf16 graph): thread = (8-channel group g, 4 consecutive samples).  The CTA stages its 262 rows as raw
-// bf16 pieces (16 bytes = 8 channels of one sample, plane pitch 265 pieces so a quarter-warp's 128-bit reads cover all banks),
-// every thread keeps its 7 x 8 weights in registers, reads 10 pieces (1/3.5 of the shared-memory wavefronts of the
-// one-sample-per-thread form, which ran at the LDS limit: 0.445 ms for 629 MB) and the 4 group partials meet in two shuffles.
+// Planar bf16 input (the bf16 graph): thread = (8-channel group g, two runs of 4 consecutive samples, 256 samples apart).  The CTA
+// stages its 512 + 6 rows as raw bf16 pieces (16 bytes = 8 channels of one sample, plane pitch 521 pieces so a quarter-warp's
+// 128-bit reads cover all banks), reads 2 x 10 pieces per thread (1/2.8 of the shared-memory wavefronts of the one-sample-per-thread
+// form, which ran at the LDS limit) and the 4 group partials meet in two shuffles.  9 x 16-byte global loads per thread are in
+// flight before the first is used (33 KB per CTA); the 7 x 32 weights sit in shared memory (same-address broadcast within a
+// group) so that three CTAs (100 KB of loads in flight) fit an SM.
+// Output addressing (vocoder_infer's trim, utils/model.py:88-90, fused): row b is written at wav16 + row_off[b] (or b * S) and only
+// its first row_len[b] samples (or S) are stored — with offsets = prefix sums of the lengths this is the packed layout.
 template <bool ACT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 k_conv_post_planar(const bf16* __restrict__ x, const float* __restrict__ w, float bias, long S, float slope,
-                   float* __restrict__ wav, int16_t* __restrict__ wav16) {
-    constexpr int PP = 265;                                  // plane pitch in 16-byte pieces (== 1 mod 8)
+                   float* __restrict__ wav, int16_t* __restrict__ wav16, const int64_t* __restrict__ row_len,
+                   const int64_t* __restrict__ row_off) {
+    constexpr int TILE = 512, ROWS = TILE + 6, PP = 521;     // plane pitch in 16-byte pieces (== 1 mod 8)
     __shared__ uint4 xs[4 * PP];
-    const int b = blockIdx.y; const long s0 = (long)blockIdx.x * 256;
+    __shared__ __align__(16) float ws[7 * 32];
+    const int b = blockIdx.y; const long s0 = (long)blockIdx.x * TILE;
+    const long n_valid = row_len ? min((long)row_len[b], S) : S;
+    if (s0 >= n_valid) return;                               // the whole tile lies in the trimmed tail
     const int tid = threadIdx.x;
+    if (tid < 224) ws[tid] = w[tid];
     {
-        constexpr int NP = (262 * 4 + 255) / 256;
+        constexpr int NP = (ROWS * 4 + 255) / 256;
         uint4 u[NP];
 #pragma unroll
         for (int k = 0; k < NP; ++k) {
             const int i = tid + k * 256;
-            const int g = i / 262, r = i % 262;
+            const int g = i / ROWS, r = i % ROWS;
             const long srow = s0 + r - 3;
             u[k] = make_uint4(0u, 0u, 0u, 0u);
-            if (i < 262 * 4 && srow >= 0 && srow < S) u[k] = *reinterpret_cast<const uint4*>(x + (((long)b * 4 + g) * S + srow) * 8);
+            if (i < ROWS * 4 && srow >= 0 && srow < S) u[k] = *reinterpret_cast<const uint4*>(x + (((long)b * 4 + g) * S + srow) * 8);
         }
 #pragma unroll
         for (int k = 0; k < NP; ++k) {
             const int i = tid + k * 256;
-            if (i < 262 * 4) xs[(i / 262) * PP + i % 262] = u[k];
+            if (i < ROWS * 4) xs[(i / ROWS) * PP + i % ROWS] = u[k];
         }
     }
     const int g = tid & 3, og = tid >> 2;
-    float wr[7][8];
-#pragma unroll
-    for (int j = 0; j < 7; ++j) {
-        const float4 a = *reinterpret_cast<const float4*>(w + j * 32 + g * 8), c = *reinterpret_cast<const float4*>(w + j * 32 + g * 8 + 4);
-        wr[j][0] = a.x; wr[j][1] = a.y; wr[j][2] = a.z; wr[j][3] = a.w; wr[j][4] = c.x; wr[j][5] = c.y; wr[j][6] = c.z; wr[j][7] = c.w;
-    }
     __syncthreads();
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const long obase = row_off ? (long)row_off[b] : (long)b * S;
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint4 u = xs[g * PP + og * 4 + r];
-        const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
-        float f[8];
+    for (int run = 0; run < 2; ++run) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const int r0 = run * 256 + og * 4;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) { f[2 * q] = __uint_as_float(w4[q] << 16); f[2 * q + 1] = __uint_as_float(w4[q] & 0xffff0000u); }
+        for (int r = 0; r < 10; ++r) {
+            const uint4 u = xs[g * PP + r0 + r];
+            const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+            float f[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) if (ACT) f[q] = fmaxf(f[q], f[q] * slope);        // leaky-relu, 0 < slope < 1
+            for (int q = 0; q < 4; ++q) { f[2 * q] = __uint_as_float(w4[q] << 16); f[2 * q + 1] = __uint_as_float(w4[q] & 0xffff0000u); }
 #pragma unroll
-        for (int o = 0; o < 4; ++o) {
-            const int j = r - o;
-            if (j >= 0 && j < 7) {
+            for (int q = 0; q < 8; ++q) if (ACT) f[q] = fmaxf(f[q], f[q] * slope);    // leaky-relu, 0 < slope < 1
 #pragma unroll
-                for (int q = 0; q < 8; ++q) acc[o] += f[q] * wr[j][q];
+            for (int o = 0; o < 4; ++o) {
+                const int j = r - o;
+                if (j >= 0 && j < 7) {
+                    const float4 wa = *reinterpret_cast<const float4*>(&ws[j * 32 + g * 8]), wb = *reinterpret_cast<const float4*>(&ws[j * 32 + g * 8 + 4]);
+                    acc[o] += f[0] * wa.x; acc[o] += f[1] * wa.y; acc[o] += f[2] * wa.z; acc[o] += f[3] * wa.w;
+                    acc[o] += f[4] * wb.x; acc[o] += f[5] * wb.y; acc[o] += f[6] * wb.z; acc[o] += f[7] * wb.w;
+                }
             }
         }
-    }
 #pragma unroll
-    for (int o = 0; o < 4; ++o) {
-        acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], 1);
-        acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], 2);
+        for (int o = 0; o < 4; ++o) {
+            acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], 1);
+            acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], 2);
+        }
+        // lane g writes sample r0 + g
+        const float mine = g == 0 ? acc[0] : g == 1 ? acc[1] : g == 2 ? acc[2] : acc[3];
+        const long sidx = s0 + r0 + g;
+        if (sidx < n_valid) {
+            const float y = tanhf(mine + bias);
+            if (wav) wav[obase + sidx] = y;
+            if (wav16) wav16[obase + sidx] = (int16_t)__float2int_rz(y * 32768.0f);
+        }
     }
-    // lane g writes sample og*4 + g
-    const float mine = g == 0 ? acc[0] : g == 1 ? acc[1] : g == 2 ? acc[2] : acc[3];
-    const long sidx = s0 + og * 4 + g;
-    if (sidx >= S) return;
-    const float y = tanhf(mine + bias);
-    if (wav) wav[(long)b * S + sidx] = y;
-    if (wav16) wav16[(long)b * S + sidx] = (int16_t)__float2int_rz(y * 32768.0f);
+}
+// packed-output offsets: off[b] = hop * sum_{i<b} max(mel_lens[i], 0), off[B] = total; len[b] = hop * mel_lens[b]   (one block)
+__global__ void k_wav_offsets(const int64_t* __restrict__ mel_lens, int B, int hop, int64_t* __restrict__ off, int64_t* __restrict__ len) {
+    __shared__ long part[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    long carry = 0;
+    for (int base = 0; base < B; base += blockDim.x) {
+        const int i = base + tid;
+        const long v = i < B ? max((long)mel_lens[i], 0L) * hop : 0;
+        long sc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const long n = __shfl_up_sync(FULL, sc, o); if (lane >= o) sc += n; }
+        if (lane == 31) part[wid] = sc;
+        __syncthreads();
+        if (wid == 0) {
+            long p = lane < (int)(blockDim.x >> 5) ? part[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const long n = __shfl_up_sync(FULL, p, o); if (lane >= o) p += n; }
+            part[lane] = p;
+        }
+        __syncthreads();
+        const long incl = carry + sc + (wid > 0 ? part[wid - 1] : 0);
+        if (i < B) { off[i] = incl - v; if (len) len[i] = v; }
+        carry += part[(blockDim.x >> 5) - 1];
+        __syncthreads();
+    }
+    if (tid == 0) off[B] = carry;
+}
+void launch_wav_offsets(masg_ctx* c, cudaStream_t s, const int64_t* mel_lens, int B, int hop, int64_t* off, int64_t* len) {
+    k_wav_offsets<<<1, 256, 0, s>>>(mel_lens, B, hop, off, len);
+    c->launches++;
 }
 void launch_conv_post(masg_ctx* c, cudaStream_t s, const void* x, int x_bf16, const float* w, float bias, int B, long S,
-                      float in_slope, float* wav, int16_t* wav16) {
-    dim3 grid(cdiv(S, 256), B);
-    if (x_bf16 && in_slope == 1.f) k_conv_post_planar<false><<<grid, 256, 0, s>>>((const bf16*)x, w, bias, S, in_slope, wav, wav16);
-    else if (x_bf16 && in_slope > 0.f && in_slope < 1.f) k_conv_post_planar<true><<<grid, 256, 0, s>>>((const bf16*)x, w, bias, S, in_slope, wav, wav16);
-    else if (x_bf16) k_conv_post<true><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16);
-    else k_conv_post<false><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16);
+                      float in_slope, float* wav, int16_t* wav16, const int64_t* row_len, const int64_t* row_off) {
+    if (x_bf16 && in_slope > 0.f && in_slope <= 1.f) {
+        dim3 grid(cdiv(S, 512), B);
+        if (in_slope == 1.f) k_conv_post_planar<false><<<grid, 256, 0, s>>>((const bf16*)x, w, bias, S, in_slope, wav, wav16, row_len, row_off);
+        else k_conv_post_planar<true><<<grid, 256, 0, s>>>((const bf16*)x, w, bias, S, in_slope, wav, wav16, row_len, row_off);
+    } else {
+        dim3 grid(cdiv(S, 256), B);
+        if (x_bf16) k_conv_post<true><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16, row_len, row_off);
+        else k_conv_post<false><<<grid, 256, 0, s>>>(x, w, bias, S, in_slope, wav, wav16, row_len, row_off);
+    }
     c->launches++;
 }
 

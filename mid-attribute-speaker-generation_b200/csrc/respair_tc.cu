@@ -448,9 +448,7 @@ void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const Co
     a.slope = 0.1f; a.out_scale = out_scale; a.post_slope = post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
     { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
-    static int n_sm = 0;
-    if (!n_sm) { int dev = 0; CUDA_OK(cudaGetDevice(&dev)); CUDA_OK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
-    const dim3 grid(std::min(a.total_tiles, n_sm), 1, 1);
+    const dim3 grid(std::min(a.total_tiles, c->n_sm), 1, 1);
     int xs = 0, nh = 0;
     rp_config(C, K, a.Rx, xs, nh);
     const size_t smem = rp_smem(C, K, a.Rx, xs, nh);

@@ -43,7 +43,7 @@ class _DeviceSampleMixin:
 
 
 class InterpolateGMM(_DeviceSampleMixin, D.MixtureSameFamily):
-    def __init__(self, distri_a: D.MixtureSameFamily, distri_b: D.MixtureSameFamily):
+    def __init__(self, distri_a: D.MixtureSameFamily, distri_b: D.MixtureSameFamily, _plan=None, _t=0.5, _cost=None):
         pa, na = _unwrap(distri_a)
         pb, nb = _unwrap(distri_b)
         dev = na.loc.device
@@ -53,10 +53,17 @@ class InterpolateGMM(_DeviceSampleMixin, D.MixtureSameFamily):
         f32 = dict(device=dev, dtype=torch.float32)
         self._a = (pa[0].to(**f32).contiguous(), na.loc[0].to(**f32).contiguous(), na.scale[0].to(**f32).contiguous())
         self._b = (pb[0].to(**f32).contiguous(), nb.loc[0].to(**f32).contiguous(), nb.scale[0].to(**f32).contiguous())
-        self.t = 0.5
-        w, mu, sc, cost = self._run(recompute_plan=True)
-        self.ot_Cost = cost.tolist()
-        self.ot_Matrix = w.reshape(self._a[0].shape[0], -1).double().cpu().numpy()
+        self.t = _t
+        if _plan is None:
+            w, mu, sc, cost = self._run(recompute_plan=True)
+            self.ot_Cost = cost.tolist()
+            self.ot_Matrix = w.reshape(self._a[0].shape[0], -1).double().cpu().numpy()
+        else:
+            # a transport plan that was solved elsewhere (a reference-made pickle carries POT's own ot.emd result): keep it
+            _, mu, sc, _ = self._run(recompute_plan=False)
+            self.ot_Matrix = np.asarray(_plan, dtype=np.float64)
+            self.ot_Cost = _cost
+            w = torch.from_numpy(self.ot_Matrix).flatten().to(**f32)
         self.mix = D.Categorical(w.unsqueeze(0))
         comp = D.Independent(D.Normal(mu.unsqueeze(0), sc.unsqueeze(0)), 1)
         super(InterpolateGMM, self).__init__(self.mix, comp)
@@ -137,3 +144,90 @@ class BarycenterGMM(_DeviceSampleMixin, D.MixtureSameFamily):
         mix, comp = self._build()
         self._component_distribution = comp
         self._mixture_distribution = mix
+
+
+# ------------------------------------------------------------------------------------------------
+# reference-pickled distribution artefacts: result/<...>/distributions/distri_*.pth are
+# ``torch.save(InterpolateGMM | BarycenterGMM)`` of the REFERENCE classes (class path model.distributions.*), loaded back by
+# examples_gen_distri.py:211 with torch.load.  Without the reference package on sys.path that unpickling fails; the loader
+# below maps the class path onto plain holders, reads the parts and rebinds them to the drop-in classes above.
+# ------------------------------------------------------------------------------------------------
+class _RefHolder:
+    """Receives the pickled __dict__ of a reference InterpolateGMM / BarycenterGMM (no constructor runs)."""
+
+
+class _RefInterpolateGMM(_RefHolder):
+    pass
+
+
+class _RefBarycenterGMM(_RefHolder):
+    pass
+
+
+_REF_CLASSES = {"InterpolateGMM": _RefInterpolateGMM, "BarycenterGMM": _RefBarycenterGMM}
+
+
+def _ref_pickle_module():
+    import pickle
+    import types
+
+    class _Unpickler(pickle.Unpickler):
+        def find_class(self, module, name):
+            if module == "model.distributions" and name in _REF_CLASSES:      # the reference's class path
+                return _REF_CLASSES[name]
+            return super().find_class(module, name)
+
+    m = types.ModuleType("pickle")
+    m.Unpickler = _Unpickler
+    m.load = lambda f, **kw: _Unpickler(f, **kw).load()
+    m.loads = lambda b, **kw: _Unpickler(__import__("io").BytesIO(b), **kw).load()
+    return m
+
+
+def read_reference_distribution(path):
+    """Parts of a reference-made ``distri_*.pth`` as CPU tensors (no GPU needed):
+    {"kind": "interpolate", "a": (pi [K], mu [K,D], sigma [K,D]), "b": (...), "t", "plan" [K,K] float64, "cost"} or
+    {"kind": "barycenter", "pi" [A,K], "mu" [A,K,D], "sigma" [A,K,D], "rate", "metadata_list"}; an object saved by the drop-in
+    classes of this module is returned as {"kind": "dropin", "object": obj}."""
+    obj = torch.load(path, map_location="cpu", weights_only=False, pickle_module=_ref_pickle_module())
+    cpu = lambda t: t.detach().to("cpu", torch.float32).contiguous()
+    if isinstance(obj, _RefInterpolateGMM):
+        (pa, na), (pb, nb) = obj.distri_a, obj.distri_b
+        return {"kind": "interpolate", "a": (cpu(pa[0]), cpu(na.loc[0]), cpu(na.scale[0])), "b": (cpu(pb[0]), cpu(nb.loc[0]), cpu(nb.scale[0])),
+                "t": float(obj.t), "plan": np.asarray(obj.ot_Matrix, dtype=np.float64), "cost": obj.ot_Cost}
+    if isinstance(obj, _RefBarycenterGMM):
+        ds = list(obj.original_distri.values())
+        return {"kind": "barycenter", "pi": torch.stack([cpu(d["probs"].reshape(-1)) for d in ds]),
+                "mu": torch.stack([cpu(d["distributes"].loc[0]) for d in ds]), "sigma": torch.stack([cpu(d["distributes"].scale[0]) for d in ds]),
+                "rate": [float(r) for r in obj.rate], "metadata_list": obj.metadata_list}
+    if isinstance(obj, (InterpolateGMM, BarycenterGMM)):
+        return {"kind": "dropin", "object": obj}
+    raise TypeError("%s holds a %s, not a pickled InterpolateGMM / BarycenterGMM" % (path, type(obj).__name__))
+
+
+def _mixture(pi, mu, sigma, dev):
+    f = dict(device=dev, dtype=torch.float32)
+    return D.MixtureSameFamily(D.Categorical(pi.to(**f).unsqueeze(0)), D.Independent(D.Normal(mu.to(**f).unsqueeze(0), sigma.to(**f).unsqueeze(0)), 1))
+
+
+def load_reference_distribution(path, device="cuda"):
+    """examples_gen_distri.py:211 ``dist = torch.load(path)`` for a file written by the REFERENCE: returns the drop-in
+    InterpolateGMM / BarycenterGMM on ``device`` with the same parameters, interpolation rate and — for InterpolateGMM — the very
+    transport plan the reference's ``ot.emd`` solved (it is read from the pickle, not recomputed), so ``.sample()``,
+    ``interpolate_rate`` and ``barycenter_rate`` continue from where the reference left off."""
+    parts = read_reference_distribution(path)
+    dev = torch.device(device)
+    if parts["kind"] == "dropin":
+        return parts["object"]
+    if parts["kind"] == "interpolate":
+        return InterpolateGMM(_mixture(*parts["a"], dev), _mixture(*parts["b"], dev), _plan=parts["plan"], _t=parts["t"], _cost=parts["cost"])
+    obj = BarycenterGMM.__new__(BarycenterGMM)
+    obj.metadata_list = parts["metadata_list"]
+    obj.device = dev
+    obj._meta = torch.zeros(parts["pi"].shape[0], 1, device=dev)                # only its row count is used (barycenter_rate)
+    f = dict(device=dev, dtype=torch.float32)
+    obj._params = (parts["pi"].to(**f).contiguous(), parts["mu"].to(**f).contiguous(), parts["sigma"].to(**f).contiguous())
+    obj.rate = list(parts["rate"])
+    mix, comp = obj._build()
+    D.MixtureSameFamily.__init__(obj, mix, comp)
+    return obj

@@ -106,8 +106,7 @@ class Generator(nn.Module):
             self._dirty = False
         return self._ctx
 
-    def forward(self, x, channels_last=False, return_int16=False):
-        """x: mel [B,80,T] (or [B,T,80] with channels_last=True) → wav fp32 [B,1,256·T]."""
+    def _prep(self, x, channels_last):
         ctx = self._context()
         if x.device != ctx.device:
             raise RuntimeError("mel is on %s but the vocoder is on %s (no CPU fallback)" % (x.device, ctx.device))
@@ -118,26 +117,58 @@ class Generator(nn.Module):
             B, C, T = x.shape
         if C != 80:
             raise ValueError("expected 80 mel channels, got %d" % C)
-        wav = torch.empty(B, 1, T * 256, dtype=torch.float32, device=ctx.device)
-        w16 = torch.empty(B, T * 256, dtype=torch.int16, device=ctx.device) if return_int16 else None
+        return ctx, x, B, T
+
+    def forward(self, x, channels_last=False, return_int16=False, int16_only=False):
+        """x: mel [B,80,T] (or [B,T,80] with channels_last=True) → wav fp32 [B,1,256·T].
+        return_int16: also the int16 waveform [B, 256·T] (utils/model.py:82-85, fused into the last kernel);
+        int16_only: skip the fp32 waveform altogether (4 of the last kernel's 70 bytes per sample) and return only int16."""
+        ctx, x, B, T = self._prep(x, channels_last)
+        want16 = return_int16 or int16_only
+        wav = None if int16_only else torch.empty(B, 1, T * 256, dtype=torch.float32, device=ctx.device)
+        w16 = torch.empty(B, T * 256, dtype=torch.int16, device=ctx.device) if want16 else None
         ctx.check(ctx.lib.masg_hifigan_forward(ctx.h, ctx.stream(), _lib.ptr(x), 1 if channels_last else 0, B, T,
                                                _lib.ptr(wav), _lib.ptr(w16)), "masg_hifigan_forward")
+        if int16_only:
+            return w16
         return (wav, w16) if return_int16 else wav
+
+    def forward_packed(self, x, mel_lens, channels_last=False, hop=256):
+        """Vocoder + int16 cast + per-utterance trim in one pass (utils/model.py:74-92 without its host work): returns
+        (packed int16 [sum(mel_lens)·hop] on the device, offsets int64 [B+1] on the device); utterance b is
+        packed[offsets[b]:offsets[b+1]].  ``mel_lens``: int64 [B] tensor (device or host)."""
+        ctx, x, B, T = self._prep(x, channels_last)
+        lens = torch.as_tensor(mel_lens).to(device=ctx.device, dtype=torch.int64).contiguous()
+        if lens.shape != (B,):
+            raise ValueError("mel_lens must be [B]")
+        packed = torch.empty(B * T * hop, dtype=torch.int16, device=ctx.device)          # capacity: the padded size bounds the total
+        offsets = torch.empty(B + 1, dtype=torch.int64, device=ctx.device)
+        ctx.check(ctx.lib.masg_hifigan_forward_packed(ctx.h, ctx.stream(), _lib.ptr(x), 1 if channels_last else 0, B, T, _lib.ptr(lens),
+                                                      int(hop), _lib.ptr(packed), _lib.ptr(offsets)), "masg_hifigan_forward_packed")
+        return packed, offsets
 
 
 def vocoder_infer(mels, vocoder, model_config, preprocess_config, lengths=None):
     """utils/model.py:74-92 for the HiFi-GAN branch: mel [B,80,T] → list of int16 numpy arrays cut to
-    ``lengths``.  The ×32768 and the C-cast int16 conversion are fused into the conv_post kernel, so the
-    D2H copy moves 2 bytes per sample instead of 4."""
+    ``lengths``.  The ×32768, the C-cast int16 conversion AND the trim are fused into the conv_post kernel (packed
+    output), so the D2H copy moves 2 bytes per VALID sample instead of 4 per padded one."""
     name = model_config["vocoder"]["model"]
     if name != "HiFi-GAN":
         raise NotImplementedError("only the HiFi-GAN vocoder is on the B200 path")
     if float(preprocess_config["audio"]["max_wav_value"]) != 32768.0:
         raise NotImplementedError("max_wav_value must be 32768.0")
+    hop = int(preprocess_config["stft"]["hop_length"]) if "stft" in preprocess_config else 256
     with torch.no_grad():
-        _, w16 = vocoder(mels, return_int16=True)
-    wavs = [w for w in w16.cpu().numpy()]
-    for i in range(len(mels)):
-        if lengths is not None:
-            wavs[i] = wavs[i][: lengths[i]]
-    return wavs
+        if lengths is None:
+            return [w for w in vocoder(mels, int16_only=True).cpu().numpy()]
+        # trimmed on the device: one D2H copy of exactly the valid samples, then zero-copy views per utterance.  The reference
+        # slices to `lengths` samples (utils/model.py:88-90); callers pass mel_len * hop, which is what the packed kernel keeps.
+        lens = torch.as_tensor(lengths).to(torch.int64).cpu()
+        T = mels.shape[2]
+        if bool((lens % hop != 0).any()) or bool((lens > T * hop).any()):
+            w16 = vocoder(mels, int16_only=True).cpu().numpy()           # arbitrary sample counts: slice on the host
+            return [w16[i][: int(lens[i])] for i in range(len(w16))]
+        packed, offsets = vocoder.forward_packed(mels, lens // hop, hop=hop)
+        off = offsets.cpu().numpy()
+        flat = packed[: int(off[-1])].cpu().numpy()
+    return [flat[off[i]: off[i + 1]] for i in range(len(off) - 1)]

@@ -4,6 +4,7 @@ utterances over ranks.  Host logic only; all arithmetic is in
 """
 import ctypes
 import heapq
+import os
 
 import numpy as np
 import torch
@@ -33,7 +34,7 @@ class Synthesizer:
         out = self.fs2.synthesize_from_speaker_emb(None, texts, src_lens, texts.shape[1], p_control=p_control,
                                                    e_control=e_control, d_control=d_control, accents=accents,
                                                    speaker_emb=speaker_emb)
-        _, w16 = self.vocoder(out[1], channels_last=True, return_int16=True)
+        w16 = self.vocoder(out[1], channels_last=True, int16_only=True)
         return w16, out[9], out[1]
 
     def _pinned(self, name, shape, dtype):
@@ -64,35 +65,162 @@ class Synthesizer:
         d2h = B * T * 256 * 2 + B * 8
         return h_w, h_m, T, h2d, d2h
 
+    def synthesize_host_packed(self, texts, accents, src_lens, speaker_emb, cap_samples, p_control=1.0, e_control=1.0, d_control=1.0):
+        """The same through masg_synthesize_host_packed: the per-utterance trim (utils/model.py:88-90) happens in the vocoder's
+        last kernel and ONE D2H copy moves exactly the valid samples.  Returns (packed int16 [cap_samples] pinned host tensor,
+        offsets int64 [B+1] host, mel_lens int64 [B] host, T_max, h2d_bytes, d2h_bytes); utterance b is
+        packed[offsets[b]:offsets[b+1]]."""
+        B, L = texts.shape
+        h_t = self._pinned("texts", (B, L), torch.int64); h_t.copy_(texts)
+        h_a = self._pinned("accents", (B, L), torch.int64); h_a.copy_(accents)
+        h_l = self._pinned("lens", (B,), torch.int64); h_l.copy_(src_lens)
+        h_s = self._pinned("spk", (B, 256), torch.float32); h_s.copy_(speaker_emb)
+        h_w = self._pinned("wav_packed", (int(cap_samples),), torch.int16)
+        h_o = self._pinned("offsets", (B + 1,), torch.int64)
+        h_m = self._pinned("mel_lens", (B,), torch.int64)
+        tmax = ctypes.c_int64(0)
+        ctx = self.ctx
+        ctx.check(ctx.lib.masg_synthesize_host_packed(ctx.h, ctx.stream(), _lib.ptr(h_t), _lib.ptr(h_a), _lib.ptr(h_l), B, L,
+                                                      _lib.ptr(h_s), float(p_control), float(e_control), float(d_control),
+                                                      ctypes.c_int64(int(cap_samples)), _lib.ptr(h_w), _lib.ptr(h_o), _lib.ptr(h_m),
+                                                      ctypes.byref(tmax)), "masg_synthesize_host_packed")
+        h2d = h_t.numel() * 8 + h_a.numel() * 8 + h_l.numel() * 8 + h_s.numel() * 4
+        d2h = int(h_o[B]) * 2 + (B + 1) * 8
+        return h_w, h_o, h_m, int(tmax.value), h2d, d2h
+
+    def generate(self, texts, speakers, out_dir=None, speaker_names=None, text_ids=None, n_speakers=None, seed=0, p_control=1.0,
+                 e_control=1.0, d_control=1.0, frame_budget=40000, max_batch=64, frames_per_phoneme=6.0, writer=None,
+                 save_embeddings=True, sampling_rate=SAMPLING_RATE):
+        """"N speakers x M texts" in one call — the batched form of the reference's generation scripts, which synthesise one
+        (speaker, sentence) pair per Python iteration at batch size 1 (examples_gen.py:247-273, examples_gen_distri.py:209-218).
+
+        texts:    tokenised batch {"texts", "accents" int64 [M, L] zero padded, "src_lens" int64 [M]} (frontend.Frontend.tokenize).
+        speakers: float tensor [N, 256] of embeddings; or a distribution with ``.sample()`` (the drop-in InterpolateGMM /
+                  BarycenterGMM, or one loaded with distributions.load_reference_distribution) together with ``n_speakers``; or a
+                  metadata one-hot tensor [N, 4], sampled through ``speaker_gen`` (examples_gen.py:256-268).
+        Every (speaker, text) pair becomes one utterance; utterances are sorted into length-bucketed batches under a padded-frame
+        budget (plan_batches), each batch runs through masg_synthesize_host_packed (trim on the device, one D2H of the valid
+        samples) and, with ``out_dir``, a background writer emits ``<speaker>_<text id>.wav`` while the next batch is synthesised;
+        the embeddings are saved as ``<speaker>.npy`` ([1, 256] float32, the reference's format).
+        Returns a list of dicts (speaker, text_id, path or wav, samples, mel_len) in (speaker, text) order."""
+        from .wavio import WavWriter
+        from .fastspeech2 import gmm_sample
+        ids, acc, lens = (torch.as_tensor(texts[k]).to("cpu", torch.int64) for k in ("texts", "accents", "src_lens"))
+        M = ids.shape[0]
+        dev = self.device
+        # ---- speakers -> [N, 256] on the host (one or two launches, one D2H) ----
+        if torch.is_tensor(speakers) and speakers.dim() == 2 and speakers.shape[1] == 256:
+            emb = speakers.detach().to("cpu", torch.float32)
+        elif torch.is_tensor(speakers) and speakers.dim() == 2:
+            emb = self.fs2.speaker_gen(speakers.to(dev), seed=seed).cpu()
+        elif hasattr(speakers, "component_distribution"):
+            if not n_speakers:
+                raise ValueError("n_speakers is required when `speakers` is a distribution")
+            comp = speakers.component_distribution.base_dist
+            emb = gmm_sample(self.ctx, speakers.mixture_distribution.probs.reshape(1, -1).to(dev), comp.loc.reshape(1, comp.loc.shape[-2], -1).to(dev),
+                             comp.scale.reshape(1, comp.scale.shape[-2], -1).to(dev), int(n_speakers), seed=seed).cpu()
+        else:
+            raise TypeError("speakers must be an [N, 256] embedding tensor, an [N, 4] metadata tensor or a mixture distribution")
+        N = emb.shape[0]
+        speaker_names = list(speaker_names) if speaker_names is not None else ["spk%03d" % (i + 1) for i in range(N)]
+        text_ids = list(text_ids) if text_ids is not None else ["%04d" % i for i in range(M)]
+        if len(speaker_names) != N or len(text_ids) != M:
+            raise ValueError("speaker_names / text_ids do not match the speakers / texts")
+        # ---- N x M utterances, length-bucketed ----
+        utt_text = np.tile(np.arange(M), N)
+        utt_spk = np.repeat(np.arange(N), M)
+        utt_len = lens.numpy()[utt_text]
+        batches = plan_batches(utt_len, frame_budget=frame_budget, max_batch=max_batch, frames_per_phoneme=frames_per_phoneme)
+        own_writer = writer is None and out_dir is not None
+        if own_writer:
+            writer = WavWriter()
+        results = [None] * (N * M)
+        try:
+            if out_dir is not None and save_embeddings:
+                save_speaker_embeddings(out_dir, speaker_names, emb)
+            for idx in batches:
+                t_idx = torch.from_numpy(utt_text[idx])
+                L = int(utt_len[idx].max())
+                b_ids, b_acc, b_len = ids[t_idx, :L].contiguous(), acc[t_idx, :L].contiguous(), lens[t_idx].contiguous()
+                b_emb = emb[torch.from_numpy(utt_spk[idx])].contiguous()
+                cap = int(len(idx) * L * 2 * frames_per_phoneme) * HOP
+                while True:
+                    try:
+                        h_w, h_o, h_m, T, _, _ = self.synthesize_host_packed(b_ids, b_acc, b_len, b_emb, cap, p_control, e_control, d_control)
+                        break
+                    except RuntimeError as e:
+                        if "capacity" not in str(e):
+                            raise
+                        cap *= 2                                      # durations longer than the estimate: retry with more room
+                off = h_o.numpy()
+                flat = h_w.numpy()
+                for k, u in enumerate(idx):
+                    wav = flat[off[k]: off[k + 1]]
+                    rec = {"speaker": speaker_names[utt_spk[u]], "text_id": text_ids[utt_text[u]], "samples": int(off[k + 1] - off[k]),
+                           "mel_len": int(h_m[k])}
+                    if out_dir is not None:
+                        rec["path"] = os.path.join(str(out_dir), "%s_%s.wav" % (rec["speaker"], rec["text_id"]))
+                        writer.submit(rec["path"], sampling_rate, wav, copy=True)     # the pinned buffer is reused by the next batch
+                    else:
+                        rec["wav"] = wav.copy()
+                    results[int(u)] = rec
+        finally:
+            if own_writer:
+                writer.close()
+        return results
+
+
+class SpeakerSampler:
+    """A speaker set drawn from the TacoSpawn prior and its mid-attribute interpolations, re-sampled on every call with TWO
+    kernel launches whatever its size (the reference draws one speaker per Python iteration: examples_gen.py:258-273,
+    examples_gen_distri.py:209-218).  Default set = config 3 of BASELINE.json: ``n_sampled`` embeddings from
+    ``speaker_gen`` cycling the four (gender, language) metadata combos + ``n_interp`` from ``InterpolateGMM(a, b)`` over the 6
+    unordered combo pairs with t in {0.25, 0.5, 0.75}.  The priors are built once (the reference, too, loads a pickled
+    distribution once); their K*K-component parameters are stacked so that one batched ``masg_gmm_sample`` launch serves all
+    interpolated speakers."""
+
+    def __init__(self, fs2, n_sampled, n_interp, seed=0, metas=None, rates=(0.25, 0.5, 0.75)):
+        from .distributions import InterpolateGMM
+        self.fs2, self.ctx, self.seed, self.calls = fs2, fs2._context(), int(seed), 0
+        dev = self.ctx.device
+        combos = torch.tensor(META_COMBOS, dtype=torch.float32, device=dev)
+        self.meta = (torch.as_tensor(metas, dtype=torch.float32).to(dev) if metas is not None
+                     else combos[torch.arange(n_sampled, device=dev) % 4]).reshape(-1, 4)[:n_sampled].contiguous()
+        self.n_sampled, self.n_interp = n_sampled, n_interp
+        self.interp_spec = []
+        if n_interp:
+            dists = [fs2.speaker_distribution(combos[i:i + 1]) for i in range(4)]
+            pairs = [(a, b) for a in range(4) for b in range(a + 1, 4)]
+            cache, pis, mus, scs = {}, [], [], []
+            for i in range(n_interp):
+                a, b = pairs[i % len(pairs)]
+                t = rates[(i // len(pairs)) % len(rates)]
+                if (a, b) not in cache:
+                    cache[(a, b)] = InterpolateGMM(dists[a], dists[b])
+                ig = cache[(a, b)]
+                ig.interpolate_rate(t)
+                comp = ig.component_distribution.base_dist
+                pis.append(ig.mixture_distribution.probs.reshape(1, -1).clone())
+                mus.append(comp.loc.reshape(1, -1, 256).clone())
+                scs.append(comp.scale.reshape(1, -1, 256).clone())
+                self.interp_spec.append((a, b, t))
+            self.pi, self.mu, self.sc = torch.cat(pis).contiguous(), torch.cat(mus).contiguous(), torch.cat(scs).contiguous()
+
+    def sample(self):
+        """[n_sampled + n_interp, 256] on the model's device; a new draw per call (Philox seed = seed + 2 * call [+ 1])."""
+        from .fastspeech2 import gmm_sample
+        self.calls += 1
+        embs = []
+        if self.n_sampled:
+            embs.append(self.fs2.speaker_gen(self.meta, seed=self.seed + 2 * self.calls))
+        if self.n_interp:
+            embs.append(gmm_sample(self.ctx, self.pi, self.mu, self.sc, self.n_interp, seed=self.seed + 2 * self.calls + 1))
+        return torch.cat(embs, 0)
+
 
 def sample_speakers(fs2, n_sampled, n_interp, seed=0):
-    """Config-3 speaker set: n_sampled embeddings from speaker_gen (cycling the four
-    metadata combos) + n_interp from InterpolateGMM(a, b) over the 6 unordered combo pairs with
-    t ∈ {0.25, 0.5, 0.75}.  Returns [n_sampled + n_interp, 256] on the model's device."""
-    from .distributions import InterpolateGMM
-    dev = next(fs2.parameters()).device
-    g = torch.Generator().manual_seed(seed)
-    metas = torch.tensor([META_COMBOS[i % 4] for i in range(n_sampled)], dtype=torch.float32, device=dev)
-    embs = [fs2.speaker_gen(metas, seed=int(torch.randint(0, 2 ** 62, (1,), generator=g)))] if n_sampled else []
-    if n_interp:
-        combos = torch.tensor(META_COMBOS, dtype=torch.float32, device=dev)
-        dists = [fs2.speaker_distribution(combos[i:i + 1]) for i in range(4)]
-        pairs = [(a, b) for a in range(4) for b in range(a + 1, 4)]
-        cache = {}
-        rates = (0.25, 0.5, 0.75)
-        ctx = fs2._context()
-        from .fastspeech2 import gmm_sample
-        for i in range(n_interp):
-            a, b = pairs[i % len(pairs)]
-            t = rates[(i // len(pairs)) % len(rates)]
-            if (a, b) not in cache:
-                cache[(a, b)] = InterpolateGMM(dists[a], dists[b])
-            ig = cache[(a, b)]
-            ig.interpolate_rate(t)
-            comp = ig.component_distribution.base_dist
-            embs.append(gmm_sample(ctx, ig.mixture_distribution.probs.reshape(1, -1), comp.loc.reshape(1, -1, 256),
-                                   comp.scale.reshape(1, -1, 256), 1, seed=int(torch.randint(0, 2 ** 62, (1,), generator=g))))
-    return torch.cat(embs, 0)
+    """One draw of the config-3 speaker set (see SpeakerSampler): [n_sampled + n_interp, 256] on the model's device."""
+    return SpeakerSampler(fs2, n_sampled, n_interp, seed=seed).sample()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -183,3 +311,74 @@ def shard_batch(B, rank, world_size):
 
 def audio_seconds(mel_lens):
     return float(np.sum(np.asarray(mel_lens, dtype=np.float64)) * HOP / SAMPLING_RATE)
+
+
+# ------------------------------------------------------------------------------------------------
+# optional gather of the output waveforms over NVLink (SURVEY.md §8(e) "Collective"): the only data-path collective
+# ------------------------------------------------------------------------------------------------
+class WaveformGather:
+    """All-gather of every rank's packed int16 audio (row b = packed[offsets[b]:offsets[b+1]]) so that rank 0 — or every rank —
+    holds the whole job's waveforms.  Lengths differ per rank, so the exchange is two collectives on a side stream: an
+    ``all_gather`` of the [total samples, utterances] counts, then one ``all_gather_into_tensor`` each of the offsets and of
+    the sample buffers padded to the largest rank's size (C4: ~1.0 GB of int16 in total, ~1-2 ms at NVLink-5 rates; C3:
+    19.7 MB per rank).  ``start()`` returns at once — the next batch's kernels run on the compute stream while NCCL moves the
+    previous batch — and ``wait()`` yields [(packed, offsets)] per rank, trimmed.  Backend-agnostic through torch.distributed:
+    NCCL over NVLink / NVSwitch on the GPUs, gloo in the CPU tests of the bookkeeping."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.stream = None
+        self._pending = None
+
+    def start(self, packed, offsets):
+        dist = self.dist
+        dev = packed.device
+        cuda = dev.type == "cuda"
+        if cuda and self.stream is None:
+            self.stream = torch.cuda.Stream(device=dev)
+        B = offsets.numel() - 1
+        counts = torch.stack([offsets[B].to(torch.int64), torch.tensor(B, dtype=torch.int64, device=dev)])
+        ready = torch.cuda.current_stream(dev).record_event() if cuda else None
+
+        def run():
+            all_counts = torch.empty(self.world * 2, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(all_counts, counts, group=self.group)
+            host = all_counts.view(self.world, 2).cpu()                                          # sizes of the padded exchange (16 bytes per rank)
+            n_max, b_max = int(host[:, 0].max()), int(host[:, 1].max())
+            send_w = torch.zeros(max(n_max, 1), dtype=torch.int16, device=dev)
+            send_w[: int(host[self.rank, 0])] = packed[: int(host[self.rank, 0])]
+            send_o = torch.zeros(b_max + 1, dtype=torch.int64, device=dev)
+            send_o[: B + 1] = offsets
+            recv_w = torch.empty(self.world * max(n_max, 1), dtype=torch.int16, device=dev)
+            recv_o = torch.empty(self.world * (b_max + 1), dtype=torch.int64, device=dev)
+            # neither NCCL nor gloo has a 16-bit integer type: the samples travel as bytes
+            dist.all_gather_into_tensor(recv_w.view(torch.uint8), send_w.view(torch.uint8), group=self.group)
+            dist.all_gather_into_tensor(recv_o, send_o, group=self.group)
+            return host, recv_w.view(self.world, -1), recv_o.view(self.world, -1)
+
+        if cuda:
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ready)
+                packed.record_stream(self.stream); offsets.record_stream(self.stream)
+                res = run()
+                done = self.stream.record_event()
+        else:
+            res, done = run(), None
+        self._pending = (res, done, dev)
+        return self
+
+    def wait(self):
+        """[(packed int16 [n_r], offsets int64 [B_r + 1])] for r in ranks; the compute stream waits for the side stream."""
+        (host, w, o), done, dev = self._pending
+        self._pending = None
+        if done is not None:
+            torch.cuda.current_stream(dev).wait_event(done)
+        return [(w[r, : int(host[r, 0])], o[r, : int(host[r, 1]) + 1]) for r in range(self.world)]
+
+
+def gather_waveforms(packed, offsets, group=None):
+    """Blocking form of WaveformGather: every rank returns the list of all ranks' (packed, offsets)."""
+    return WaveformGather(group).start(packed, offsets).wait()

@@ -132,11 +132,31 @@ def barycenter(ref=None):
             rec["probs_" + tag], rec["mean_" + tag], rec["std_" + tag] = probs.numpy(), mean.numpy(), std.numpy()
             print("barycenter", tag, "components", probs.shape[0], "probs", probs.numpy().round(4))
     np.savez_compressed(os.path.join(OUT, "barycenter.npz"), weights_seed=1234, rate=np.array(BARY_RATE), **rec)
+    distri_artefacts(ref)
+
+
+def distri_artefacts(ref=None):
+    """tests/golden/distri_ref_{interp,bary}.pth: ``torch.save`` of the REFERENCE's distribution objects, i.e. the on-disk
+    artefacts examples_gen_distri.py:211 loads (class path model.distributions.*), for the loader tests."""
+    ns = ref_import.load()
+    if ref is None:
+        ref = ref_import.build_fs2(syn.make_fs2_state_dict(seed=1234), syn.speakers_json(), syn.STATS_JSON)
+    metas = torch.tensor(syn.META_COMBOS, dtype=torch.float32)
+    with torch.no_grad():
+        ig = ns.InterpolateGMM(ref.speaker_distribution(metas[1:2]), ref.speaker_distribution(metas[2:3]))
+        ig.interpolate_rate(0.75)
+        torch.save(ig, os.path.join(OUT, "distri_ref_interp.pth"))
+        _, _, _, bg = ref_import.run_barycenter(ref, BARY_RATE)
+        bg.__class__ = ns.BarycenterGMM                  # the harness subclass is local; the artefact carries the reference class
+        torch.save(bg, os.path.join(OUT, "distri_ref_bary.pth"))
+    print("distribution artefacts:", [os.path.getsize(os.path.join(OUT, f)) for f in ("distri_ref_interp.pth", "distri_ref_bary.pth")])
 
 
 if __name__ == "__main__":
     if "--barycenter" in sys.argv:
         barycenter()
+    elif "--distri" in sys.argv:
+        distri_artefacts()
     elif "--frontend" in sys.argv:
         frontend_fixture()
     else:

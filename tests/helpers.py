@@ -82,18 +82,19 @@ def check_unforced_durations(out_log_d, ref_log_d, out_d, ref_d, tag=""):
     return n
 
 
-def check_unforced_buckets(out_v, ref_v, bins, tag=""):
+def check_unforced_buckets(out_v, ref_v, bins, tag="", assert_boundary=True):
     """Un-forced pitch / energy bucket parity (torch.bucketize of the predictor output, model/modules.py:85-88): the bucket
     index must be EQUAL, except where the reference's own value sits within twice the measured prediction error of a bin
     boundary (an adjacent-bucket flip there is the reference's rounding accident, exactly like a duration on a .5 boundary).
-    Returns a bool mask [B, L] of the flipped positions."""
+    assert_boundary=False only reports (used for the un-forced ENERGY, whose predictor input already differs wherever a pitch
+    bucket flipped upstream; it is checked again with the pitch teacher-forced).  Returns a bool mask [B, L] of the flips."""
     out_v, ref_v, bins = out_v.detach().cpu().float(), torch.as_tensor(ref_v).float(), torch.as_tensor(bins).float().cpu()
     err = (out_v - ref_v).abs().max().item()
     io, ir = torch.bucketize(out_v, bins), torch.bucketize(ref_v, bins)
     flips = io != ir
     n = int(flips.sum())
     print("un-forced buckets %s: max-abs err %.2e, flips %d of %d" % (tag, err, n, flips.numel()))
-    if n:
+    if n and assert_boundary:
         assert int((io - ir).abs().max()) == 1, "%s: bucket flip by more than one bin" % tag
         dist = (ref_v[flips][:, None] - bins[None, :]).abs().min(1).values
         assert (dist <= 2 * err + 1e-7).all(), "%s: bucket flip away from a bin boundary (distances %s, err %.2e)" % (tag, dist.tolist()[:8], err)

@@ -59,7 +59,8 @@ def _oracle_rows(sd, hsd, b, emb, rows, vocoder_rows=None, **kw):
 
 def _check(fs2, voc, sd, b, emb, out, wav, ref, ref_wav, rows, vr, tag):
     """(1) the integer decisions of the un-forced run against the oracle's: durations, mel lengths, masks equal; pitch / energy
-    buckets equal — a flip is accepted only on a boundary of the reference's own value (helpers.check_unforced_*) and is counted;
+    buckets equal (energy with the pitch forced: its input contains the pitch embedding) — a flip is accepted only on a boundary
+    of the reference's own value (helpers.check_unforced_*) and is counted;
     (2) rows without any flip: the UN-FORCED mel / postnet mel / waveform against the oracle at the north_star tolerances;
     (3) all checked rows again with the oracle's pitch / energy / durations teacher-forced (p_targets / e_targets / d_targets,
     model/modules.py:80-100,128-130 — 'given identical predictor outputs'), so rows with a boundary flip are compared too."""
@@ -67,7 +68,11 @@ def _check(fs2, voc, sd, b, emb, out, wav, ref, ref_wav, rows, vr, tag):
     pb, eb = sd["variance_adaptor.pitch_bins"], sd["variance_adaptor.energy_bins"]
     d_flips = helpers.check_unforced_durations(out[4].cpu()[rows_t], ref[4], out[5].cpu()[rows_t], ref[5], tag)
     fp = helpers.check_unforced_buckets(out[2].cpu()[rows_t], ref[2], pb, tag + " pitch")
-    fe = helpers.check_unforced_buckets(out[3].cpu()[rows_t], ref[3], eb, tag + " energy")
+    fe = helpers.check_unforced_buckets(out[3].cpu()[rows_t], ref[3], eb, tag + " energy (un-forced)", assert_boundary=False)
+    # the energy predictor reads x + pitch_embedding: its bucket decision is checked 'given identical predictor outputs'
+    # upstream, i.e. with the oracle's pitch teacher-forced (a pitch-bucket flip legitimately changes the energy near it)
+    out_p, _ = _gpu(fs2, voc, b, emb, rows=rows, p_targets=ref[2].to(DEV))
+    helpers.check_unforced_buckets(out_p[3], ref[3], eb, tag + " energy (pitch forced)")
     assert torch.equal(out[6].cpu()[rows_t], ref[6]), tag + ": src masks differ"
     if d_flips == 0:
         assert torch.equal(out[9].cpu()[rows_t], ref[9]), tag + ": mel_lens differ"
