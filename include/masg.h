@@ -197,8 +197,11 @@ int masg_profile_read(masg_ctx* ctx, void* stream, double* h_ms_total, double* h
 
 /* Counters for the benchmark harness: number of kernels this context launched since the last reset. */
 int64_t masg_launch_count(masg_ctx* ctx, int reset);
-/* Intermediate tap for parity tests: copies a named internal fp32 buffer of the last forward
- * ("encoder_out" [B,L,256], "lr_out" [B,T,256], "decoder_out" [B,T,256]) into dst (device, fp32). */
+/* Intermediate taps for parity tests (off by default: they cost two extra activation copies per forward).  After
+ * masg_debug_enable_taps(ctx, 1), masg_debug_tap copies a named internal fp32 buffer of the LAST FastSpeech2 forward
+ * ("encoder_out" [B,L,256], "va_out" [B,L,256], "lr_out" [B,T,256], "decoder_out" [B,T,256]) into dst (device, fp32); the
+ * phase-B taps are valid until the next call that uses the phase-B workspace (vocoder, GMM interpolation / barycentre). */
+int masg_debug_enable_taps(masg_ctx* ctx, int enable);
 int masg_debug_tap(masg_ctx* ctx, void* stream, const char* name, float* dst, int64_t n_elems);
 
 /* ---- text front-end (host only, no device work): the Japanese branch of the reference's tokenisation, batched ----

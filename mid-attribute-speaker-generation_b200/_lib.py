@@ -50,6 +50,7 @@ SIGNATURES = {
     "masg_profile": (c_int, [P, c_int]),
     "masg_profile_read": (c_int, [P, P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_i64)]),
     "masg_launch_count": (c_i64, [P, c_int]),
+    "masg_debug_enable_taps": (c_int, [P, c_int]),
     "masg_debug_tap": (c_int, [P, P, c_char_p, P, c_i64]),
     "masg_frontend_create": (c_int, [ctypes.POINTER(c_char_p), c_int, ctypes.POINTER(P)]),
     "masg_frontend_destroy": (None, [P]),
@@ -149,6 +150,10 @@ class Context:
         self.check(self.lib.masg_profile_read(self.h, self.stream(), ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(n)),
                    "masg_profile_read")
         return ms.value, fl.value, int(n.value)
+
+    def enable_taps(self, on=True):
+        """Keep copies of the intermediate tensors of the next forwards for ``tap`` (off by default)."""
+        self.check(self.lib.masg_debug_enable_taps(self.h, 1 if on else 0), "masg_debug_enable_taps")
 
     def tap(self, name, shape):
         out = torch.empty(shape, dtype=torch.float32, device=self.device)

@@ -48,8 +48,8 @@ int masg_ctx_create(int device, int precision, masg_ctx** out) {
 }
 
 static void free_owned(masg_ctx* c) {
-    for (void* p : c->owned) cudaFree(p);
-    c->owned.clear();
+    for (auto* v : {&c->owned, &c->owned_fs2, &c->owned_hg}) { for (void* p : *v) cudaFree(p); v->clear(); }
+    if (c->pos_long) cudaFree(c->pos_long);
     c->pos_long = nullptr; c->pos_long_n = 0;
 }
 
@@ -59,6 +59,7 @@ void masg_ctx_destroy(masg_ctx* c) {
     cudaDeviceSynchronize();
     free_owned(c);
     c->arena.release(); c->arena_b.release();
+    for (auto& kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->io_buf) cudaFree(c->io_buf);
     if (c->out_buf) cudaFree(c->out_buf);
@@ -233,7 +234,7 @@ int masg_gmm_interpolate(masg_ctx* c, void* stream, const float* pi_a, const flo
     MASG_CHECK(K >= 1 && K <= 4, "K=%d unsupported (exact EMD enumerates supports for K <= 4)", K);
     launch_gmm_interp_comps(c, s, mu_a, sig_a, mu_b, sig_b, K, D, t, comp_mu, comp_scale);
     if (recompute_plan) {
-        c->arena_b.reset();
+        c->arena_b.reset(); c->tap_lr = c->tap_dec = nullptr;             // the phase-B taps lived in this arena
         double* cost = c->arena_b.get<double>(K * K);
         launch_gmm_interp_cost(c, s, mu_a, sig_a, mu_b, sig_b, K, D, cost);
         double hc[16], G[16], ha[4], hb[4]; float fa[4], fb[4], fw[16];
@@ -257,7 +258,7 @@ int masg_gmm_barycenter(masg_ctx* c, void* stream, const float* pi, const float*
     cudaStream_t s = (cudaStream_t)stream;
     MASG_CHECK(A >= 1 && A <= 8 && K >= 1, "A=%d K=%d unsupported", A, K);
     int nb = 1; for (int a = 0; a < A; ++a) nb *= K;
-    c->arena_b.reset();
+    c->arena_b.reset(); c->tap_lr = c->tap_dec = nullptr;
     float* rate = c->arena_b.get<float>(A);
     CUDA_OK(cudaMemcpyAsync(rate, h_rate, A * sizeof(float), cudaMemcpyHostToDevice, s));
     launch_gmm_bary(c, s, mu, sigma, rate, A, K, D, bary_mean, bary_std);
@@ -270,6 +271,60 @@ int masg_gmm_barycenter(masg_ctx* c, void* stream, const float* pi, const float*
     CUDA_OK(cudaMemcpyAsync(bary_weight, hw.data(), nb * sizeof(float), cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaStreamSynchronize(s));
     API_END(c)
+}
+
+}  // extern "C"
+
+// Replay `body` (a sequence of kernel launches on library-owned buffers) as a CUDA graph when the small-batch latency path asks
+// for it (MASG_GRAPH=1, or automatically for batches of <= MASG_GRAPH_ROWS phoneme rows).  First sight of a key: plain run
+// (sizes the arenas, sets kernel attributes); second: capture + instantiate + launch; afterwards: one cudaGraphLaunch, as long
+// as no buffer the captured kernels point into has moved and the weights have not been re-committed.
+static int graph_rows_limit() {
+    static int lim = -2;
+    if (lim == -2) {
+        const char* g = getenv("MASG_GRAPH"); const char* r = getenv("MASG_GRAPH_ROWS");
+        lim = g ? (atoi(g) ? (1 << 30) : -1) : (r ? atoi(r) : 512);
+    }
+    return lim;
+}
+template <typename F>
+static void run_graphed(masg_ctx* c, cudaStream_t s, const std::vector<long>& key, long rows, F body) {
+    if (rows > graph_rows_limit() || c->profiling || c->taps) { body(); return; }
+    GraphEntry& e = c->graphs[key];
+    void* snap[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
+    const bool same = !memcmp(snap, e.snap, sizeof(snap));
+    if (e.exec && same) {
+        CUDA_OK(cudaGraphLaunch(e.exec, s));
+        c->launches += e.launches;
+        if (key[0] == 0) { c->va_out = e.va_out; c->d_rounded_dev = e.d_rounded_dev; c->mel_lens_dev = e.mel_lens_dev; c->src_lens_dev = e.src_lens_dev; c->B = (int)key[1]; c->L = (int)key[2]; }
+        return;
+    }
+    if (e.exec) { cudaGraphExecDestroy(e.exec); e.exec = nullptr; }
+    if (e.seen++ == 0 || !same) {                             // plain run; remember where the buffers are now
+        body();
+        void* after[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
+        memcpy(e.snap, after, sizeof(after));
+        return;
+    }
+    const int64_t l0 = c->launches;
+    CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+    try { body(); }
+    catch (...) { cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); throw; }
+    cudaGraph_t g = nullptr;
+    CUDA_OK(cudaStreamEndCapture(s, &g));
+    void* after[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
+    if (memcmp(after, snap, sizeof(after))) {                 // a buffer moved while capturing: the graph is stale already
+        cudaGraphDestroy(g);
+        memcpy(e.snap, after, sizeof(after));
+        body();
+        return;
+    }
+    cudaError_t ie = cudaGraphInstantiate(&e.exec, g, 0);
+    cudaGraphDestroy(g);
+    CUDA_OK(ie);
+    e.launches = c->launches - l0;
+    e.va_out = c->va_out; e.d_rounded_dev = c->d_rounded_dev; e.mel_lens_dev = c->mel_lens_dev; e.src_lens_dev = c->src_lens_dev;
+    CUDA_OK(cudaGraphLaunch(e.exec, s));
 }
 
 // shared body of the two host-buffer entry points.  packed == 0: rows of stride 256 * t_cap in h_wav (every row is copied up to
@@ -302,8 +357,13 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     CUDA_OK(cudaMemcpyAsync(lens, h_src_lens, B * 8, cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaMemcpyAsync(spk, h_spk_emb, (size_t)B * 256 * 4, cudaMemcpyHostToDevice, s));
     int64_t tmax = 0;
-    fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
-                nullptr, &tmax);
+    // the controls are baked into a captured graph: they are part of the key (as float bit patterns)
+    auto fbits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return (long)u; };
+    run_graphed(c, s, {0, B, L, 0, 0, fbits(p_ctl), fbits(d_ctl)}, (long)rows, [&]() {
+        fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
+                    nullptr, nullptr);
+    });
+    fs2_phase_a_publish(c, s, &tmax);
     MASG_CHECK(tmax > 0, "no frames to synthesise (all durations are zero)");
     const int T = (int)tmax;
     // phase A's single sync left [mel_lens | T_max] in the pinned scratch: the host knows every row's length from here on
@@ -319,20 +379,23 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     }
     p = (char*)c->out_buf;
     float* mel = (float*)take((size_t)B * T * 80 * 4); float* post = (float*)take((size_t)B * T * 80 * 4);
-    fs2_phase_b(c, s, T, mel, post, nullptr);
-    if (packed) {
-        int16_t* w16 = (int16_t*)take((size_t)total * 512);
-        launch_wav_offsets(c, s, mel_lens, B, 256, woff, wlen);
-        hifigan_forward(c, s, post, 1, B, T, nullptr, w16, wlen, woff);
-        CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, s));
-    } else {
-        int16_t* w16 = (int16_t*)take((size_t)B * T * 256 * 2);
-        hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
-        CUDA_OK(cudaMemcpy2DAsync(h_wav, (size_t)cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
-    }
+    int16_t* w16 = (int16_t*)take(packed ? (size_t)total * 512 : (size_t)B * T * 512);
+    run_graphed(c, s, {1, B, L, T, packed}, (long)rows, [&]() {
+        fs2_phase_b(c, s, T, mel, post, nullptr);
+        if (packed) {
+            launch_wav_offsets(c, s, mel_lens, B, 256, woff, wlen);
+            hifigan_forward(c, s, post, 1, B, T, nullptr, w16, wlen, woff);
+        } else {
+            hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
+        }
+    });
+    if (packed) CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, s));
+    else CUDA_OK(cudaMemcpy2DAsync(h_wav, (size_t)cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
     if (h_tmax) *h_tmax = tmax;
 }
+
+extern "C" {
 
 int masg_synthesize_host(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
                          int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int t_cap,
@@ -525,8 +588,16 @@ int64_t masg_launch_count(masg_ctx* c, int reset) {
     return n;
 }
 
+int masg_debug_enable_taps(masg_ctx* c, int enable) {
+    API_BEGIN(c)
+    c->taps = enable != 0;
+    if (!c->taps) { c->tap_enc = c->tap_lr = c->tap_dec = nullptr; }
+    API_END(c)
+}
+
 int masg_debug_tap(masg_ctx* c, void* stream, const char* name, float* dst, int64_t n_elems) {
     API_BEGIN(c)
+    MASG_CHECK(c->taps, "intermediate taps are off: call masg_debug_enable_taps(ctx, 1) before the forward");
     const float* src = nullptr; int64_t n = 0;
     if (!strcmp(name, "encoder_out")) { src = c->tap_enc; n = (int64_t)c->B * c->L * 256; }
     else if (!strcmp(name, "va_out")) { src = c->va_out; n = (int64_t)c->B * c->L * 256; }

@@ -69,8 +69,20 @@ struct Predictor {
     const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *lin_w; float lin_b;
 };
 
+// One captured CUDA graph of a phase of the host-buffer entry points (api.cu): the launch-bound small-batch path replays
+// ~50-120 kernel launches as one graph launch.  Valid while the library-owned buffers it was captured on have not moved.
+struct GraphEntry {
+    cudaGraphExec_t exec = nullptr;
+    void* snap[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int64_t launches = 0; int seen = 0;
+    // phase-A -> phase-B context state as the captured body left it
+    float* va_out = nullptr; float* d_rounded_dev = nullptr; int64_t* mel_lens_dev = nullptr; const int64_t* src_lens_dev = nullptr;
+};
+
 struct masg_ctx {
     int device = 0, precision = 0, n_sm = 148;
+    std::map<std::vector<long>, GraphEntry> graphs;   // key: (phase, B, L, T, packed)
+    int64_t weights_gen = 0;                          // bumped by every commit: captured graphs bake weight pointers
     std::string err;
     int64_t launches = 0;
     // per-launch device timing of the dense-contraction kernel (masg_profile): event pairs + algorithmic FLOPs
@@ -78,12 +90,15 @@ struct masg_ctx {
     struct ProfRec { cudaEvent_t e0, e1; double flops; };
     std::vector<ProfRec> prof;
     Arena arena;                      // per-forward workspace
-    std::vector<void*> owned;         // repacked weights
+    std::vector<void*> owned;         // repacked weights being built / temporaries of the diagnostic hooks
+    std::vector<void*> owned_fs2, owned_hg;   // ... of the last commit of each model (freed by the next commit of that model)
+    bool taps = false;                // keep copies of the intermediate tensors for masg_debug_tap (masg_debug_enable_taps)
     std::map<std::string, TensorRef> fs2_t, hg_t;
     bool fs2_ready = false, hg_ready = false;
     // ---- FastSpeech2 ----
     int n_enc = 0, n_dec = 0, max_seq_len = 1000;
     const float *word_emb = nullptr, *accent_emb = nullptr, *enc_pos = nullptr, *dec_pos = nullptr;
+    int n_vocab = 0, n_accent = 0;
     float* pos_long = nullptr; int pos_long_n = 0;           // rebuilt table for len > max_seq_len
     std::vector<FFTLayer> enc, dec;
     Predictor pred[3];                                       // duration, pitch, energy
@@ -125,7 +140,8 @@ void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvI
 void launch_conv(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
 
 void launch_embed(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
-                  const float* wemb, const float* aemb, const float* pos, int B, int L, float* out);
+                  const float* wemb, const float* aemb, const float* pos, int B, int L, int n_vocab, int n_accent,
+                  int64_t* err /*nullable device word: bit 0 = phoneme id, bit 1 = accent id out of range*/, float* out);
 void launch_add_rowvec(masg_ctx* c, cudaStream_t s, float* x, const float* v, int B, int L, int C);   // x[b,l,:] += v[b,:]
 void launch_add_pos(masg_ctx* c, cudaStream_t s, float* x, const float* pos, int B, int T, int C);
 // y = LN(x (+res)) * g + b ; rows with t >= lens[b] are zeroed when lens != null
@@ -189,6 +205,7 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
                  const int64_t* src_lens, int B, int L, const float* spk, float p_ctl, float e_ctl, float d_ctl,
                  const float* d_target, const float* p_target, const float* e_target, float* pitch, float* energy, float* log_d,
                  float* d_rounded, int64_t* mel_lens, uint8_t* src_mask, int64_t* h_tmax);
+void fs2_phase_a_publish(masg_ctx* c, cudaStream_t s, int64_t* h_tmax);   // D2H of [mel_lens | T_max | error word] + the one sync
 void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, uint8_t* mel_mask);
 // row_len / row_off (nullable, device int64 [B]): per-utterance trim + packed placement of the output rows (launch_conv_post)
 void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int B, int T, float* wav, int16_t* w16,

@@ -71,9 +71,16 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
     const char* ds_env = getenv("MASG_DEC_MODE");
     const int dec_mode = ds_env ? atoi(ds_env) : 2;
     c->fs2_ready = false;
+    // the repacked buffers of the previous commit are dead once the stream has drained (re-commit after load_state_dict / .to())
+    CUDA_OK(cudaStreamSynchronize(s));
+    for (void* p : c->owned_fs2) cudaFree(p);
+    c->owned_fs2.clear();
+    const size_t owned_mark = c->owned.size();
     c->enc.clear(); c->dec.clear();
-    c->word_emb = T_(m, "encoder.src_word_emb.weight", {-1, 256}).ptr;
-    c->accent_emb = T_(m, "encoder.src_accent_emb.weight", {-1, 256}).ptr;
+    const TensorRef& we = T_(m, "encoder.src_word_emb.weight", {-1, 256});
+    const TensorRef& ae = T_(m, "encoder.src_accent_emb.weight", {-1, 256});
+    c->word_emb = we.ptr; c->n_vocab = (int)we.shape[0];
+    c->accent_emb = ae.ptr; c->n_accent = (int)ae.shape[0];
     const TensorRef& pe = T_(m, "encoder.position_enc", {1, -1, 256});
     c->enc_pos = pe.ptr; c->max_seq_len = (int)pe.shape[1] - 1;
     c->dec_pos = T_(m, "decoder.position_enc", {1, pe.shape[1], 256}).ptr;
@@ -144,6 +151,9 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
     c->gmm_mu_w = T_(m, "speaker_enc.mu_linear.weight", {768, 4}).ptr; c->gmm_mu_b = T_(m, "speaker_enc.mu_linear.bias", {768}).ptr;
     CUDA_OK(cudaStreamSynchronize(s));
     for (int i = 0; i < 3; ++i) c->pred[i].lin_b = lin_b[i];
+    c->weights_gen++;
+    c->owned_fs2.assign(c->owned.begin() + owned_mark, c->owned.end());
+    c->owned.resize(owned_mark);
     c->fs2_ready = true;
 }
 
@@ -153,7 +163,7 @@ static const float* pos_table(masg_ctx* c, cudaStream_t s, bool decoder, int n) 
         int cap = n + 1024;
         float* p = nullptr;
         CUDA_OK(cudaMalloc(&p, (size_t)cap * 256 * sizeof(float)));
-        c->owned.push_back(p);
+        if (c->pos_long) { CUDA_OK(cudaStreamSynchronize(s)); cudaFree(c->pos_long); }     // the shorter table is dead after the sync
         launch_pos_table(c, s, cap, p);
         c->pos_long = p; c->pos_long_n = cap;
     }
@@ -273,18 +283,16 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
     // persistent phase-A → phase-B state first
     c->va_out = ar.get<float>(rows * 256);
     c->d_rounded_dev = ar.get<float>(rows);
-    c->mel_lens_dev = ar.get<int64_t>(B + 1);
-    c->tap_enc = ar.get<float>(rows * 256);
+    c->mel_lens_dev = ar.get<int64_t>(B + 2);                                   // [mel_lens (B) | T_max | error word]
+    c->tap_enc = c->taps ? ar.get<float>(rows * 256) : nullptr;
     c->B = B; c->L = L; c->src_lens_dev = src_lens;
     if (src_mask) launch_mask(c, s, src_lens, B, L, src_mask);
     const float* pos = pos_table(c, s, false, L);
-    {
-        float* x = c->tap_enc;
-        launch_embed(c, s, texts, accents, acc1d, c->word_emb, c->accent_emb, pos, B, L, x);
-        for (auto& Lr : c->enc) fft_block_f32(c, s, ar, Lr, x, src_lens, B, L);
-    }
     float* x = c->va_out;
-    CUDA_OK(cudaMemcpyAsync(x, c->tap_enc, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    CUDA_OK(cudaMemsetAsync(c->mel_lens_dev + B + 1, 0, sizeof(int64_t), s));
+    launch_embed(c, s, texts, accents, acc1d, c->word_emb, c->accent_emb, pos, B, L, c->n_vocab, c->n_accent, c->mel_lens_dev + B + 1, x);
+    for (auto& Lr : c->enc) fft_block_f32(c, s, ar, Lr, x, src_lens, B, L);
+    if (c->taps) CUDA_OK(cudaMemcpyAsync(c->tap_enc, x, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));   // opt-in debug copy
     launch_add_rowvec(c, s, x, spk, B, L, 256);                                 // pads too (fastspeech2.py:215-218)
     auto predict = [&](int which, float scale, float* out) {
         predictor_f32(c, s, ar, c->pred[which], x, src_lens, B, L, scale, out);
@@ -300,17 +308,25 @@ void fs2_phase_a(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_
     if (d_rounded) CUDA_OK(cudaMemcpyAsync(d_rounded, c->d_rounded_dev, rows * sizeof(float), cudaMemcpyDeviceToDevice, s));
     launch_mel_lens(c, s, c->d_rounded_dev, B, L, c->mel_lens_dev, c->mel_lens_dev + B);
     if (mel_lens) CUDA_OK(cudaMemcpyAsync(mel_lens, c->mel_lens_dev, B * sizeof(int64_t), cudaMemcpyDeviceToDevice, s));
-    if (h_tmax) {
-        if (c->h_pinned_n < B + 1) {
+    if (h_tmax) fs2_phase_a_publish(c, s, h_tmax);
+}
+
+// the single documented synchronisation of phase A: [mel_lens (B) | T_max | error word] -> pinned host scratch
+void fs2_phase_a_publish(masg_ctx* c, cudaStream_t s, int64_t* h_tmax) {
+    const int B = c->B;
+    {
+        if (c->h_pinned_n < B + 2) {
             if (c->h_pinned) cudaFreeHost(c->h_pinned);
             c->h_pinned = nullptr; c->h_pinned_n = 0;
-            CUDA_OK(cudaMallocHost(&c->h_pinned, (size_t)(B + 1 + 64) * sizeof(int64_t)));
-            c->h_pinned_n = B + 1 + 64;
+            CUDA_OK(cudaMallocHost(&c->h_pinned, (size_t)(B + 2 + 64) * sizeof(int64_t)));
+            c->h_pinned_n = B + 2 + 64;
         }
-        // [mel_lens (B) | T_max] in one copy: the host-buffer entry points size their trimmed D2H from the lengths
-        CUDA_OK(cudaMemcpyAsync(c->h_pinned, c->mel_lens_dev, (size_t)(B + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+        // [mel_lens (B) | T_max | error word] in one copy: the host-buffer entry points size their trimmed D2H from the lengths
+        CUDA_OK(cudaMemcpyAsync(c->h_pinned, c->mel_lens_dev, (size_t)(B + 2) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
         CUDA_OK(cudaStreamSynchronize(s));                                      // the single documented sync
         *h_tmax = c->h_pinned[B];
+        MASG_CHECK(c->h_pinned[B + 1] == 0, "%s id outside its embedding table (nn.Embedding raises IndexError: transformer/Models.py:101-103)",
+                   (c->h_pinned[B + 1] & 1) ? "phoneme" : "accent");
     }
 }
 
@@ -321,15 +337,16 @@ void fs2_phase_b(masg_ctx* c, cudaStream_t s, int T, float* mel, float* post, ui
     Arena& ar = c->arena_b;
     ar.reset();
     size_t rows = (size_t)B * T;
-    c->tap_lr = ar.get<float>(rows * 256);
-    c->tap_dec = ar.get<float>(rows * 256);
+    float* x = ar.get<float>(rows * 256);
+    c->tap_lr = c->taps ? ar.get<float>(rows * 256) : nullptr;
+    c->tap_dec = c->taps ? x : nullptr;
     c->tap_T = T;
-    launch_length_regulate(c, s, c->va_out, c->d_rounded_dev, B, L, 256, T, nullptr, c->tap_lr, nullptr, mel_mask);
     const float* pos = pos_table(c, s, true, T);
     const int64_t* lens = c->mel_lens_dev;
-    float* x = c->tap_dec;
-    CUDA_OK(cudaMemcpyAsync(x, c->tap_lr, rows * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
-    launch_add_pos(c, s, x, pos, B, T, 256);
+    // LengthRegulator with the decoder's position encoding added on the way out (valid and padded rows: Models.py:176-180 adds
+    // it to the zero-padded batch); the un-encoded copy exists only for the opt-in debug tap
+    if (c->taps) launch_length_regulate(c, s, c->va_out, c->d_rounded_dev, B, L, 256, T, nullptr, c->tap_lr, nullptr, nullptr);
+    launch_length_regulate(c, s, c->va_out, c->d_rounded_dev, B, L, 256, T, pos, x, nullptr, mel_mask);
     {
         // between decoder blocks the LayerNorm output also travels as planar fp16 (the next block's QKV operand)
         const bool pl = c->precision == MASG_PREC_BF16 && !c->dec.empty() && c->dec[0].qkv.f16 && ln_planar(2);

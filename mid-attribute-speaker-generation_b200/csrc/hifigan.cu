@@ -37,6 +37,10 @@ static const float* bias_of(masg_ctx* c, const std::string& name, int n) {
 
 void hifigan_commit(masg_ctx* c, cudaStream_t s) {
     c->hg_ready = false;
+    CUDA_OK(cudaStreamSynchronize(s));                       // previous generation of repacked buffers: dead once the stream drained
+    for (void* p : c->owned_hg) cudaFree(p);
+    c->owned_hg.clear();
+    const size_t owned_mark = c->owned.size();
     std::vector<int64_t> sh;
     const float* w = folded_weight(c, s, "conv_pre", sh);
     MASG_CHECK(sh[0] == 512 && sh[1] == 80 && sh[2] == 7, "conv_pre must be (512,80,7): unsupported generator config");
@@ -78,6 +82,9 @@ void hifigan_commit(masg_ctx* c, cudaStream_t s) {
     CUDA_OK(cudaMemcpyAsync(&pb, bias_of(c, "conv_post", 1), 4, cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaStreamSynchronize(s));
     c->hg_post_b = pb;
+    c->weights_gen++;
+    c->owned_hg.assign(c->owned.begin() + owned_mark, c->owned.end());
+    c->owned.resize(owned_mark);
     c->hg_ready = true;
 }
 
@@ -157,6 +164,7 @@ void hifigan_forward(masg_ctx* c, cudaStream_t s, const float* mel, int cl, int 
     const size_t esz = bf ? 2 : 4;
     Arena& ar = c->arena_b;
     ar.reset();
+    c->tap_lr = c->tap_dec = nullptr;                        // the phase-B debug taps lived in this arena
     const float* melT = mel;
     if (!cl) {
         float* t = ar.get<float>((size_t)B * T * 80);

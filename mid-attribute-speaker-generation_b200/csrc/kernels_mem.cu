@@ -25,13 +25,18 @@ static inline int cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 // ------------------------------------------------------------------------------------------------
 __global__ void k_embed(const int64_t* __restrict__ texts, const int64_t* __restrict__ accents, int acc1d,
                         const float4* __restrict__ wemb, const float4* __restrict__ aemb,
-                        const float4* __restrict__ pos, int B, int L, float4* __restrict__ out) {
+                        const float4* __restrict__ pos, int B, int L, int n_vocab, int n_accent,
+                        unsigned long long* __restrict__ err, float4* __restrict__ out) {
     int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     int lane = threadIdx.x & 31;
     if (row >= B * L) return;
     int l = row % L;
     long id = texts[row];
     long ac = acc1d ? accents[l] : accents[row];
+    // nn.Embedding raises IndexError on an id outside its table; here the row is read as id 0 and the error word is raised
+    // (checked by the host at phase A's synchronisation)
+    if (id < 0 || id >= n_vocab) { if (lane == 0 && err) atomicOr(err, 1ull); id = 0; }
+    if (ac < 0 || ac >= n_accent) { if (lane == 0 && err) atomicOr(err, 2ull); ac = 0; }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         int c = lane + 32 * h;
@@ -42,9 +47,10 @@ __global__ void k_embed(const int64_t* __restrict__ texts, const int64_t* __rest
     }
 }
 void launch_embed(masg_ctx* c, cudaStream_t s, const int64_t* texts, const int64_t* accents, int acc1d,
-                  const float* wemb, const float* aemb, const float* pos, int B, int L, float* out) {
+                  const float* wemb, const float* aemb, const float* pos, int B, int L, int n_vocab, int n_accent, int64_t* err,
+                  float* out) {
     k_embed<<<cdiv((long)B * L, 8), 256, 0, s>>>(texts, accents, acc1d, (const float4*)wemb, (const float4*)aemb,
-                                                 (const float4*)pos, B, L, (float4*)out);
+                                                 (const float4*)pos, B, L, n_vocab, n_accent, (unsigned long long*)err, (float4*)out);
     c->launches++;
 }
 
@@ -183,10 +189,10 @@ __global__ void k_bucket_add(const float* __restrict__ v, const float* __restric
     int lane = threadIdx.x & 31;
     if (row >= rows) return;
     float val = v[row];
-    int lo = 0, hi = nb;                 // first i with bins[i] >= val
+    int lo = 0, hi = nb;                 // first i with bins[i] >= val; NaN compares false everywhere: torch.bucketize sends it to nb
     while (lo < hi) {
         int mid = (lo + hi) >> 1;
-        if (bins[mid] < val) lo = mid + 1; else hi = mid;
+        if (!(bins[mid] >= val)) lo = mid + 1; else hi = mid;
     }
     if (idx_out && lane == 0) idx_out[row] = lo;
     for (int c = lane; c < C4; c += 32) {

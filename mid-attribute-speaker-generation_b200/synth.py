@@ -102,7 +102,8 @@ class Synthesizer:
         budget (plan_batches), each batch runs through masg_synthesize_host_packed (trim on the device, one D2H of the valid
         samples) and, with ``out_dir``, a background writer emits ``<speaker>_<text id>.wav`` while the next batch is synthesised;
         the embeddings are saved as ``<speaker>.npy`` ([1, 256] float32, the reference's format).
-        Returns a list of dicts (speaker, text_id, path or wav, samples, mel_len) in (speaker, text) order."""
+        Returns a list of dicts (speaker, text_id, path or wav, samples, mel_len, and the batch / row / padded length the utterance
+        was synthesised in — the reference's outputs depend on the padding) in (speaker, text) order."""
         from .wavio import WavWriter
         from .fastspeech2 import gmm_sample
         ids, acc, lens = (torch.as_tensor(texts[k]).to("cpu", torch.int64) for k in ("texts", "accents", "src_lens"))
@@ -138,7 +139,7 @@ class Synthesizer:
         try:
             if out_dir is not None and save_embeddings:
                 save_speaker_embeddings(out_dir, speaker_names, emb)
-            for idx in batches:
+            for bi, idx in enumerate(batches):
                 t_idx = torch.from_numpy(utt_text[idx])
                 L = int(utt_len[idx].max())
                 b_ids, b_acc, b_len = ids[t_idx, :L].contiguous(), acc[t_idx, :L].contiguous(), lens[t_idx].contiguous()
@@ -157,7 +158,7 @@ class Synthesizer:
                 for k, u in enumerate(idx):
                     wav = flat[off[k]: off[k + 1]]
                     rec = {"speaker": speaker_names[utt_spk[u]], "text_id": text_ids[utt_text[u]], "samples": int(off[k + 1] - off[k]),
-                           "mel_len": int(h_m[k])}
+                           "mel_len": int(h_m[k]), "batch": bi, "row": k, "padded_to": L}
                     if out_dir is not None:
                         rec["path"] = os.path.join(str(out_dir), "%s_%s.wav" % (rec["speaker"], rec["text_id"]))
                         writer.submit(rec["path"], sampling_rate, wav, copy=True)     # the pinned buffer is reused by the next batch

@@ -91,19 +91,24 @@ def test_generation_driver_n_speakers_x_m_texts(tmp_path, golden_dir):
     embs = load_speaker_embeddings([out / (n + ".npy") for n in names])
     assert embs.shape == (6, 256) and torch.equal(embs, fs2.speaker_gen(metas.to(DEV), seed=3).cpu())
     hsd_f = restate.fold_weight_norm(hsd)
-    for k in (0, 7, 29):
-        r = res[k]
+    assert len({r["batch"] for r in res}) >= 4
+    checked = 0
+    for k, r in enumerate(res):
         rate, data = wavfile.read(r["path"])
         assert rate == 22050 and len(data) == r["samples"] == r["mel_len"] * 256
         si, ti = k // 5, k % 5
         L = int(tok["src_lens"][ti])
+        assert r["mel_len"] == 3 * L and r["padded_to"] >= L
+        # the reference's result depends on the padding of the batch an utterance sits in (pad leak into the last phonemes,
+        # then global attention: SURVEY Appendix B-1), so a solo oracle run is comparable for the un-padded rows: the longest
+        # utterance of each batch
+        if r["padded_to"] != L or checked >= 3:
+            continue
         ref = restate.fs2_forward(sd, tok["texts"][ti:ti + 1, :L], tok["accents"][ti:ti + 1, :L], tok["src_lens"][ti:ti + 1], L, embs[si:si + 1])
-        assert int(ref[9][0]) == r["mel_len"] == 3 * L
-        # batch-mates are longer utterances, so this row's padded tail differs from the solo oracle run: compare away from the
-        # last 11 frames (pad leak)
-        n = (r["mel_len"] - 11) * 256
         ref_wav = restate.hifigan_forward(hsd_f, ref[1].transpose(1, 2))[0, 0]
-        assert helpers.snr_db(ref_wav[:n].numpy(), data[:n].astype(np.float64) / 32768.0) >= 60.0
+        assert helpers.snr_db(ref_wav.numpy(), data.astype(np.float64) / 32768.0) >= 60.0
+        checked += 1
+    assert checked == 3
     # a distribution as the speaker source: one batched draw for all speakers, no files
     from masg_b200.distributions import InterpolateGMM
     da = fs2.speaker_distribution(metas[0:1].to(DEV)); db = fs2.speaker_distribution(metas[3:4].to(DEV))
@@ -191,3 +196,65 @@ def test_synth_samples_dropin_against_the_reference_function(tmp_path):
         r1, d1 = wavfile.read(str(refdir / os.path.basename(p)))
         assert r0 == r1 == 22050 and d0.shape == d1.shape and d0.dtype == d1.dtype == np.int16
         assert np.abs(d0.astype(np.int32) - d1.astype(np.int32)).max() <= 4
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_small_batch_graph_replay_is_bit_identical(packed):
+    """The latency path (host-buffer entry points, <= 512 phoneme rows): first call plain, second captured into CUDA graphs
+    (phase A; phase B + vocoder), later calls replayed — same audio bit for bit, same kernel count claimed, and a change of
+    inputs, controls or shape must not replay a stale graph."""
+    from masg_b200.synth import Synthesizer
+    fs2, sd = helpers.fs2_on_gpu(11, "spread", "bf16")
+    voc, hsd = helpers.hifigan_on_gpu(4321, "bf16")
+    s = Synthesizer(fs2, voc, "bf16")
+    b = syn.make_batch(2, 24, seed=41, lens=[24, 13])
+    emb = torch.randn(2, 256, generator=torch.Generator().manual_seed(4)) * 0.5
+
+    def call(bb, e, **kw):
+        n0 = s.ctx.launch_count()
+        if packed:
+            w, o, m, T, _, _ = s.synthesize_host_packed(bb["texts"], bb["accents"], bb["src_lens"], e, 2 * 600 * 256, **kw)
+            return w[: int(o[-1])].clone(), m.clone(), s.ctx.launch_count() - n0
+        w, m, T, _, _ = s.synthesize_host(bb["texts"], bb["accents"], bb["src_lens"], e, 600, **kw)
+        return w[:, : T * 256].clone(), m.clone(), s.ctx.launch_count() - n0
+
+    runs = [call(b, emb) for _ in range(4)]                                   # plain, capture, replay, replay
+    for w, m, n in runs[1:]:
+        assert torch.equal(w, runs[0][0]) and torch.equal(m, runs[0][1]) and n == runs[0][2]
+    emb2 = emb * 0.5
+    w2, m2, _ = call(b, emb2)                                                  # new inputs through the replayed graph
+    gb = helpers.to_gpu(b)
+    ref16, ref_m, _ = s.synthesize(gb["texts"], gb["accents"], gb["src_lens"], emb2.to(DEV))
+    assert torch.equal(m2, ref_m.cpu())
+    if packed:
+        assert torch.equal(w2[: int(m2[0]) * 256], ref16[0, : int(m2[0]) * 256].cpu())
+    else:
+        assert torch.equal(w2, ref16.cpu())
+    w3, m3, _ = call(b, emb, d_control=1.5)                                    # another control value: another graph key
+    assert int(m3.sum()) > int(runs[0][1].sum())
+    w4, m4, _ = call(b, emb)
+    assert torch.equal(w4, runs[0][0])
+
+
+def test_out_of_range_ids_raise_like_nn_embedding():
+    """transformer/Models.py:101-103: nn.Embedding raises IndexError for an id outside its table; the kernel flags it and the
+    host raises at phase A's synchronisation instead of reading out of bounds."""
+    fs2, sd = helpers.fs2_on_gpu(11, "spread", "fp32")
+    b = syn.make_batch(2, 9, seed=3)
+    gb = helpers.to_gpu(b)
+    emb = torch.zeros(2, 256, device=DEV)
+    bad = gb["texts"].clone(); bad[1, 4] = 429
+    with pytest.raises(RuntimeError, match="phoneme id"):
+        fs2.synthesize_from_speaker_emb(None, bad, gb["src_lens"], 9, accents=gb["accents"], speaker_emb=emb)
+    bad_a = gb["accents"].clone(); bad_a[0, 0] = -1
+    with pytest.raises(RuntimeError, match="accent id"):
+        fs2.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], 9, accents=bad_a, speaker_emb=emb)
+    out = fs2.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], 9, accents=gb["accents"], speaker_emb=emb)   # still healthy
+    assert torch.isfinite(out[1]).all()
+    # torch.bucketize sends NaN to the last bucket (index 255)
+    from masg_b200 import _lib
+    cx = _lib.default_context(DEV, "fp32")
+    v = torch.tensor([float("nan"), 0.0], device=DEV); bins = torch.linspace(-1, 1, 255, device=DEV)
+    table = torch.zeros(256, 256, device=DEV); x = torch.zeros(2, 256, device=DEV); idx = torch.empty(2, dtype=torch.int64, device=DEV)
+    cx.check(cx.lib.masg_bucketize_embed_add(cx.h, cx.stream(), _lib.ptr(v), _lib.ptr(bins), 255, _lib.ptr(table), 2, 256, _lib.ptr(x), _lib.ptr(idx)), "bucket")
+    assert idx.tolist() == torch.bucketize(v.cpu(), bins.cpu()).tolist() == [255, 127]

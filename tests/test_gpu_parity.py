@@ -134,10 +134,19 @@ def test_fs2_matches_oracle_ragged_batch(precision):
     emb = torch.randn(4, 256, generator=g) * 0.5
     taps = {}
     ref = restate.fs2_forward(sd, b["texts"], b["accents"], b["src_lens"], 40, emb, p_control=0.9, d_control=1.2, taps=taps)
+    cx = model._context()
+    with pytest.raises(RuntimeError):
+        cx.tap("encoder_out", (4, 40, 256))                                   # taps are opt-in (they cost two activation copies)
+    cx.enable_taps(True)
     out = _run_fs2(model, b, emb, p_control=0.9, d_control=1.2)
     tol = MEL_TOL[precision]
-    enc = model._context().tap("encoder_out", (4, 40, 256)).cpu()
+    enc = cx.tap("encoder_out", (4, 40, 256)).cpu()
     assert (enc - taps["encoder_out"]).abs().max() <= tol * 2
+    T_ = out[0].shape[1]
+    if torch.equal(out[5].cpu(), ref[5]):
+        assert (cx.tap("lr_out", (4, T_, 256)).cpu() - taps["lr_out"]).abs().max() <= 4.0 + tol   # a bucket flip moves one embedding row
+        assert (cx.tap("decoder_out", (4, T_, 256)).cpu() - taps["decoder_out"]).abs().max() <= 1.0
+    cx.enable_taps(False)
     for i, name in ((2, "pitch"), (3, "energy"), (4, "log_d")):
         assert (out[i].cpu() - ref[i]).abs().max() <= tol * 4, name
     assert torch.equal(out[6].cpu(), ref[6]) and torch.equal(out[8].cpu(), b["src_lens"])

@@ -14,6 +14,7 @@ b = {k: (v[:B] if torch.is_tensor(v) else v) for k, v in b.items()}
 g = torch.Generator().manual_seed(3)
 emb = (torch.randn(64, 256, generator=g) * 0.5)[:B]
 gb = helpers.to_gpu(b)
+fs2._context().enable_taps(True)
 out = fs2.synthesize_from_speaker_emb(None, gb["texts"], gb["src_lens"], L, accents=gb["accents"], speaker_emb=emb.cuda())
 torch.cuda.synchronize()
 T = out[0].shape[1]
