@@ -60,6 +60,7 @@ void masg_ctx_destroy(masg_ctx* c) {
     free_owned(c);
     c->arena.release(); c->arena_b.release();
     for (auto& kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (c->cap_stream) cudaStreamDestroy(c->cap_stream);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->io_buf) cudaFree(c->io_buf);
     if (c->out_buf) cudaFree(c->out_buf);
@@ -289,7 +290,7 @@ static int graph_rows_limit() {
 }
 template <typename F>
 static void run_graphed(masg_ctx* c, cudaStream_t s, const std::vector<long>& key, long rows, F body) {
-    if (rows > graph_rows_limit() || c->profiling || c->taps) { body(); return; }
+    if (rows > graph_rows_limit() || c->profiling || c->taps) { body(s); return; }
     GraphEntry& e = c->graphs[key];
     void* snap[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
     const bool same = !memcmp(snap, e.snap, sizeof(snap));
@@ -301,22 +302,25 @@ static void run_graphed(masg_ctx* c, cudaStream_t s, const std::vector<long>& ke
     }
     if (e.exec) { cudaGraphExecDestroy(e.exec); e.exec = nullptr; }
     if (e.seen++ == 0 || !same) {                             // plain run; remember where the buffers are now
-        body();
+        body(s);
         void* after[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
         memcpy(e.snap, after, sizeof(after));
         return;
     }
+    // the caller's stream may be the legacy default stream, which cannot be captured: the body is recorded on a stream of the
+    // context's own and the instantiated graph is then launched into the caller's stream
+    if (!c->cap_stream) CUDA_OK(cudaStreamCreateWithFlags(&c->cap_stream, cudaStreamNonBlocking));
     const int64_t l0 = c->launches;
-    CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
-    try { body(); }
-    catch (...) { cudaGraph_t g = nullptr; cudaStreamEndCapture(s, &g); if (g) cudaGraphDestroy(g); throw; }
+    CUDA_OK(cudaStreamBeginCapture(c->cap_stream, cudaStreamCaptureModeRelaxed));
+    try { body(c->cap_stream); }
+    catch (...) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->cap_stream, &g); if (g) cudaGraphDestroy(g); throw; }
     cudaGraph_t g = nullptr;
-    CUDA_OK(cudaStreamEndCapture(s, &g));
+    CUDA_OK(cudaStreamEndCapture(c->cap_stream, &g));
     void* after[6] = {c->arena.base, c->arena_b.base, c->io_buf, c->out_buf, (void*)(intptr_t)c->weights_gen, c->pos_long};
     if (memcmp(after, snap, sizeof(after))) {                 // a buffer moved while capturing: the graph is stale already
         cudaGraphDestroy(g);
         memcpy(e.snap, after, sizeof(after));
-        body();
+        body(s);
         return;
     }
     cudaError_t ie = cudaGraphInstantiate(&e.exec, g, 0);
@@ -359,8 +363,8 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     int64_t tmax = 0;
     // the controls are baked into a captured graph: they are part of the key (as float bit patterns)
     auto fbits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return (long)u; };
-    run_graphed(c, s, {0, B, L, 0, 0, fbits(p_ctl), fbits(d_ctl)}, (long)rows, [&]() {
-        fs2_phase_a(c, s, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
+    run_graphed(c, s, {0, B, L, 0, 0, fbits(p_ctl), fbits(d_ctl)}, (long)rows, [&](cudaStream_t bs) {
+        fs2_phase_a(c, bs, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
                     nullptr, nullptr);
     });
     fs2_phase_a_publish(c, s, &tmax);
@@ -380,13 +384,13 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     p = (char*)c->out_buf;
     float* mel = (float*)take((size_t)B * T * 80 * 4); float* post = (float*)take((size_t)B * T * 80 * 4);
     int16_t* w16 = (int16_t*)take(packed ? (size_t)total * 512 : (size_t)B * T * 512);
-    run_graphed(c, s, {1, B, L, T, packed}, (long)rows, [&]() {
-        fs2_phase_b(c, s, T, mel, post, nullptr);
+    run_graphed(c, s, {1, B, L, T, packed}, (long)rows, [&](cudaStream_t bs) {
+        fs2_phase_b(c, bs, T, mel, post, nullptr);
         if (packed) {
-            launch_wav_offsets(c, s, mel_lens, B, 256, woff, wlen);
-            hifigan_forward(c, s, post, 1, B, T, nullptr, w16, wlen, woff);
+            launch_wav_offsets(c, bs, mel_lens, B, 256, woff, wlen);
+            hifigan_forward(c, bs, post, 1, B, T, nullptr, w16, wlen, woff);
         } else {
-            hifigan_forward(c, s, post, 1, B, T, nullptr, w16);
+            hifigan_forward(c, bs, post, 1, B, T, nullptr, w16);
         }
     });
     if (packed) CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, s));

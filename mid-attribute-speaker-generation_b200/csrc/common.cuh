@@ -82,6 +82,7 @@ struct GraphEntry {
 struct masg_ctx {
     int device = 0, precision = 0, n_sm = 148;
     std::map<std::vector<long>, GraphEntry> graphs;   // key: (phase, B, L, T, packed)
+    cudaStream_t cap_stream = nullptr;                // graphs are recorded here (the caller's stream may be the legacy stream)
     int64_t weights_gen = 0;                          // bumped by every commit: captured graphs bake weight pointers
     std::string err;
     int64_t launches = 0;
