@@ -51,7 +51,12 @@ def _ncu_traffic():
     (profiles/r*_ncu_full_conv_tc_*.csv, written by tools/ncu_summary.py).  A profiler number, reported beside the live ones."""
     import csv, glob
     # r<round>_ncu_<full|dram>_conv_tc_<tag>.csv: `--set full` captures and the cheaper DRAM / tensor-pipe metric captures; newest tag wins
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_*_conv_tc_*.csv")), key=lambda f: os.path.basename(f).rsplit("_", 1)[1])
+    import re
+
+    def order(f):
+        m = re.match(r"r(\d+)_ncu_.*_conv_tc_(.*)\.csv", os.path.basename(f))
+        return (int(m.group(1)), m.group(2)) if m else (0, "")
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_*_conv_tc_*.csv")), key=order)
     if not files:
         return None, None
     rows = list(csv.DictReader(open(files[-1])))
@@ -411,9 +416,22 @@ def run_ours(args):
             return float(t.item())
         return x
 
+    # --gather (N > 1): the optional NCCL all-gather of every rank's int16 audio, issued on a side stream after each
+    # step and waited for one step later, so the transfer of batch n overlaps the kernels of batch n + 1
+    gather = None
+    if args.gather and world > 1:
+        from masg_b200.synth import WaveformGather
+        gather = WaveformGather()
+        g_off = torch.arange(B + 1, dtype=torch.int64, device=dev) * (3 * L * syn.HOP)
+    pending = [None]
+
     def step_device():
         emb = sampler.sample()
         w16, mel_lens, _ = synth.synthesize(texts, accents, lens, emb)
+        if gather is not None:
+            if pending[0] is not None:
+                pending[0].wait()
+            pending[0] = gather.start(w16.view(-1), g_off)
         return w16, mel_lens
 
     # ---- device-resident throughput -----------------------------------------------------------------
@@ -440,10 +458,15 @@ def run_ours(args):
         ev[i][0].record()
         w16, mel_lens = step_device()
         ev[i][1].record()
+    if pending[0] is not None:
+        got = pending[0].wait()                                              # the last step's gather is inside the barrier-to-barrier span
+        pending[0] = None
+        assert len(got) == world and all(int(o[-1]) == B * 3 * L * syn.HOP for _, o in got)
     barrier()
     launches = ctx.launch_count()
     ms_dev = sum(a.elapsed_time(b) for a, b in ev)
     ms_dev = max_over_ranks(ms_dev)
+    gather_was_on, gather = gather is not None, None                         # the e2e / roofline legs below run without it
     assert int(mel_lens.sum().item()) == B * 3 * L, "unexpected mel lengths (benchmark shape is 3 frames/phoneme)"
     value = world * audio_per_step * args.steps / (ms_dev / 1e3)
 
@@ -513,6 +536,8 @@ def run_ours(args):
         "precision": args.precision + (" (HiFi-GAN bf16; FastSpeech2 encoder + variance predictors split-bf16 hi/lo, 3 MMAs per K step; decoder, mel_linear, PostNet fp16 operands; fp32 accumulation everywhere)" if args.precision == "bf16" else ""),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
+        "gather": ({"collective": "NCCL all_gather of every rank's int16 audio (padded-to-max exchange + counts), side stream, overlapped with the next step",
+                    "bytes_per_rank_per_step": B * 3 * L * syn.HOP * 2} if gather_was_on else None),
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc (tcgen05 implicit-GEMM conv1d / linear / convT and the fused ResBlock pairs)", "achieved": ach, "peak": pk["tflops"],
                      "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
@@ -687,6 +712,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"], help="c3 = the headline configuration (default); c4 / c5 = the sharded configurations of BASELINE.json")
     ap.add_argument("--frame-budget", type=int, default=40000, help="c4: padded frames per batch")
     ap.add_argument("--max-batch", type=int, default=64, help="c4: utterances per batch")
+    ap.add_argument("--gather", action="store_true", help="N > 1: all-gather every rank's int16 audio over NCCL each step (optional collective of SURVEY 8(e))")
     ap.add_argument("--profile-range", action="store_true", help="warm up, then run ONE step inside cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":

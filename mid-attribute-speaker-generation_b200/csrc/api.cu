@@ -277,14 +277,15 @@ int masg_gmm_barycenter(masg_ctx* c, void* stream, const float* pi, const float*
 }  // extern "C"
 
 // Replay `body` (a sequence of kernel launches on library-owned buffers) as a CUDA graph when the small-batch latency path asks
-// for it (MASG_GRAPH=1, or automatically for batches of <= MASG_GRAPH_ROWS phoneme rows).  First sight of a key: plain run
+// for it (MASG_GRAPH=1 / 0, or automatically for batches of <= MASG_GRAPH_ROWS = 4096 phoneme rows; measured: nothing at C2 —
+// its 161 kernels take 20-30 us each, the launches are not the limit — and 4 % at 2 x 1000 phonemes, the C5-on-8-GPUs shard).  First sight of a key: plain run
 // (sizes the arenas, sets kernel attributes); second: capture + instantiate + launch; afterwards: one cudaGraphLaunch, as long
 // as no buffer the captured kernels point into has moved and the weights have not been re-committed.
 static int graph_rows_limit() {
     static int lim = -2;
     if (lim == -2) {
         const char* g = getenv("MASG_GRAPH"); const char* r = getenv("MASG_GRAPH_ROWS");
-        lim = g ? (atoi(g) ? (1 << 30) : -1) : (r ? atoi(r) : 512);
+        lim = g ? (atoi(g) ? (1 << 30) : -1) : (r ? atoi(r) : 4096);
     }
     return lim;
 }

@@ -135,6 +135,9 @@ struct ConvIO {
     int in_act = ACT_NONE; float in_slope = 0.f;
     int out_act = ACT_NONE; float out_slope = 0.f;
     const void* R1 = nullptr; const void* R2 = nullptr; int r_bf16 = 0; float out_scale = 1.f;   // residuals (fp32 or bf16)
+    // fused LayerNorm epilogue (tcgen05 path, N == 256 == one tile row): Y = mask(LN(act(acc + bias) + R1) * ln_g + ln_b), rows with
+    // t >= ln_lens[b] written as zeros (Layers.py:25,28); Y16p (nullable) = the same as planar fp16 [B][32][ln_T][8]
+    const float* ln_g = nullptr; const float* ln_b = nullptr; const int64_t* ln_lens = nullptr; int ln_T = 0; bf16* Y16p = nullptr;
 };
 void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
 // precision dispatch: MASG_PREC_FP32 → conv_simt.cu, MASG_PREC_BF16 → conv_tc.cu (tcgen05)

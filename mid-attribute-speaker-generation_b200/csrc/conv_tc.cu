@@ -49,6 +49,11 @@ constexpr int A_WARP0 = 14;             // activation workers
 constexpr int A_WARPS = 8;
 constexpr int A_THREADS = A_WARPS * 32;
 constexpr int NTHREADS = (A_WARP0 + A_WARPS) * 32;     // 704
+// Per-role register budgets (setmaxnreg.dec in the issuer / copy groups, .inc in the epilogue groups, 768 threads = six aligned
+// groups of four warps) were tried in round 2 and do not pay: ptxas then allocates each role's region at that role's cap, and
+// every split of the 61,440 registers that was tried (epilogue / control / workers = 128/40/72, 112/56/72, 104/56/80, 96/64/80)
+// spills MORE (300-3,000 bytes per thread against 64-144 at a uniform 80): the fully unrolled issue loops and the fp32 staging
+// loop need ~80 registers themselves, so there is nothing to give to the epilogue.
 constexpr int W_STAGES = 4;
 constexpr int W_STAGE_BYTES = 16384;
 constexpr int A_SLOTS = 3;
@@ -76,6 +81,8 @@ struct TcArgs {
     int w_resident;                                    // the whole weight set is one stage, loaded once per CTA
     int res_pf;                                        // copy warp prefetches the tile's residual rows into L2 (MASG_TC_RESPF, default on)
     int w_stages;                                      // weight ring depth (3 with 32 KB stages, else 4 with 16 KB stages)
+    // fused LayerNorm epilogue (NT == N == 256, row-major fp32 output): see epi_layernorm
+    const float* ln_g; const float* ln_b; const int64_t* ln_lens; int ln_T; bf16* Y16p;
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
 
@@ -160,6 +167,10 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
         TRACE(tr, 2, it, 0);
         const uint32_t tacc_w = tmem_base + (uint32_t)(accb * MS * NT + w * NT);
         uint32_t accum = 0;
+        // (Not issuing the MMAs of a sub-tile that starts beyond the utterance's last row — the tail tile of T = 600 covers rows
+        // 512..767, its second sub-tile is empty: 1 of 6 — was tried: the test inside the issue loop slows EVERY layer of this
+        // instantiation by ~10 % (stage-1 k = 11 0.335 -> 0.375 ms, w_1 0.192 -> 0.210): one thread issues an instruction every
+        // few cycles and has no slack.  Removed.)
         int g = a.G;                                                       // forces a stage fetch before the first blob
         bool have_stage = false;
         uint32_t wbase16 = 0;
@@ -424,6 +435,100 @@ __device__ __forceinline__ void epi_res_run(const TcArgs& a, const ResTile& t, c
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused LayerNorm epilogue: the CTA owns whole 256-column rows (NT = N = 256, one 128-row accumulator), so
+// fc / w_2 (+ bias + residual) -> LayerNorm -> pad-row zeroing (SubLayers.py:54-55,88-91 + Layers.py:25,28) and the variance
+// predictors' conv -> ReLU -> LayerNorm (modules.py:209-240) never leave the SM between the GEMM and the normalised output.
+// Thread = (row = TMEM lane, column half).  Pass 1 adds bias, activation and the residual row, parks the result back in TMEM
+// (tcgen05.st) and sums it; pass 2 re-reads it for the centred second moment (the two-pass form nn.LayerNorm uses); pass 3
+// normalises and stores fp32 row-major and, optionally, the planar fp16 copy the next fp16 layer consumes.  The two column
+// halves of a row meet through 2 KB of shared memory and a 64-thread named barrier per lane quadrant.
+// ---------------------------------------------------------------------------------------------
+// PARTS = 2: the eight epilogue warps (column halves).  PARTS = 4: the eight activation-worker warps join when they have nothing
+// to stage (planar input without an input activation: the decoder side) — a row is then shared by four threads, which doubles
+// the residual bytes in flight per SM; the epilogue is bound by exactly that (one 64-byte run per thread at ~1 us of latency:
+// 16 KB per SM = 2.4 TB/s chip-wide; what-if timing: fc 26 us without its loads and stores, 69 us with them).
+template <int PARTS>
+__device__ __forceinline__ void epi_layernorm(const TcArgs& a, const uint32_t trow, float* smem_f, const int q, const long boff,
+                                              const int b_tile, const int quad, const int part, const int lane) {
+    constexpr int CW = 256 / PARTS;                        // columns per thread
+    const float* bias_s = smem_f;                          // [256]
+    const float* g_s = smem_f + 256; const float* b_s = smem_f + 512;
+    float* psum = smem_f + 1024;                           // [4 parts][128 rows]
+    float* psq = smem_f + 1536;                            // [4 parts][128 rows]
+    const int c0 = part * CW, r = quad * 32 + lane;
+    const bool rowok = q < a.Q;
+    const float* R1f = reinterpret_cast<const float*>(a.R1);
+    const long e0 = boff + (long)q * 256 + c0;
+    float sum = 0.f;
+#pragma unroll 1
+    for (int cc = 0; cc < CW; cc += 16) {
+        float v[16];
+        float4 rr[4];
+        if (a.R1) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) rr[h] = (rowok && !(a.dbg & 256)) ? *reinterpret_cast<const float4*>(R1f + e0 + cc + h * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        tmem_ld16(trow + (uint32_t)(c0 + cc), v);
+        epi_bias_act(a, v, bias_s + c0 + cc);
+        if (a.R1) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h) { v[h * 4] += rr[h].x; v[h * 4 + 1] += rr[h].y; v[h * 4 + 2] += rr[h].z; v[h * 4 + 3] += rr[h].w; }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) sum += v[i];
+        tmem_st16(trow + (uint32_t)(c0 + cc), v);
+    }
+    psum[part * 128 + r] = sum;
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + quad), "n"(PARTS * 32) : "memory");
+    float tot = 0.f;
+#pragma unroll
+    for (int p = 0; p < PARTS; ++p) tot += psum[p * 128 + r];                  // same order in every thread of the row
+    const float mean = tot * (1.f / 256.f);
+    float sq = 0.f;
+#pragma unroll 1
+    for (int cc = 0; cc < CW; cc += 16) {
+        float v[16];
+        tmem_ld16(trow + (uint32_t)(c0 + cc), v);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { const float d = v[i] - mean; sq += d * d; }
+    }
+    psq[part * 128 + r] = sq;
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + quad), "n"(PARTS * 32) : "memory");
+    float qt = 0.f;
+#pragma unroll
+    for (int p = 0; p < PARTS; ++p) qt += psq[p * 128 + r];
+    const float rstd = rsqrtf(qt * (1.f / 256.f) + 1e-5f);
+    // row -> (utterance, frame): k = 1 layers run flattened over the B * T rows
+    int bq = b_tile, tq = q;
+    if (a.ln_T > 0 && a.B == 1) { bq = q / a.ln_T; tq = q - bq * a.ln_T; }
+    const bool keep = a.ln_lens == nullptr || (rowok && tq < (int)a.ln_lens[bq]);
+    __half* p16 = a.Y16p ? reinterpret_cast<__half*>(a.Y16p) + (((long)bq * 32 + (c0 >> 3)) * a.ln_T + tq) * 8 : nullptr;
+    const long gs16 = (long)a.ln_T * 8;
+#pragma unroll 1
+    for (int cc = 0; cc < CW; cc += 16) {
+        float v[16];
+        tmem_ld16(trow + (uint32_t)(c0 + cc), v);
+        if (!rowok || (a.dbg & 512)) continue;
+        const float4* g4 = reinterpret_cast<const float4*>(g_s + c0 + cc); const float4* b4 = reinterpret_cast<const float4*>(b_s + c0 + cc);
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            const float4 gg = g4[h], bb = b4[h];
+            v[h * 4 + 0] = keep ? (v[h * 4 + 0] - mean) * rstd * gg.x + bb.x : 0.f;
+            v[h * 4 + 1] = keep ? (v[h * 4 + 1] - mean) * rstd * gg.y + bb.y : 0.f;
+            v[h * 4 + 2] = keep ? (v[h * 4 + 2] - mean) * rstd * gg.z + bb.z : 0.f;
+            v[h * 4 + 3] = keep ? (v[h * 4 + 3] - mean) * rstd * gg.w + bb.w : 0.f;
+        }
+        float4* p = reinterpret_cast<float4*>(a.Y + e0 + cc);
+#pragma unroll
+        for (int h = 0; h < 4; ++h) p[h] = make_float4(v[h * 4], v[h * 4 + 1], v[h * 4 + 2], v[h * 4 + 3]);
+        if (p16) {
+            *reinterpret_cast<uint4*>(p16 + (long)(cc >> 3) * gs16) = pack8h(v);
+            *reinterpret_cast<uint4*>(p16 + (long)((cc >> 3) + 1) * gs16) = pack8h(v + 8);
+        }
+    }
+}
+
 template <int NT, bool TMA_IN>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -439,17 +544,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     const int n_stages = (a.n_blobs + a.G - 1) / a.G;
     const int acc_cols = a.msub * NT;                      // TMEM columns of one accumulator set (two sets)
     const bool a_workers = !TMA_IN || a.in_act != ACT_NONE;
+    const bool ln_helpers = NT == 256 && a.ln_g != nullptr && !a_workers && !(a.dbg & 1024);   // idle worker warps join the LayerNorm epilogue
     const int n_issuers = min(a.msub, MMA_WARPS);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_SLOTS; ++i) {
             mbar_init(bars.a_full(i), a_workers ? A_THREADS : 1); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), 1);
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), n_issuers); mbar_init(bars.acc_empty(i), EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), n_issuers); mbar_init(bars.acc_empty(i), ln_helpers ? EPI_WARPS + A_WARPS : EPI_WARPS); }
         for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), n_issuers); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int i = threadIdx.x; i < a.N; i += NTHREADS) bias_s[i] = a.bias ? a.bias[i % a.bias_mod] : 0.f;
+    if (NT == 256 && a.ln_g) for (int i = threadIdx.x; i < 256; i += NTHREADS) { bias_s[256 + i] = a.ln_g[i]; bias_s[512 + i] = a.ln_b[i]; }
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(a.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -469,6 +576,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         if (a.dbg & 2) {
             // what-if: no activation staging
         } else if (TMA_IN) {
+            if (NT == 256 && ln_helpers) {
+                // ===== nothing to stage: second half of the fused-LayerNorm epilogue (column quarters 2 and 3 of every row) =====
+                const int hw = warp - A_WARP0, quad = warp & 3;
+                // two worker warps share each TMEM lane quadrant: the one met first takes quarter 2, the other quarter 3
+                int seen = 0;
+                for (int k = 0; k < hw; ++k) if (((A_WARP0 + k) & 3) == quad) ++seen;
+                const int my_part = 2 + seen;
+                int it = 0;
+                for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+                    const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+                    const int accb = it & 1;
+                    mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1);
+                    tc_fence_after();
+                    const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols);
+                    epi_layernorm<4>(a, trow, bias_s, rt * a.msub * 128 + quad * 32 + lane, (long)b * a.y_bs, b, quad, my_part, lane);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bars.acc_empty(accb));
+                }
+            }
             // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled =====
             if (a.in_act != ACT_NONE) {
                 const int pieces = a.a_tx >> 4;
@@ -689,6 +816,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             TRACE(tr, 3, it, 1);
             if (a.dbg & 4) {
                 // what-if: no epilogue work
+            } else if (NT == 256 && a.ln_g) {
+                const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols);
+                if (ln_helpers) epi_layernorm<4>(a, trow, bias_s, q0 + quad * 32 + lane, boff, b, quad, half, lane);
+                else epi_layernorm<2>(a, trow, bias_s, q0 + quad * 32 + lane, boff, b, quad, half, lane);
             } else if (a.y_planar) {
                 const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(accb * acc_cols);
                 if (a.R1 == nullptr) epi_planar<NT, false, false>(a, tacc, bias_s, n0, q0, boff, quad, half, lane);
@@ -812,10 +943,10 @@ __global__ void k_from_planar(const bf16* __restrict__ x, float* __restrict__ ou
 }
 
 template <int NT, bool TMA_IN>
-void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
+void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s, int n_sm) {
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
-    CUDA_OK(launch_pdl(k_conv_tc<NT, TMA_IN>, grid, NTHREADS, smem, s, a));
+    CUDA_OK(launch_pdl(k_conv_tc<NT, TMA_IN>, grid, NTHREADS, smem, s, a, a.total_tiles < n_sm));
 }
 
 }  // namespace
@@ -846,12 +977,15 @@ void launch_from_planar(masg_ctx* c, cudaStream_t s, const bf16* x, float* out, 
 }
 
 void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
+    const bool wide = (mode & TC_MODE_WIDE) != 0;          // one 256-column tile per row block: the layers with a fused LayerNorm
+    mode &= 0xff;
     const bool split = mode == 1;
     MASG_CHECK(d.w32 != nullptr, "tc_prepare_weights: fp32 GEMM weights missing");
     int NT = 0;
     const int cands[4] = {128, 80, 64, 32};
     for (int i = 0; i < 4 && !NT; ++i) if (d.N % cands[i] == 0) NT = cands[i];
     int KW = (d.Cin % 64 == 0) ? 64 : (d.Cin % 32 == 0 ? 32 : 16);
+    if (wide) { MASG_CHECK(d.N == 256 && d.Cin % 32 == 0, "wide tiles need N == 256"); NT = 256; KW = 32; }   // 16 KB blobs
     while (split && NT * KW * 4 > W_STAGE_BYTES && KW > 16) KW /= 2;
     MASG_CHECK(d.Cin % KW == 0, "conv_tc: Cin=%d must be a multiple of 16", d.Cin);
     size_t n = (size_t)d.taps * d.Cin * d.N;
@@ -904,7 +1038,7 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     }
     const int ntiles_n = d.N / NT;
     while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < c->n_sm) msub /= 2;
-    int KC = 0;
+    int KC = 0, grid_cap = c->n_sm;
     if (tma_in) {
         // one [KC/8][Rb][8] block per tile (its msub*128 rows + the halo); sub-tile ms starts 128 rows further down; every
         // 8-channel group is one contiguous run in HBM, moved by a single 1-D bulk copy
@@ -975,8 +1109,14 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
         const size_t wbytes = (size_t)a.n_blobs * a.blob_bytes;
         const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + wbytes;
         a.w_resident = 0;
-        if (res && tma_in && !d.split && ntiles_n == 1 && wbytes <= 100 * 1024 && need <= (size_t)MAX_SMEM) {
+        // several N tiles (decoder QKV: 6, fc: 2): the grid is rounded down to a multiple of the N-tile count, so that
+        // tile % n_ntiles is the same for every tile a CTA walks and its one N tile's weights can stay resident too
+        const int grid_r = (c->n_sm / ntiles_n) * ntiles_n;
+        const long tiles = (long)io.B * ((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n;
+        const bool multi_ok = ntiles_n > 1 && ntiles_n <= 8 && grid_r * 10 >= c->n_sm * 9 && tiles >= 2L * grid_r;
+        if (res && tma_in && !d.split && (ntiles_n == 1 || multi_ok) && wbytes <= 100 * 1024 && need <= (size_t)MAX_SMEM) {
             a.w_resident = 1; a.G = a.n_blobs; a.w_stages = 1;
+            if (ntiles_n > 1) grid_cap = grid_r;
         }
     }
     a.stage_bytes = a.G * a.blob_bytes;
@@ -991,6 +1131,13 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale; a.post_slope = io.post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
     { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
+    a.ln_g = io.ln_g; a.ln_b = io.ln_b; a.ln_lens = io.ln_lens; a.ln_T = io.ln_T; a.Y16p = io.Y16p;
+    if (io.ln_g) {
+        MASG_CHECK(NT == 256 && d.N == 256 && io.ln_b, "conv_tc: the fused LayerNorm needs a 256-column tile (weights prepared wide)");
+        MASG_CHECK(io.Y && !io.Y16 && !io.y_planar && !io.R2 && !io.r_bf16 && io.out_scale == 1.f && io.post_slope == 1.f && a.orow == 256 && a.ooff == 0,
+                   "conv_tc: the fused LayerNorm writes fp32 row-major rows of 256 and takes one fp32 residual");
+        MASG_CHECK((!io.ln_lens && !io.Y16p) || io.ln_T > 0, "conv_tc: ln_T is required with ln_lens / Y16p");
+    }
     a.y_planar = io.y_planar;
     if (io.y_planar) {
         MASG_CHECK(io.Y16 != nullptr && io.Y == nullptr && io.y_T > 0, "conv_tc: planar output is bf16 only and needs y_T");
@@ -1009,11 +1156,11 @@ void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO
     const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)a.w_stages * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
     MASG_CHECK(!tma_in || ((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
-    dim3 grid(std::min(a.total_tiles, c->n_sm), 1, 1);            // persistent: one CTA per SM walks the tile list
+    dim3 grid(std::min(a.total_tiles, grid_cap), 1, 1);            // persistent: one CTA per SM walks the tile list
 #define MASG_TC_CASE(NTV)                                                                       \
-    case NTV: if (tma_in) launch_inst<NTV, true>(a, grid, smem, s); else launch_inst<NTV, false>(a, grid, smem, s); break;
+    case NTV: if (tma_in) launch_inst<NTV, true>(a, grid, smem, s, c->n_sm); else launch_inst<NTV, false>(a, grid, smem, s, c->n_sm); break;
     switch (NT) {
-        MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128)
+        MASG_TC_CASE(32) MASG_TC_CASE(64) MASG_TC_CASE(80) MASG_TC_CASE(128) MASG_TC_CASE(256)
         default: MASG_CHECK(false, "conv_tc: unsupported N tile %d", NT);
     }
 #undef MASG_TC_CASE

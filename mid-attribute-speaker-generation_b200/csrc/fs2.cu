@@ -62,8 +62,17 @@ ConvDesc make_conv(masg_ctx* c, cudaStream_t s, const float* w, const float* bia
     return d;
 }
 
+// MASG_LN_FUSE (default 1): fc / w_2 / the predictor convs are tiled as one 256-column tile per row block and their epilogue is
+// the LayerNorm that follows them (conv_tc.cu epi_layernorm); 0 = separate k_layernorm256 launches (the round-1 graph)
+static bool ln_fuse_on() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("MASG_LN_FUSE"); on = e ? atoi(e) : 1; }
+    return on != 0;
+}
+
 void fs2_commit(masg_ctx* c, cudaStream_t s) {
     auto& m = c->fs2_t;
+    const int wide = ln_fuse_on() ? TC_MODE_WIDE : 0;
     // Operand mode of the dense layers (MASG_PREC_BF16): the encoder and the variance predictors decide integers (durations,
     // pitch / energy buckets) and run split-bf16 (hi + lo, 3 MMAs per K step, ~fp32).  Everything after the length regulator
     // only has to keep the mel within 1e-2: single-pass fp16 operands (11-bit mantissa, fp32 accumulation; measured 4e-3 where
@@ -104,14 +113,14 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
                 if (c->precision == MASG_PREC_BF16) tc_prepare_weights(c, s, d, part == 0 ? 1 : dec_mode);
                 L.qkv = d;
             }
-            L.fc = make_conv(c, s, T_(m, p + "slf_attn.fc.weight", {256, 256}).ptr, T_(m, p + "slf_attn.fc.bias", {256}).ptr, 256, 256, 1, 0, 1, nullptr, nullptr, part == 0 ? 1 : dec_mode);
+            L.fc = make_conv(c, s, T_(m, p + "slf_attn.fc.weight", {256, 256}).ptr, T_(m, p + "slf_attn.fc.bias", {256}).ptr, 256, 256, 1, 0, 1, nullptr, nullptr, (part == 0 ? 1 : dec_mode) | wide);
             L.ln1_g = T_(m, p + "slf_attn.layer_norm.weight", {256}).ptr; L.ln1_b = T_(m, p + "slf_attn.layer_norm.bias", {256}).ptr;
             const TensorRef& w1 = T_(m, p + "pos_ffn.w_1.weight", {1024, 256, -1});
             int k1 = (int)w1.shape[2];
             L.w1 = make_conv(c, s, w1.ptr, T_(m, p + "pos_ffn.w_1.bias", {1024}).ptr, 1024, 256, k1, (k1 - 1) / 2, 1, nullptr, nullptr, part == 0 ? 1 : dec_mode);
             const TensorRef& w2 = T_(m, p + "pos_ffn.w_2.weight", {256, 1024, -1});
             int k2 = (int)w2.shape[2];
-            L.w2 = make_conv(c, s, w2.ptr, T_(m, p + "pos_ffn.w_2.bias", {256}).ptr, 256, 1024, k2, (k2 - 1) / 2, 1, nullptr, nullptr, part == 0 ? 1 : dec_mode);
+            L.w2 = make_conv(c, s, w2.ptr, T_(m, p + "pos_ffn.w_2.bias", {256}).ptr, 256, 1024, k2, (k2 - 1) / 2, 1, nullptr, nullptr, (part == 0 ? 1 : dec_mode) | (k2 == 1 ? wide : 0));
             L.ln2_g = T_(m, p + "pos_ffn.layer_norm.weight", {256}).ptr; L.ln2_b = T_(m, p + "pos_ffn.layer_norm.bias", {256}).ptr;
             vec.push_back(L);
         }
@@ -123,9 +132,9 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
         std::string p = std::string("variance_adaptor.") + pnames[i] + "_predictor.";
         Predictor& P = c->pred[i];
         const TensorRef& w1 = T_(m, p + "conv_layer.conv1d_1.conv.weight", {256, 256, 3});
-        P.c1 = make_conv(c, s, w1.ptr, T_(m, p + "conv_layer.conv1d_1.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, true);
+        P.c1 = make_conv(c, s, w1.ptr, T_(m, p + "conv_layer.conv1d_1.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1 | wide);
         P.c2 = make_conv(c, s, T_(m, p + "conv_layer.conv1d_2.conv.weight", {256, 256, 3}).ptr,
-                         T_(m, p + "conv_layer.conv1d_2.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, true);   // padding=1 (modules.py:229-231)
+                         T_(m, p + "conv_layer.conv1d_2.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1 | wide);   // padding=1 (modules.py:229-231)
         P.ln1_g = T_(m, p + "conv_layer.layer_norm_1.weight", {256}).ptr; P.ln1_b = T_(m, p + "conv_layer.layer_norm_1.bias", {256}).ptr;
         P.ln2_g = T_(m, p + "conv_layer.layer_norm_2.weight", {256}).ptr; P.ln2_b = T_(m, p + "conv_layer.layer_norm_2.bias", {256}).ptr;
         P.lin_w = T_(m, p + "linear_layer.weight", {1, 256}).ptr;
@@ -170,10 +179,19 @@ static const float* pos_table(masg_ctx* c, cudaStream_t s, bool decoder, int n) 
     return c->pos_long;
 }
 
+// LayerNorm fused into the producing conv's epilogue (conv_tc.cu): gamma / beta, optional pad-row zeroing, optional planar copy
+struct LnSpec { const float* g = nullptr; const float* b = nullptr; const int64_t* lens = nullptr; bf16* y16p = nullptr; };
+static bool ln_fusable(const masg_ctx* c, const ConvDesc& d) { return c->precision == MASG_PREC_BF16 && d.NT == 256; }
+static void ln_apply(ConvIO& io, const LnSpec* ln, int T) {
+    if (!ln) return;
+    io.ln_g = ln->g; io.ln_b = ln->b; io.ln_lens = ln->lens; io.Y16p = ln->y16p; io.ln_T = T;
+}
+
 // ---- fp32 building blocks ---------------------------------------------------------------------
 static void conv32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const float* X, int x_ld, int B, int T, float* Y,
-                   int out_act = ACT_NONE, const float* R1 = nullptr) {
+                   int out_act = ACT_NONE, const float* R1 = nullptr, const LnSpec* ln = nullptr) {
     ConvIO io;
+    ln_apply(io, ln, T);
     io.X = X; io.x_ld = x_ld; io.x_bs = (long)T * x_ld; io.Tin = T;
     io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
     if (d.taps == 1 && c->precision == MASG_PREC_BF16) {
@@ -195,8 +213,9 @@ static void conv_to_planar16(masg_ctx* c, cudaStream_t s, const ConvDesc& d, con
     launch_conv(c, s, d, io);
 }
 static void conv_from_planar16(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const bf16* X16, int B, int T, float* Y,
-                               int out_act = ACT_NONE, const float* R1 = nullptr) {
+                               int out_act = ACT_NONE, const float* R1 = nullptr, const LnSpec* ln = nullptr) {
     ConvIO io;
+    ln_apply(io, ln, T);
     io.X = X16; io.x_ld = d.Cin; io.x_bs = (long)T * d.Cin; io.Tin = T; io.x_planar = 1; io.x_bf16 = 1;
     io.Y = Y; io.y_bs = (long)T * d.N; io.y_limit = (long)T * d.N; io.B = B; io.Q = T; io.out_act = out_act; io.R1 = R1;
     launch_conv(c, s, d, io);
@@ -226,34 +245,42 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     size_t rows = (size_t)B * S, mk = ar.mark();
     float* qkv = ar.get<float>(rows * 768);
     float* att = ar.get<float>(rows * 256);
-    float* y = ar.get<float>(rows * 256);
+    const bool chain = f16_chain(c, L.w1, L.w2);
+    bf16* xp1 = (chain && ln_planar(1)) ? ar.get<bf16>(rows * 256) : nullptr;   // LN output as w_1's operand
+    // fc (+ bias + residual x) -> LayerNorm -> masked_fill (SubLayers.py:54-55, Layers.py:25): one kernel when fc is tiled wide —
+    // the epilogue reads the residual row of x and writes the normalised row back in place (same thread, same elements)
+    const bool fuse1 = ln_fusable(c, L.fc), fuse2 = ln_fusable(c, L.w2);
+    const LnSpec ln1{L.ln1_g, L.ln1_b, lens, xp1}, ln2{L.ln2_g, L.ln2_b, lens, xp_out};
+    float* y = fuse1 ? nullptr : ar.get<float>(rows * 256);
     if (attn_planar(c, L)) {
         // fp16 layers: q | k | v and the attention output stay planar fp16 (operand layout end to end, attn_f16p.cu)
         if (xp_in) conv_to_planar16(c, s, L.qkv, xp_in, true, 256, B, S, (bf16*)qkv, ACT_NONE);
         else conv_to_planar16(c, s, L.qkv, x, false, 256, B, S, (bf16*)qkv, ACT_NONE);
         launch_attention_f16p(c, s, qkv, lens, B, S, att);
-        conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, y, ACT_NONE, x); // fc(out) + residual
+        if (fuse1) conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, x, ACT_NONE, x, &ln1);
+        else conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, y, ACT_NONE, x); // fc(out) + residual
     } else {
         if (xp_in) conv_from_planar16(c, s, L.qkv, xp_in, B, S, qkv);
         else conv32(c, s, L.qkv, x, 256, B, S, qkv);
         if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
         else launch_attention_f32(c, s, qkv, lens, B, S, att);
-        conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                     // fc(out) + residual
+        if (fuse1) conv32(c, s, L.fc, att, 256, B, S, x, ACT_NONE, x, &ln1);
+        else conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                     // fc(out) + residual
     }
-    const bool chain = f16_chain(c, L.w1, L.w2);
-    bf16* xp1 = (chain && ln_planar(1)) ? ar.get<bf16>(rows * 256) : nullptr;   // LN output as w_1's operand
-    launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x, xp1);   // LN + masked_fill (Layers.py:25)
+    if (!fuse1) launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x, xp1);   // LN + masked_fill (Layers.py:25)
     float* h = ar.get<float>(rows * 1024);
-    float* y2 = ar.get<float>(rows * 256);
+    float* y2 = fuse2 ? nullptr : ar.get<float>(rows * 256);
     if (chain) {                                                                // h only feeds w_2: planar fp16, never fp32
         if (xp1) conv_to_planar16(c, s, L.w1, xp1, true, 256, B, S, (bf16*)h, ACT_RELU);
         else conv_to_planar16(c, s, L.w1, x, false, 256, B, S, (bf16*)h, ACT_RELU);
-        conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
+        if (fuse2) conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, x, ACT_NONE, x, &ln2);
+        else conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
     } else {
         conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
-        conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
+        if (fuse2) conv32(c, s, L.w2, h, 1024, B, S, x, ACT_NONE, x, &ln2);
+        else conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
     }
-    launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x, xp_out);   // LN + masked_fill (Layers.py:28)
+    if (!fuse2) launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x, xp_out);   // LN + masked_fill (Layers.py:28)
     ar.restore(mk);
 }
 
@@ -261,11 +288,13 @@ static void predictor_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const Predicto
                           int B, int L, float scale, float* out) {
     size_t rows = (size_t)B * L, mk = ar.mark();
     float* a = ar.get<float>(rows * 256); float* b = ar.get<float>(rows * 256);
-    conv32(c, s, P.c1, x, 256, B, L, a, ACT_RELU);
-    launch_layernorm(c, s, a, nullptr, P.ln1_g, P.ln1_b, nullptr, B, L, b);
-    conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU);
-    launch_layernorm(c, s, a, nullptr, P.ln2_g, P.ln2_b, nullptr, B, L, b);
-    launch_rowdot_mask(c, s, b, P.lin_w, P.lin_b, lens, B, L, scale, out);
+    // Conv k3 -> ReLU -> LayerNorm, twice (modules.py:209-240); the LayerNorm rides in the conv's epilogue when tiled wide
+    const LnSpec l1{P.ln1_g, P.ln1_b, nullptr, nullptr}, l2{P.ln2_g, P.ln2_b, nullptr, nullptr};
+    if (ln_fusable(c, P.c1)) conv32(c, s, P.c1, x, 256, B, L, b, ACT_RELU, nullptr, &l1);
+    else { conv32(c, s, P.c1, x, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln1_g, P.ln1_b, nullptr, B, L, b); }
+    if (ln_fusable(c, P.c2)) conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU, nullptr, &l2);
+    else { conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln2_g, P.ln2_b, nullptr, B, L, b); std::swap(a, b); }
+    launch_rowdot_mask(c, s, a, P.lin_w, P.lin_b, lens, B, L, scale, out);
     ar.restore(mk);
 }
 

@@ -384,7 +384,7 @@ template <int C, int K, int XS, int NH>
 void launch_rp(const RpArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_respair_tc<C, K, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, RP_MAX_SMEM)); attr = true; }
-    CUDA_OK(launch_pdl(k_respair_tc<C, K, XS, NH>, grid, RP_THREADS, smem, s, a));
+    CUDA_OK(launch_pdl(k_respair_tc<C, K, XS, NH>, grid, RP_THREADS, smem, s, a, a.total_tiles <= (int)grid.x));
 }
 
 size_t rp_smem(int C, int K, int Rx, int xs, int nh) {

@@ -5,6 +5,8 @@
 // bf16 pre-tiled weight copy of a ConvDesc (called at commit in MASG_PREC_BF16 mode): fills d.w16/NT/KW.
 // split: carry the weights as bf16 hi + lo and issue 3 MMAs per K step (FastSpeech2 layers; ~fp32 accuracy)
 // mode 2: fp16 operands, one MMA per K step (11-bit mantissa; the FastSpeech2 decoder side, after the duration / bucket decisions)
+// mode | TC_MODE_WIDE: N == 256 handled as ONE 256-column tile (the layers whose epilogue is a fused LayerNorm over the row)
+constexpr int TC_MODE_WIDE = 0x100;
 void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode);
 // same row-GEMM contract as launch_conv_f32 (see ConvDesc / ConvIO in common.cuh)
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);

@@ -83,6 +83,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+// the reverse: 16 fp32 columns of this thread's TMEM lane are overwritten (the fused LayerNorm epilogue parks
+// acc + bias + residual there between its passes); complete before the thread's next tcgen05.ld of the same columns
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n\t"
+        "tcgen05.wait::st.sync.aligned;"
+        :: "r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+           "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+           "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+           "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+        : "memory");
+}
 // two such loads in flight, one wait (two accumulator sub-tiles of the same columns)
 __device__ __forceinline__ void tmem_ld16x2(uint32_t taddr0, uint32_t taddr1, float* v0, float* v1) {
     uint32_t r[32];
@@ -151,11 +163,15 @@ __device__ __forceinline__ void mul_f32x2(float& a0, float& a1, const float b0, 
 }
 
 
-// launch with the programmatic-stream-serialization attribute (MASG_PDL=0 turns it off); the kernel must call pdl_wait()
+// launch with the programmatic-stream-serialization attribute; the kernel must call pdl_wait().  MASG_PDL = 1 / 0 forces it on /
+// off; by default it is used for launches that do not fill the GPU (`sub_wave`: fewer tiles than SMs — the small-batch latency
+// path, where the next kernel's prologue (barrier init, TMEM allocation, bias and weight loads) overlaps this one's tail:
+// C2 p50 2.25 -> 2.13 ms) and not for full-size launches (the C3 step is power-capped: gaps are paid back as clock, A/B neutral)
 template <typename Kern, typename Args>
-inline cudaError_t launch_pdl(Kern kern, dim3 grid, int threads, size_t smem, cudaStream_t s, const Args& a) {
-    static int on = -1;
-    if (on < 0) { const char* e = getenv("MASG_PDL"); on = e ? atoi(e) : 0; }
+inline cudaError_t launch_pdl(Kern kern, dim3 grid, int threads, size_t smem, cudaStream_t s, const Args& a, bool sub_wave = false) {
+    static int env = -2;
+    if (env == -2) { const char* e = getenv("MASG_PDL"); env = e ? atoi(e) : -1; }
+    const int on = env >= 0 ? env : (sub_wave ? 1 : 0);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(threads, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = s;
     cudaLaunchAttribute at[1];
