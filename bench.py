@@ -531,7 +531,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "dtype": "bf16" if args.precision.startswith("bf16") else "f32", "data": "synthetic",
         "config": c3_config(world),
         "precision": args.precision + (" (HiFi-GAN bf16; FastSpeech2 encoder + variance predictors split-bf16 hi/lo, 3 MMAs per K step; decoder, mel_linear, PostNet fp16 operands; fp32 accumulation everywhere)" if args.precision == "bf16" else ""),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
@@ -705,7 +705,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32", "bf16x3"],
+                    help="bf16 = the benchmarked mode; fp32 = CUDA-core strict parity; bf16x3 = 1e-4 mel parity on the tensor cores (split-bf16 through all of FastSpeech2)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline and gpu_eager_baseline legs")
     ap.add_argument("--ref-sample", type=int, default=N_REF_SAMPLE, help="reference arm: utterances of the C3 batch per step")
     ap.add_argument("--latency-reps", type=int, default=5, help="reference arm: timed runs of the C1 / C2 CPU latency")

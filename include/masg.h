@@ -31,8 +31,10 @@ extern "C" {
 
 typedef struct masg_ctx masg_ctx;
 
-enum { MASG_PREC_BF16 = 0,   /* bf16 operands on tcgen05 tensor cores, fp32 accumulate (mel max-abs <= 1e-2) */
-       MASG_PREC_FP32 = 1 }; /* fp32 CUDA-core path (mel max-abs <= 1e-4); the strict-parity mode       */
+enum { MASG_PREC_BF16 = 0,   /* bf16 / fp16 operands on tcgen05 tensor cores, fp32 accumulate (mel max-abs <= 1e-2): the benchmarked mode */
+       MASG_PREC_FP32 = 1,   /* fp32 CUDA-core path (mel max-abs <= 1e-4); the strict-parity mode                                          */
+       MASG_PREC_BF16X3 = 2 }; /* the 1e-4 mode ON the tensor cores: every FastSpeech2 contraction in split-bf16 (x = hi + lo on both
+                                  operands, three MMAs per K step, ~16 mantissa bits, fp32 accumulate); HiFi-GAN as in MASG_PREC_BF16 */
 
 /* library / build identification (no reference counterpart) */
 const char* masg_version(void);

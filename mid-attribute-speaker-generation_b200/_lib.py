@@ -9,8 +9,8 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmasg.so")
 
-PREC_BF16, PREC_FP32 = 0, 1
-_PREC_NAMES = {"bf16": PREC_BF16, "fp32": PREC_FP32, PREC_BF16: PREC_BF16, PREC_FP32: PREC_FP32}
+PREC_BF16, PREC_FP32, PREC_BF16X3 = 0, 1, 2
+_PREC_NAMES = {"bf16": PREC_BF16, "fp32": PREC_FP32, "bf16x3": PREC_BF16X3, PREC_BF16: PREC_BF16, PREC_FP32: PREC_FP32, PREC_BF16X3: PREC_BF16X3}
 
 c_void_p, c_int, c_float, c_i64, c_u64, c_char_p = (ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_int64,
                                                      ctypes.c_uint64, ctypes.c_char_p)

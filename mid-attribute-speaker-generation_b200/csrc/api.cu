@@ -28,7 +28,7 @@ const char* masg_version(void) { return "masg-b200 0.1 (sm_100a)"; }
 int masg_ctx_create(int device, int precision, masg_ctx** out) {
     try {
         MASG_CHECK(out != nullptr, "null out pointer");
-        MASG_CHECK(precision == MASG_PREC_BF16 || precision == MASG_PREC_FP32, "unknown precision %d", precision);
+        MASG_CHECK(precision == MASG_PREC_BF16 || precision == MASG_PREC_FP32 || precision == MASG_PREC_BF16X3, "unknown precision %d", precision);
         int n = 0;
         cudaError_t e = cudaGetDeviceCount(&n);
         MASG_CHECK(e == cudaSuccess && n > 0, "no CUDA device available (%s): this library has no CPU fallback", cudaGetErrorString(e));
@@ -38,7 +38,8 @@ int masg_ctx_create(int device, int precision, masg_ctx** out) {
         MASG_CHECK(prop.major == 10, "device %d is sm_%d%d; libmasg is built for sm_100a (B200) only", device, prop.major, prop.minor);
         CUDA_OK(cudaSetDevice(device));
         masg_ctx* c = new masg_ctx();
-        c->device = device; c->precision = precision;
+        // MASG_PREC_BF16X3 is the tensor-core path with every FastSpeech2 contraction in split-bf16: internally the bf16 graph + a flag
+        c->device = device; c->precision = precision == MASG_PREC_BF16X3 ? MASG_PREC_BF16 : precision; c->x3 = precision == MASG_PREC_BF16X3;
         c->n_sm = prop.multiProcessorCount;
         *out = c;
         return 0;

@@ -62,10 +62,11 @@ struct ConvWeights {                  // owned storage for a ConvDesc
 
 struct FFTLayer {
     ConvDesc qkv, fc, w1, w2;
+    ConvDesc fc_n, w2_n;              // the same layers tiled 128 columns wide (small batches: more CTAs, separate LayerNorm)
     const float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
 };
 struct Predictor {
-    ConvDesc c1, c2;
+    ConvDesc c1, c2, c1_n, c2_n;
     const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *lin_w; float lin_b;
 };
 
@@ -81,6 +82,7 @@ struct GraphEntry {
 
 struct masg_ctx {
     int device = 0, precision = 0, n_sm = 148;
+    bool x3 = false;                  // MASG_PREC_BF16X3: split-bf16 (3 MMAs per K step) through the decoder / mel_linear / PostNet too
     std::map<std::vector<long>, GraphEntry> graphs;   // key: (phase, B, L, T, packed)
     cudaStream_t cap_stream = nullptr;                // graphs are recorded here (the caller's stream may be the legacy stream)
     int64_t weights_gen = 0;                          // bumped by every commit: captured graphs bake weight pointers

@@ -70,6 +70,12 @@ static bool ln_fuse_on() {
     return on != 0;
 }
 
+static int ln_fuse_min_rows() {                             // MASG_LN_FUSE_ROWS: batches with fewer rows use the 128-column tiling
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("MASG_LN_FUSE_ROWS"); v = e ? atoi(e) : 4096; }
+    return v;
+}
+
 void fs2_commit(masg_ctx* c, cudaStream_t s) {
     auto& m = c->fs2_t;
     const int wide = ln_fuse_on() ? TC_MODE_WIDE : 0;
@@ -78,7 +84,7 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
     // only has to keep the mel within 1e-2: single-pass fp16 operands (11-bit mantissa, fp32 accumulation; measured 4e-3 where
     // plain bf16 gives 3e-2).  MASG_DEC_MODE = 1 (split) / 0 (plain bf16) / 2 (fp16, default) for experiments.
     const char* ds_env = getenv("MASG_DEC_MODE");
-    const int dec_mode = ds_env ? atoi(ds_env) : 2;
+    const int dec_mode = ds_env ? atoi(ds_env) : (c->x3 ? 1 : 2);
     c->fs2_ready = false;
     // the repacked buffers of the previous commit are dead once the stream has drained (re-commit after load_state_dict / .to())
     CUDA_OK(cudaStreamSynchronize(s));
@@ -114,6 +120,7 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
                 L.qkv = d;
             }
             L.fc = make_conv(c, s, T_(m, p + "slf_attn.fc.weight", {256, 256}).ptr, T_(m, p + "slf_attn.fc.bias", {256}).ptr, 256, 256, 1, 0, 1, nullptr, nullptr, (part == 0 ? 1 : dec_mode) | wide);
+            L.fc_n = wide ? make_conv(c, s, T_(m, p + "slf_attn.fc.weight", {256, 256}).ptr, T_(m, p + "slf_attn.fc.bias", {256}).ptr, 256, 256, 1, 0, 1, nullptr, nullptr, part == 0 ? 1 : dec_mode) : L.fc;
             L.ln1_g = T_(m, p + "slf_attn.layer_norm.weight", {256}).ptr; L.ln1_b = T_(m, p + "slf_attn.layer_norm.bias", {256}).ptr;
             const TensorRef& w1 = T_(m, p + "pos_ffn.w_1.weight", {1024, 256, -1});
             int k1 = (int)w1.shape[2];
@@ -121,6 +128,7 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
             const TensorRef& w2 = T_(m, p + "pos_ffn.w_2.weight", {256, 1024, -1});
             int k2 = (int)w2.shape[2];
             L.w2 = make_conv(c, s, w2.ptr, T_(m, p + "pos_ffn.w_2.bias", {256}).ptr, 256, 1024, k2, (k2 - 1) / 2, 1, nullptr, nullptr, (part == 0 ? 1 : dec_mode) | (k2 == 1 ? wide : 0));
+            L.w2_n = (wide && k2 == 1) ? make_conv(c, s, w2.ptr, T_(m, p + "pos_ffn.w_2.bias", {256}).ptr, 256, 1024, k2, (k2 - 1) / 2, 1, nullptr, nullptr, part == 0 ? 1 : dec_mode) : L.w2;
             L.ln2_g = T_(m, p + "pos_ffn.layer_norm.weight", {256}).ptr; L.ln2_b = T_(m, p + "pos_ffn.layer_norm.bias", {256}).ptr;
             vec.push_back(L);
         }
@@ -133,8 +141,11 @@ void fs2_commit(masg_ctx* c, cudaStream_t s) {
         Predictor& P = c->pred[i];
         const TensorRef& w1 = T_(m, p + "conv_layer.conv1d_1.conv.weight", {256, 256, 3});
         P.c1 = make_conv(c, s, w1.ptr, T_(m, p + "conv_layer.conv1d_1.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1 | wide);
+        P.c1_n = wide ? make_conv(c, s, w1.ptr, T_(m, p + "conv_layer.conv1d_1.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1) : P.c1;
         P.c2 = make_conv(c, s, T_(m, p + "conv_layer.conv1d_2.conv.weight", {256, 256, 3}).ptr,
                          T_(m, p + "conv_layer.conv1d_2.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1 | wide);   // padding=1 (modules.py:229-231)
+        P.c2_n = wide ? make_conv(c, s, T_(m, p + "conv_layer.conv1d_2.conv.weight", {256, 256, 3}).ptr,
+                                  T_(m, p + "conv_layer.conv1d_2.conv.bias", {256}).ptr, 256, 256, 3, 1, 1, nullptr, nullptr, 1) : P.c2;
         P.ln1_g = T_(m, p + "conv_layer.layer_norm_1.weight", {256}).ptr; P.ln1_b = T_(m, p + "conv_layer.layer_norm_1.bias", {256}).ptr;
         P.ln2_g = T_(m, p + "conv_layer.layer_norm_2.weight", {256}).ptr; P.ln2_b = T_(m, p + "conv_layer.layer_norm_2.bias", {256}).ptr;
         P.lin_w = T_(m, p + "linear_layer.weight", {1, 256}).ptr;
@@ -249,7 +260,10 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     bf16* xp1 = (chain && ln_planar(1)) ? ar.get<bf16>(rows * 256) : nullptr;   // LN output as w_1's operand
     // fc (+ bias + residual x) -> LayerNorm -> masked_fill (SubLayers.py:54-55, Layers.py:25): one kernel when fc is tiled wide —
     // the epilogue reads the residual row of x and writes the normalised row back in place (same thread, same elements)
-    const bool fuse1 = ln_fusable(c, L.fc), fuse2 = ln_fusable(c, L.w2);
+    // small batches (the latency path) keep the 128-column tiling: twice the CTAs per layer, LayerNorm as its own launch
+    const bool big = rows >= (size_t)ln_fuse_min_rows();
+    const ConvDesc& fc = big ? L.fc : L.fc_n; const ConvDesc& w2 = big ? L.w2 : L.w2_n;
+    const bool fuse1 = ln_fusable(c, fc), fuse2 = ln_fusable(c, w2);
     const LnSpec ln1{L.ln1_g, L.ln1_b, lens, xp1}, ln2{L.ln2_g, L.ln2_b, lens, xp_out};
     float* y = fuse1 ? nullptr : ar.get<float>(rows * 256);
     if (attn_planar(c, L)) {
@@ -257,15 +271,15 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
         if (xp_in) conv_to_planar16(c, s, L.qkv, xp_in, true, 256, B, S, (bf16*)qkv, ACT_NONE);
         else conv_to_planar16(c, s, L.qkv, x, false, 256, B, S, (bf16*)qkv, ACT_NONE);
         launch_attention_f16p(c, s, qkv, lens, B, S, att);
-        if (fuse1) conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, x, ACT_NONE, x, &ln1);
-        else conv_from_planar16(c, s, L.fc, (const bf16*)att, B, S, y, ACT_NONE, x); // fc(out) + residual
+        if (fuse1) conv_from_planar16(c, s, fc, (const bf16*)att, B, S, x, ACT_NONE, x, &ln1);
+        else conv_from_planar16(c, s, fc, (const bf16*)att, B, S, y, ACT_NONE, x); // fc(out) + residual
     } else {
         if (xp_in) conv_from_planar16(c, s, L.qkv, xp_in, B, S, qkv);
         else conv32(c, s, L.qkv, x, 256, B, S, qkv);
         if (c->precision == MASG_PREC_BF16) launch_attention_tc(c, s, qkv, lens, B, S, att, L.qkv.f16);
         else launch_attention_f32(c, s, qkv, lens, B, S, att);
-        if (fuse1) conv32(c, s, L.fc, att, 256, B, S, x, ACT_NONE, x, &ln1);
-        else conv32(c, s, L.fc, att, 256, B, S, y, ACT_NONE, x);                     // fc(out) + residual
+        if (fuse1) conv32(c, s, fc, att, 256, B, S, x, ACT_NONE, x, &ln1);
+        else conv32(c, s, fc, att, 256, B, S, y, ACT_NONE, x);                       // fc(out) + residual
     }
     if (!fuse1) launch_layernorm(c, s, y, nullptr, L.ln1_g, L.ln1_b, lens, B, S, x, xp1);   // LN + masked_fill (Layers.py:25)
     float* h = ar.get<float>(rows * 1024);
@@ -273,12 +287,12 @@ static void fft_block_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const FFTLayer
     if (chain) {                                                                // h only feeds w_2: planar fp16, never fp32
         if (xp1) conv_to_planar16(c, s, L.w1, xp1, true, 256, B, S, (bf16*)h, ACT_RELU);
         else conv_to_planar16(c, s, L.w1, x, false, 256, B, S, (bf16*)h, ACT_RELU);
-        if (fuse2) conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, x, ACT_NONE, x, &ln2);
-        else conv_from_planar16(c, s, L.w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
+        if (fuse2) conv_from_planar16(c, s, w2, (const bf16*)h, B, S, x, ACT_NONE, x, &ln2);
+        else conv_from_planar16(c, s, w2, (const bf16*)h, B, S, y2, ACT_NONE, x);
     } else {
         conv32(c, s, L.w1, x, 256, B, S, h, ACT_RELU);
-        if (fuse2) conv32(c, s, L.w2, h, 1024, B, S, x, ACT_NONE, x, &ln2);
-        else conv32(c, s, L.w2, h, 1024, B, S, y2, ACT_NONE, x);
+        if (fuse2) conv32(c, s, w2, h, 1024, B, S, x, ACT_NONE, x, &ln2);
+        else conv32(c, s, w2, h, 1024, B, S, y2, ACT_NONE, x);
     }
     if (!fuse2) launch_layernorm(c, s, y2, nullptr, L.ln2_g, L.ln2_b, lens, B, S, x, xp_out);   // LN + masked_fill (Layers.py:28)
     ar.restore(mk);
@@ -290,10 +304,12 @@ static void predictor_f32(masg_ctx* c, cudaStream_t s, Arena& ar, const Predicto
     float* a = ar.get<float>(rows * 256); float* b = ar.get<float>(rows * 256);
     // Conv k3 -> ReLU -> LayerNorm, twice (modules.py:209-240); the LayerNorm rides in the conv's epilogue when tiled wide
     const LnSpec l1{P.ln1_g, P.ln1_b, nullptr, nullptr}, l2{P.ln2_g, P.ln2_b, nullptr, nullptr};
-    if (ln_fusable(c, P.c1)) conv32(c, s, P.c1, x, 256, B, L, b, ACT_RELU, nullptr, &l1);
-    else { conv32(c, s, P.c1, x, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln1_g, P.ln1_b, nullptr, B, L, b); }
-    if (ln_fusable(c, P.c2)) conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU, nullptr, &l2);
-    else { conv32(c, s, P.c2, b, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln2_g, P.ln2_b, nullptr, B, L, b); std::swap(a, b); }
+    const bool big = rows >= (size_t)ln_fuse_min_rows();
+    const ConvDesc& c1 = big ? P.c1 : P.c1_n; const ConvDesc& c2 = big ? P.c2 : P.c2_n;
+    if (ln_fusable(c, c1)) conv32(c, s, c1, x, 256, B, L, b, ACT_RELU, nullptr, &l1);
+    else { conv32(c, s, c1, x, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln1_g, P.ln1_b, nullptr, B, L, b); }
+    if (ln_fusable(c, c2)) conv32(c, s, c2, b, 256, B, L, a, ACT_RELU, nullptr, &l2);
+    else { conv32(c, s, c2, b, 256, B, L, a, ACT_RELU); launch_layernorm(c, s, a, nullptr, P.ln2_g, P.ln2_b, nullptr, B, L, b); std::swap(a, b); }
     launch_rowdot_mask(c, s, a, P.lin_w, P.lin_b, lens, B, L, scale, out);
     ar.restore(mk);
 }
