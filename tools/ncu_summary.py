@@ -2,7 +2,7 @@
 """Per-launch table from an `ncu --set full ... --page raw --csv` export: duration, DRAM bytes, DRAM and tensor-pipe
 utilisation, shared-memory wavefronts.  Usage: ncu_summary.py prof.csv [out.csv]"""
 import csv, re, sys
-rows = list(csv.reader(open(sys.argv[1])))
+rows = list(csv.reader([l for l in open(sys.argv[1]) if not l.startswith('==')]))
 hdr, units, data = rows[0], rows[1], rows[2:]
 col = {h: i for i, h in enumerate(hdr)}
 def scale(v, u):
