@@ -431,7 +431,7 @@ def run_ours(args):
         if gather is not None:
             if pending[0] is not None:
                 pending[0].wait()
-            pending[0] = gather.start(w16.view(-1), g_off)
+            pending[0] = gather.start(w16.view(-1), g_off, n_max=w16.numel(), b_max=B)
         return w16, mel_lens
 
     # ---- device-resident throughput -----------------------------------------------------------------

@@ -334,31 +334,47 @@ class WaveformGather:
         self.stream = None
         self._pending = None
 
-    def start(self, packed, offsets):
+    def start(self, packed, offsets, n_max=None, b_max=None):
+        """Enqueue the exchange.  ``n_max`` / ``b_max`` (upper bounds, identical on every rank, on the samples and utterances any
+        rank holds — e.g. B * T_cap * hop and B): with them the sizes of the padded exchange are known up front and ``start`` does
+        not touch the host; without them the counts are all-gathered first and read back (one host synchronisation, which stalls
+        the launch of the next batch: measured +1.7 ms per C3 step on 8 GPUs)."""
         dist = self.dist
         dev = packed.device
         cuda = dev.type == "cuda"
         if cuda and self.stream is None:
             self.stream = torch.cuda.Stream(device=dev)
         B = offsets.numel() - 1
-        counts = torch.stack([offsets[B].to(torch.int64), torch.tensor(B, dtype=torch.int64, device=dev)])
+        known = n_max is not None and b_max is not None
         ready = torch.cuda.current_stream(dev).record_event() if cuda else None
 
         def run():
-            all_counts = torch.empty(self.world * 2, dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(all_counts, counts, group=self.group)
-            host = all_counts.view(self.world, 2).cpu()                                          # sizes of the padded exchange (16 bytes per rank)
-            n_max, b_max = int(host[:, 0].max()), int(host[:, 1].max())
-            send_w = torch.zeros(max(n_max, 1), dtype=torch.int16, device=dev)
-            send_w[: int(host[self.rank, 0])] = packed[: int(host[self.rank, 0])]
-            send_o = torch.zeros(b_max + 1, dtype=torch.int64, device=dev)
-            send_o[: B + 1] = offsets
-            recv_w = torch.empty(self.world * max(n_max, 1), dtype=torch.int16, device=dev)
-            recv_o = torch.empty(self.world * (b_max + 1), dtype=torch.int64, device=dev)
+            nm, bm = (int(n_max), int(b_max)) if known else (None, None)
+            if not known:
+                counts = torch.stack([offsets[B].to(torch.int64), torch.tensor(B, dtype=torch.int64, device=dev)])
+                all_counts = torch.empty(self.world * 2, dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(all_counts, counts, group=self.group)
+                host = all_counts.view(self.world, 2).cpu()                      # sizes of the padded exchange (16 bytes per rank)
+                nm, bm = int(host[:, 0].max()), int(host[:, 1].max())
+            nm = max(nm, 1)
+            if packed.numel() > nm or B > bm:
+                raise ValueError("WaveformGather: this rank holds more than n_max / b_max")
+            send_w = torch.zeros(nm, dtype=torch.int16, device=dev)
+            send_w[: packed.numel()] = packed                                    # samples beyond offsets[B] are never read back
+            send_o = torch.full((bm + 2,), -1, dtype=torch.int64, device=dev)    # [B | offsets (B + 1) | -1 padding]
+            send_o[0] = B
+            send_o[1: B + 2] = offsets
+            recv_w = torch.empty(self.world * nm, dtype=torch.int16, device=dev)
+            recv_o = torch.empty(self.world * (bm + 2), dtype=torch.int64, device=dev)
             # neither NCCL nor gloo has a 16-bit integer type: the samples travel as bytes
             dist.all_gather_into_tensor(recv_w.view(torch.uint8), send_w.view(torch.uint8), group=self.group)
             dist.all_gather_into_tensor(recv_o, send_o, group=self.group)
-            return host, recv_w.view(self.world, -1), recv_o.view(self.world, -1)
+            # the bookkeeping goes to the host on THIS stream, so that wait() never has to synchronise with the compute stream
+            host_o = recv_o
+            if cuda:
+                host_o = torch.empty(recv_o.shape, dtype=torch.int64).pin_memory()
+                host_o.copy_(recv_o, non_blocking=True)
+            return recv_w.view(self.world, -1), recv_o.view(self.world, -1), host_o.view(self.world, -1)
 
         if cuda:
             with torch.cuda.stream(self.stream):
@@ -373,11 +389,16 @@ class WaveformGather:
 
     def wait(self):
         """[(packed int16 [n_r], offsets int64 [B_r + 1])] for r in ranks; the compute stream waits for the side stream."""
-        (host, w, o), done, dev = self._pending
+        (w, o, host), done, dev = self._pending
         self._pending = None
         if done is not None:
+            done.synchronize()                                                   # the side stream only: long finished when waited a step later
             torch.cuda.current_stream(dev).wait_event(done)
-        return [(w[r, : int(host[r, 0])], o[r, : int(host[r, 1]) + 1]) for r in range(self.world)]
+        out = []
+        for r in range(self.world):
+            nb = int(host[r, 0])
+            out.append((w[r, : int(host[r, 1 + nb])], o[r, 1: nb + 2]))
+        return out
 
 
 def gather_waveforms(packed, offsets, group=None):

@@ -341,6 +341,8 @@ def _gather_worker(rank, world, port, q):
     off[1:] = torch.cumsum(torch.tensor(lens) * 256, 0)
     packed = torch.randint(-32768, 32767, (int(off[-1]),), generator=g, dtype=torch.int16)
     got = synth.gather_waveforms(packed, off)
+    got2 = synth.WaveformGather().start(packed, off, n_max=6 * 256, b_max=3).wait()   # sizes known up front: no counts exchange
+    assert all(torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) for a, b in zip(got, got2))
     q.put((rank, packed.numpy(), off.numpy(), [(w.numpy().copy(), o.numpy().copy()) for w, o in got]))
     dist.destroy_process_group()
 
