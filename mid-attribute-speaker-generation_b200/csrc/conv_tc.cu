@@ -14,14 +14,18 @@
 //   * A operand (activations), UMMA no-swizzle K-major layout (8-row x 16-byte core matrices), so that a conv tap is
 //     a 16-byte-granular shift of the descriptor start address: all taps (and dilations, and the two taps of a
 //     phase-decomposed ConvTranspose1d) reuse one resident tile — no im2col, no per-tap re-read.
-//       - planar input (HiFi-GAN): activations live in HBM as bf16 [B][C/8][T][8] — the operand layout itself —
-//         and ONE thread moves each (128 + halo)-row block with a 4-D TMA tile copy (cp.async.bulk.tensor); rows
-//         outside [0, T) are zero-filled by the TMA unit (= conv padding).  When the conv takes leaky_relu(x)
-//         (hifigan/models.py:98,152) 8 worker warps apply it in place in shared memory before the tile is released.
+//       - planar input (HiFi-GAN, the fp16 decoder side): activations live in HBM as bf16 / fp16 [B][C/8][T][8] — the operand
+//         layout itself — so the rows [t, t + R) of one 8-channel group are ONE contiguous run and the copy warp moves a
+//         (128 msub + halo)-row block with one 1-D bulk async copy per group (cp.async.bulk + mbarrier complete_tx, UBLKCP in
+//         SASS; no tensor maps: a 4-D cp.async.bulk.tensor box with a 16-byte innermost dimension was measured at ~16 B/clk/SM
+//         and removed in round 1).  Rows outside [0, T) (= conv padding, first / last tile only) are zero-filled by the lanes.
+//         When the conv takes leaky_relu(x) (hifigan/models.py:98,152) 8 worker warps apply it in place in shared memory
+//         before the tile is released.
 //       - row-major fp32 input (FastSpeech2): 8 worker warps stage the tile with 128-bit loads, converting to bf16
 //         (hi + lo halves in split mode).
 //   * B operand (weights): pre-tiled at commit (k_tile_w) into contiguous blobs already in UMMA layout, streamed by
-//     one thread with 1-D bulk async copies (cp.async.bulk + mbarrier complete_tx) through a 4-stage ring.
+//     one thread with 1-D bulk async copies through a 3- or 4-stage ring, or resident for the life of the CTA when one N
+//     tile's weights fit (<= 100 KB).
 //   * One thread issues tcgen05.mma (M=128, N=NT, K=16, bf16 x bf16 -> fp32) into msub TMEM accumulators; the issue
 //     loop is specialised on msub and keeps every descriptor a running add (a single thread issues one instruction
 //     every few cycles, and an N=32 MMA only lasts 16); tcgen05.commit releases weight stages / activation slots.
@@ -44,7 +48,7 @@ constexpr int EPI_WARPS = 8;            // warps 0-7: epilogue (warp % 4 = TMEM 
 constexpr int MMA_WARP = 8;             // warps 8-11: MMA issuers (one thread each, on the four different warp schedulers)
 constexpr int MMA_WARPS = 4;
 constexpr int W_WARP = 12;              // weight stream
-constexpr int T_WARP = 13;              // TMA issuer for planar activations
+constexpr int T_WARP = 13;              // bulk-copy issuer for planar activations
 constexpr int A_WARP0 = 14;             // activation workers
 constexpr int A_WARPS = 8;
 constexpr int A_THREADS = A_WARPS * 32;
