@@ -163,6 +163,18 @@ int masg_synthesize_host_packed(masg_ctx* ctx, void* stream, const int64_t* h_te
                                 float p_ctl, float e_ctl, float d_ctl, int64_t cap_samples,
                                 int16_t* h_wav_packed, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax);
 
+/* Deferred-copy form for a stream of batches (a generation job, a service): the call returns once the batch is enqueued — after
+ * phase A's one synchronisation — with the D2H copy of the audio queued on a copy stream of the context's own; h_offsets and
+ * h_mel_lens are valid on return, h_wav_packed after masg_synthesize_host_wait(ctx, *ticket).  Two output buffers alternate, so
+ * the copy of batch n overlaps phase A of batch n + 1; at most two tickets are outstanding (the third call waits, on the device,
+ * for the first copy).  The caller alternates its own pinned destination buffers. */
+int masg_synthesize_host_packed_async(masg_ctx* ctx, void* stream, const int64_t* h_texts, const int64_t* h_accents,
+                                      const int64_t* h_src_lens, int B, int L, const float* h_spk_emb,
+                                      float p_ctl, float e_ctl, float d_ctl, int64_t cap_samples,
+                                      int16_t* h_wav_packed, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax,
+                                      int* ticket);
+int masg_synthesize_host_wait(masg_ctx* ctx, int ticket);
+
 /* One Conv1d (torch.nn.Conv1d as used throughout transformer/SubLayers.py:72-83, model/modules.py:253-296,
  * hifigan/models.py:24-91) or, with stride_transposed = u > 0, one ConvTranspose1d(k = 2u, stride u,
  * padding u/2) (hifigan/models.py:127-133) through the context's dense-contraction kernel — the tcgen05

@@ -42,6 +42,9 @@ SIGNATURES = {
                                      ctypes.POINTER(c_i64)]),
     "masg_synthesize_host_packed": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_i64, P, P, P,
                                             ctypes.POINTER(c_i64)]),
+    "masg_synthesize_host_packed_async": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_i64, P, P, P,
+                                                  ctypes.POINTER(c_i64), ctypes.POINTER(c_int)]),
+    "masg_synthesize_host_wait": (c_int, [P, c_int]),
     "masg_conv1d": (c_int, [P, P, P, c_int, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_float, c_int, c_int, c_int, P,
                             ctypes.POINTER(c_float)]),
     "masg_attention": (c_int, [P, P, P, P, c_int, c_int, P]),

@@ -65,6 +65,9 @@ void masg_ctx_destroy(masg_ctx* c) {
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->io_buf) cudaFree(c->io_buf);
     if (c->out_buf) cudaFree(c->out_buf);
+    if (c->out_alt) cudaFree(c->out_alt);
+    for (int i = 0; i < 2; ++i) { if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]); if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     delete c;
 }
 
@@ -338,9 +341,20 @@ static void run_graphed(masg_ctx* c, cudaStream_t s, const std::vector<long>& ke
 // samples at h_offsets[b]) and ONE D2H copy moves exactly the valid samples.
 static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
                             int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int packed, int64_t cap,
-                            int16_t* h_wav, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax) {
+                            int16_t* h_wav, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax, int* ticket = nullptr) {
     MASG_CHECK(h_texts && h_accents && h_src_lens && h_spk_emb && h_wav, "null argument");
     MASG_CHECK(B > 0 && L > 0, "empty batch B=%d L=%d", B, L);
+    const bool defer = ticket != nullptr;
+    if (defer) {                                             // the other output buffer: the previous call's audio may still be in flight
+        std::swap(c->out_buf, c->out_alt); std::swap(c->out_cap, c->out_alt_cap); c->out_idx ^= 1;
+        if (!c->copy_stream) {
+            CUDA_OK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming)); }
+        }
+    }
+    const int oi = c->out_idx;
+    // whatever was last copied out of THIS buffer (two deferred calls ago) must have left before anything overwrites it
+    if (c->ev_copied[oi]) CUDA_OK(cudaStreamWaitEvent(s, c->ev_copied[oi], 0));
     // two growth-only staging buffers of their own (arena / arena_b are reset by the phases): io_buf for the inputs and phase A's
     // small outputs (sized by B and L, before anything is enqueued), out_buf for mel / postnet mel / audio (sized once T_max and
     // the lengths are known, right after phase A's sync — growing it there costs no extra synchronisation)
@@ -365,7 +379,7 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     int64_t tmax = 0;
     // the controls are baked into a captured graph: they are part of the key (as float bit patterns)
     auto fbits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return (long)u; };
-    run_graphed(c, s, {0, B, L, 0, 0, fbits(p_ctl), fbits(d_ctl)}, (long)rows, [&](cudaStream_t bs) {
+    run_graphed(c, s, {0, B, L, 0, oi, fbits(p_ctl), fbits(d_ctl)}, (long)rows, [&](cudaStream_t bs) {
         fs2_phase_a(c, bs, texts, acc, 0, lens, B, L, spk, p_ctl, e_ctl, d_ctl, nullptr, nullptr, nullptr, pitch, energy, logd, drnd, mel_lens,
                     nullptr, nullptr);
     });
@@ -380,13 +394,14 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
     else MASG_CHECK(tmax <= cap, "T_max=%lld exceeds t_cap=%lld", (long long)tmax, (long long)cap);
     const size_t out_bytes = ((size_t)B * T * 80 * 4 + 256) * 2 + (packed ? (size_t)total * 512 : (size_t)B * T * 512) + 1024;
     if (c->out_cap < out_bytes) {                            // the stream is idle here (phase A just synchronised)
+        if (c->ev_copied[oi]) CUDA_OK(cudaEventSynchronize(c->ev_copied[oi]));
         if (c->out_buf) { cudaFree(c->out_buf); c->out_buf = nullptr; c->out_cap = 0; }
         CUDA_OK(cudaMalloc(&c->out_buf, out_bytes + out_bytes / 4)); c->out_cap = out_bytes + out_bytes / 4;
     }
     p = (char*)c->out_buf;
     float* mel = (float*)take((size_t)B * T * 80 * 4); float* post = (float*)take((size_t)B * T * 80 * 4);
     int16_t* w16 = (int16_t*)take(packed ? (size_t)total * 512 : (size_t)B * T * 512);
-    run_graphed(c, s, {1, B, L, T, packed}, (long)rows, [&](cudaStream_t bs) {
+    run_graphed(c, s, {1, B, L, T, packed, oi}, (long)rows, [&](cudaStream_t bs) {
         fs2_phase_b(c, bs, T, mel, post, nullptr);
         if (packed) {
             launch_wav_offsets(c, bs, mel_lens, B, 256, woff, wlen);
@@ -395,9 +410,18 @@ static void synthesize_host(masg_ctx* c, cudaStream_t s, const int64_t* h_texts,
             hifigan_forward(c, bs, post, 1, B, T, nullptr, w16);
         }
     });
-    if (packed) CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, s));
-    else CUDA_OK(cudaMemcpy2DAsync(h_wav, (size_t)cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, s));
-    CUDA_OK(cudaStreamSynchronize(s));
+    // deferred: the copy goes to the context's copy stream behind an event and the call returns; masg_synthesize_host_wait(ticket)
+    // makes the audio visible.  The next call's phase A (and its one synchronisation) then overlaps this copy.
+    cudaStream_t cs = s;
+    if (defer) {
+        CUDA_OK(cudaEventRecord(c->ev_done[oi], s));
+        CUDA_OK(cudaStreamWaitEvent(c->copy_stream, c->ev_done[oi], 0));
+        cs = c->copy_stream;
+    }
+    if (packed) CUDA_OK(cudaMemcpyAsync(h_wav, w16, (size_t)total * 512, cudaMemcpyDeviceToHost, cs));
+    else CUDA_OK(cudaMemcpy2DAsync(h_wav, (size_t)cap * 256 * 2, w16, (size_t)T * 256 * 2, (size_t)T * 256 * 2, B, cudaMemcpyDeviceToHost, cs));
+    if (defer) { CUDA_OK(cudaEventRecord(c->ev_copied[oi], cs)); *ticket = oi; }
+    else CUDA_OK(cudaStreamSynchronize(s));
     if (h_tmax) *h_tmax = tmax;
 }
 
@@ -419,6 +443,23 @@ int masg_synthesize_host_packed(masg_ctx* c, void* stream, const int64_t* h_text
     MASG_CHECK(h_offsets != nullptr, "null h_offsets");
     synthesize_host(c, (cudaStream_t)stream, h_texts, h_accents, h_src_lens, B, L, h_spk_emb, p_ctl, e_ctl, d_ctl, 1, cap_samples,
                     h_wav_packed, h_offsets, h_mel_lens, h_tmax);
+    API_END(c)
+}
+
+int masg_synthesize_host_packed_async(masg_ctx* c, void* stream, const int64_t* h_texts, const int64_t* h_accents, const int64_t* h_src_lens,
+                                      int B, int L, const float* h_spk_emb, float p_ctl, float e_ctl, float d_ctl, int64_t cap_samples,
+                                      int16_t* h_wav_packed, int64_t* h_offsets, int64_t* h_mel_lens, int64_t* h_tmax, int* ticket) {
+    API_BEGIN(c)
+    MASG_CHECK(h_offsets != nullptr && ticket != nullptr, "null h_offsets / ticket");
+    synthesize_host(c, (cudaStream_t)stream, h_texts, h_accents, h_src_lens, B, L, h_spk_emb, p_ctl, e_ctl, d_ctl, 1, cap_samples,
+                    h_wav_packed, h_offsets, h_mel_lens, h_tmax, ticket);
+    API_END(c)
+}
+
+int masg_synthesize_host_wait(masg_ctx* c, int ticket) {
+    API_BEGIN(c)
+    MASG_CHECK((ticket == 0 || ticket == 1) && c->ev_copied[ticket], "unknown ticket %d", ticket);
+    CUDA_OK(cudaEventSynchronize(c->ev_copied[ticket]));
     API_END(c)
 }
 

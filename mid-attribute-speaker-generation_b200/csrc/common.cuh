@@ -116,6 +116,10 @@ struct masg_ctx {
     int64_t* h_pinned = nullptr; int h_pinned_n = 0;   // pinned host scratch: [mel_lens (B) | T_max] of the last phase A
     void* io_buf = nullptr; size_t io_cap = 0;   // device staging of the host-buffer entry points: inputs + phase-A outputs
     void* out_buf = nullptr; size_t out_cap = 0; // ... and mel / postnet mel / audio (sized after phase A)
+    // deferred-copy mode of the host-buffer entry points: a second output buffer, a copy stream and per-buffer events, so that the
+    // D2H of call n runs while call n + 1 computes
+    void* out_alt = nullptr; size_t out_alt_cap = 0; int out_idx = 0;
+    cudaStream_t copy_stream = nullptr; cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
     // ---- HiFi-GAN ----
     ConvDesc hg_pre, hg_ups[4], hg_c1[12][3], hg_c2[12][3];
     const float* hg_post_w = nullptr; float hg_post_b = 0.f;   // [7][32] fp32

@@ -88,6 +88,30 @@ class Synthesizer:
         d2h = int(h_o[B]) * 2 + (B + 1) * 8
         return h_w, h_o, h_m, int(tmax.value), h2d, d2h
 
+    def synthesize_host_packed_async(self, texts, accents, src_lens, speaker_emb, cap_samples, p_control=1.0, e_control=1.0, d_control=1.0):
+        """Deferred-copy form (masg_synthesize_host_packed_async): returns a handle as soon as the batch is enqueued; ``handle.wait()``
+        yields the tuple of ``synthesize_host_packed`` once the audio has landed.  Two sets of pinned buffers alternate, so keep at
+        most two handles un-waited; the D2H copy of one batch overlaps the next batch's phase A."""
+        B, L = texts.shape
+        k = self._async_i = getattr(self, "_async_i", 0) ^ 1
+        tag = "a%d_" % k
+        h_t = self._pinned(tag + "texts", (B, L), torch.int64); h_t.copy_(texts)
+        h_a = self._pinned(tag + "accents", (B, L), torch.int64); h_a.copy_(accents)
+        h_l = self._pinned(tag + "lens", (B,), torch.int64); h_l.copy_(src_lens)
+        h_s = self._pinned(tag + "spk", (B, 256), torch.float32); h_s.copy_(speaker_emb)
+        h_w = self._pinned(tag + "wav_packed", (int(cap_samples),), torch.int16)
+        h_o = self._pinned(tag + "offsets", (B + 1,), torch.int64)
+        h_m = self._pinned(tag + "mel_lens", (B,), torch.int64)
+        tmax, ticket = ctypes.c_int64(0), ctypes.c_int(-1)
+        ctx = self.ctx
+        ctx.check(ctx.lib.masg_synthesize_host_packed_async(ctx.h, ctx.stream(), _lib.ptr(h_t), _lib.ptr(h_a), _lib.ptr(h_l), B, L,
+                                                            _lib.ptr(h_s), float(p_control), float(e_control), float(d_control),
+                                                            ctypes.c_int64(int(cap_samples)), _lib.ptr(h_w), _lib.ptr(h_o), _lib.ptr(h_m),
+                                                            ctypes.byref(tmax), ctypes.byref(ticket)), "masg_synthesize_host_packed_async")
+        h2d = h_t.numel() * 8 + h_a.numel() * 8 + h_l.numel() * 8 + h_s.numel() * 4
+        d2h = int(h_o[B]) * 2 + (B + 1) * 8
+        return _PendingAudio(ctx, ticket.value, (h_w, h_o, h_m, int(tmax.value), h2d, d2h))
+
     def generate(self, texts, speakers, out_dir=None, speaker_names=None, text_ids=None, n_speakers=None, seed=0, p_control=1.0,
                  e_control=1.0, d_control=1.0, frame_budget=40000, max_batch=64, frames_per_phoneme=6.0, writer=None,
                  save_embeddings=True, sampling_rate=SAMPLING_RATE):
@@ -169,6 +193,19 @@ class Synthesizer:
             if own_writer:
                 writer.close()
         return results
+
+
+class _PendingAudio:
+    """Handle of a deferred-copy synthesis call."""
+
+    def __init__(self, ctx, ticket, result):
+        self._ctx, self._ticket, self._result = ctx, ticket, result
+
+    def wait(self):
+        if self._ticket is not None:
+            self._ctx.check(self._ctx.lib.masg_synthesize_host_wait(self._ctx.h, self._ticket), "masg_synthesize_host_wait")
+            self._ticket = None
+        return self._result
 
 
 class SpeakerSampler:

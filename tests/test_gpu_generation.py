@@ -258,3 +258,28 @@ def test_out_of_range_ids_raise_like_nn_embedding():
     table = torch.zeros(256, 256, device=DEV); x = torch.zeros(2, 256, device=DEV); idx = torch.empty(2, dtype=torch.int64, device=DEV)
     cx.check(cx.lib.masg_bucketize_embed_add(cx.h, cx.stream(), _lib.ptr(v), _lib.ptr(bins), 255, _lib.ptr(table), 2, 256, _lib.ptr(x), _lib.ptr(idx)), "bucket")
     assert idx.tolist() == torch.bucketize(v.cpu(), bins.cpu()).tolist() == [255, 127]
+
+
+def test_deferred_copy_calls_match_blocking_calls():
+    """masg_synthesize_host_packed_async: three batches in flight-order (two output buffers alternate, the third call waits on
+    the device for the first copy) give bit for bit the audio of the blocking call, whatever order the handles are waited in."""
+    from masg_b200.synth import Synthesizer
+    fs2, sd = helpers.fs2_on_gpu(11, "spread", "bf16")
+    voc, hsd = helpers.hifigan_on_gpu(4321, "bf16")
+    s = Synthesizer(fs2, voc, "bf16")
+    batches = [syn.make_batch(3, 20, seed=50 + i, lens=[20, 12 + i, 5]) for i in range(3)]
+    embs = [torch.randn(3, 256, generator=torch.Generator().manual_seed(60 + i)) * 0.5 for i in range(3)]
+    want = []
+    for b, e in zip(batches, embs):
+        w, o, m, T, _, _ = s.synthesize_host_packed(b["texts"], b["accents"], b["src_lens"], e, 3 * 400 * 256)
+        want.append((w[: int(o[-1])].clone(), o.clone(), m.clone()))
+    for rep in range(2):                                                       # second round: replayed graphs on both buffers
+        h0 = s.synthesize_host_packed_async(batches[0]["texts"], batches[0]["accents"], batches[0]["src_lens"], embs[0], 3 * 400 * 256)
+        h1 = s.synthesize_host_packed_async(batches[1]["texts"], batches[1]["accents"], batches[1]["src_lens"], embs[1], 3 * 400 * 256)
+        r0 = h0.wait()
+        got0 = (r0[0][: int(r0[1][-1])].clone(), r0[1].clone(), r0[2].clone())  # its pinned set is reused by the third call
+        h2 = s.synthesize_host_packed_async(batches[2]["texts"], batches[2]["accents"], batches[2]["src_lens"], embs[2], 3 * 400 * 256)
+        r2, r1 = h2.wait(), h1.wait()
+        got = [got0, (r1[0][: int(r1[1][-1])], r1[1], r1[2]), (r2[0][: int(r2[1][-1])], r2[1], r2[2])]
+        for (gw, go, gm), (ww, wo, wm) in zip(got, want):
+            assert torch.equal(go, wo) and torch.equal(gm, wm) and torch.equal(gw, ww)
