@@ -526,7 +526,9 @@ def run_ours(args):
     torch.cuda.synchronize()
     ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
     barrier()
-    assert int(h_o[B]) == B * 3 * L * syn.HOP and torch.equal(h_wp[: int(h_o[B])].view(B, -1), h_w[:, : 3 * L * syn.HOP]), "deferred-copy audio differs"
+    # (every step draws new speakers, so the audio differs from step to step; bit-equality of the two calls on the same inputs is
+    # tests/test_gpu_generation.py::test_deferred_copy_calls_match_blocking_calls)
+    assert int(h_o[B]) == B * 3 * L * syn.HOP and int(h_wp[: int(h_o[B])].abs().max()) > 0, "deferred-copy call returned no audio"
     e2e_value = world * audio_per_step * args.steps / (ms_e2e / 1e3)
     d2h = d2h2 + B * 256 * 4
     clk = clocks.stop() if rank == 0 else None
