@@ -163,20 +163,8 @@ class Synthesizer:
         try:
             if out_dir is not None and save_embeddings:
                 save_speaker_embeddings(out_dir, speaker_names, emb)
-            for bi, idx in enumerate(batches):
-                t_idx = torch.from_numpy(utt_text[idx])
-                L = int(utt_len[idx].max())
-                b_ids, b_acc, b_len = ids[t_idx, :L].contiguous(), acc[t_idx, :L].contiguous(), lens[t_idx].contiguous()
-                b_emb = emb[torch.from_numpy(utt_spk[idx])].contiguous()
-                cap = int(len(idx) * L * 2 * frames_per_phoneme) * HOP
-                while True:
-                    try:
-                        h_w, h_o, h_m, T, _, _ = self.synthesize_host_packed(b_ids, b_acc, b_len, b_emb, cap, p_control, e_control, d_control)
-                        break
-                    except RuntimeError as e:
-                        if "capacity" not in str(e):
-                            raise
-                        cap *= 2                                      # durations longer than the estimate: retry with more room
+            def collect(bi, idx, L, handle):
+                h_w, h_o, h_m, T, _, _ = handle.wait()
                 off = h_o.numpy()
                 flat = h_w.numpy()
                 for k, u in enumerate(idx):
@@ -185,10 +173,36 @@ class Synthesizer:
                            "mel_len": int(h_m[k]), "batch": bi, "row": k, "padded_to": L}
                     if out_dir is not None:
                         rec["path"] = os.path.join(str(out_dir), "%s_%s.wav" % (rec["speaker"], rec["text_id"]))
-                        writer.submit(rec["path"], sampling_rate, wav, copy=True)     # the pinned buffer is reused by the next batch
+                        writer.submit(rec["path"], sampling_rate, wav, copy=True)     # the pinned buffer is reused two batches later
                     else:
                         rec["wav"] = wav.copy()
                     results[int(u)] = rec
+
+            # deferred-copy calls, one batch in flight behind the one being collected: the D2H copy and the file hand-over of batch
+            # n overlap the synthesis of batch n + 1
+            prev = None
+            for bi, idx in enumerate(batches):
+                t_idx = torch.from_numpy(utt_text[idx])
+                L = int(utt_len[idx].max())
+                b_ids, b_acc, b_len = ids[t_idx, :L].contiguous(), acc[t_idx, :L].contiguous(), lens[t_idx].contiguous()
+                b_emb = emb[torch.from_numpy(utt_spk[idx])].contiguous()
+                cap = int(len(idx) * L * 2 * frames_per_phoneme) * HOP
+                while True:
+                    try:
+                        handle = self.synthesize_host_packed_async(b_ids, b_acc, b_len, b_emb, cap, p_control, e_control, d_control)
+                        break
+                    except RuntimeError as e:
+                        if "capacity" not in str(e):
+                            raise
+                        cap *= 2                                      # durations longer than the estimate: retry with more room
+                        if prev is not None:                          # the retry reuses the pinned set of the batch still in flight
+                            collect(*prev)
+                            prev = None
+                if prev is not None:
+                    collect(*prev)
+                prev = (bi, idx, L, handle)
+            if prev is not None:
+                collect(*prev)
         finally:
             if own_writer:
                 writer.close()
