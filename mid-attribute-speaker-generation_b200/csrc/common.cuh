@@ -54,6 +54,9 @@ struct ConvDesc {
     // tcgen05 path (conv_tc.cu): bf16 weights pre-tiled into UMMA no-swizzle K-major blobs
     // [n_tile = N/NT][ci = Cin/KW][tap][KW/8][NT][8]; one blob = one (channel slab, tap) B operand
     const bf16* w16 = nullptr; int NT = 0, KW = 0, split = 0, f16 = 0;   // f16: the blobs hold fp16, not bf16
+    // second tiling of the same weights at 32 columns per tile, for launches that would otherwise run on a handful of CTAs (small
+    // batches: the latency path): 4x the CTAs, each streaming a quarter of the weights
+    const bf16* w16s = nullptr; int NTs = 0, KWs = 0;
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc

@@ -999,9 +999,42 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
     k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, w16, d.Cin, d.N, d.taps, NT, KW, mode);
     c->launches++;
     d.w16 = w16; d.NT = NT; d.KW = KW; d.split = split ? 1 : 0; d.f16 = mode == 2 ? 1 : 0;
+    d.w16s = nullptr; d.NTs = 0; d.KWs = 0;
+    static int small = -1;
+    if (small < 0) { const char* e = getenv("MASG_TC_SMALL"); small = e ? atoi(e) : 1; }
+    if (small && !wide && NT > 32 && d.N % 32 == 0) {
+        const int KWs = (d.Cin % 64 == 0) ? 64 : (d.Cin % 32 == 0 ? 32 : 16);
+        bf16* ws = nullptr;
+        CUDA_OK(cudaMalloc(&ws, n * sizeof(bf16) * (split ? 2 : 1)));
+        c->owned.push_back(ws);
+        k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, ws, d.Cin, d.N, d.taps, 32, KWs, mode);
+        c->launches++;
+        d.w16s = ws; d.NTs = 32; d.KWs = KWs;
+    }
 }
 
+static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
+
+// Tiling choice per launch: the commit-time tiling (128 / 80 / 64 / 32 / 256 columns), or — when that would put the layer on fewer
+// than a third of the SMs (B = 1: a 256-channel HiFi-GAN conv is 10 tiles of 128 columns, each CTA streaming 0.7 MB of weights
+// alone) — the 32-column tiling of the same weights: four times the CTAs, a quarter of the weight stream each.  N = 32 MMAs run at
+// 40 % of the tensor peak, which does not matter where the launch is bound by weight latency (C2: 20-30 us per launch).
 void launch_conv_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
+    if (d.w16s && io.Q > 0 && io.B > 0 && !io.ln_g) {
+        static int thr = -1;
+        if (thr < 0) { const char* e = getenv("MASG_TC_SMALL_TILES"); thr = e ? atoi(e) : c->n_sm / 3; }
+        const long tiles = (long)io.B * ((io.Q + 127) / 128) * (d.N / d.NT);
+        if (tiles < thr) {
+            ConvDesc ds = d;
+            ds.w16 = d.w16s; ds.NT = d.NTs; ds.KW = d.KWs;
+            launch_conv_tc_tiled(c, s, ds, io);
+            return;
+        }
+    }
+    launch_conv_tc_tiled(c, s, d, io);
+}
+
+static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io) {
     MASG_CHECK(d.w16 != nullptr && d.NT > 0, "conv_tc: bf16 weights not committed");
     MASG_CHECK(io.Y != nullptr || io.Y16 != nullptr, "conv_tc: no output tensor");
     MASG_CHECK(d.N <= BIAS_MAX, "conv_tc: N=%d exceeds the staged bias row (%d)", d.N, BIAS_MAX);
