@@ -146,6 +146,19 @@ int masg_gmm_barycenter(masg_ctx* ctx, void* stream, const float* pi, const floa
                         const float* h_rate, int A, int K, int D, float* bary_mean, float* bary_std,
                         float* bary_weight, int32_t* assign /* [A*K] nearest barycentre index */);
 
+/* masg_gmm_barycenter for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, same results
+ * (bit for bit) as masg_gmm_barycenter, but the call allocates nothing — no cudaMalloc / cudaFree, no host heap — and never
+ * synchronises the stream: the rate vector and the per-barycentre weight accumulators live in one fixed file-scope device array
+ * (16.25 KB, held by every GPU that loads the library until exit) and the weights are summed on the device.
+ * Limit: K^A <= MASG_NOALLOC_MAX_BARYCENTRES (and A <= 8); beyond it the call fails with a message naming the limit.
+ * All contexts and streams of one device share that array: calls that overlap on the GPU race on it (serialise them on one
+ * stream, or with events).  h_rate is read on the host before the call returns. */
+#define MASG_NOALLOC_MAX_BARYCENTRES 4096
+int masg_gmm_barycenter_noalloc(masg_ctx* ctx, void* stream, const float* pi, const float* mu, const float* sigma,
+                                const float* h_rate, int A, int K, int D, float* bary_mean, float* bary_std,
+                                float* bary_weight, int32_t* assign /* [A*K] nearest barycentre index */);
+
 /* End-to-end with HOST buffers (examples_gen.py:114-140 synthesize() + utils/model.py:74-92
  * vocoder_infer): H2D of ids/lens/speaker embeddings, FastSpeech2, HiFi-GAN, int16 conversion and D2H
  * of the waveforms, all inside the call.  h_wav_i16 must hold B * 256 * t_cap samples; rows are

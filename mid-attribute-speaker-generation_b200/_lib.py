@@ -38,6 +38,7 @@ SIGNATURES = {
     "masg_gmm_sample": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_u64, c_u64, P, P, P, P]),
     "masg_gmm_interpolate": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int, c_float, c_int, P, P, P, P]),
     "masg_gmm_barycenter": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P]),
+    "masg_gmm_barycenter_noalloc": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P]),
     "masg_synthesize_host": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_int, P, P,
                                      ctypes.POINTER(c_i64)]),
     "masg_synthesize_host_packed": (c_int, [P, P, P, P, P, c_int, c_int, P, c_float, c_float, c_float, c_i64, P, P, P,
