@@ -552,17 +552,22 @@ int masg_respair(masg_ctx* c, void* stream, const float* x, const float* acc, in
     const size_t keep = c->owned.size();
     ConvDesc d1 = make_conv(c, s, w1, b1, C, C, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, false);
     ConvDesc d2 = make_conv(c, s, w2, b2, C, C, k, (k - 1) / 2, 1, nullptr, nullptr, false);
-    MASG_CHECK(respair_tc_supported(c, d1, d2), "masg_respair: unsupported pair C=%d k=%d dilation=%d", C, k, dilation);
+    const bool one_sm = respair_tc_supported(c, d1, d2);
+    MASG_CHECK(one_sm || respair2_tc_supported(c, d1, d2), "masg_respair: unsupported pair C=%d k=%d dilation=%d", C, k, dilation);
+    auto run = [&](const bf16* xi, bf16* yo, const bf16* ai) {
+        if (one_sm) launch_respair_tc(c, s, d1, d2, xi, B, T, yo, ai, out_scale, post_slope);
+        else launch_respair2_tc(c, s, d1, d2, xi, B, T, yo, ai, out_scale, post_slope);
+    };
     const size_t n = (size_t)B * T * C;
     bf16 *x16 = nullptr, *y16 = nullptr, *a16 = nullptr;
     CUDA_OK(cudaMalloc(&x16, n * 2)); c->owned.push_back(x16);
     CUDA_OK(cudaMalloc(&y16, n * 2)); c->owned.push_back(y16);
     launch_to_planar(c, s, x, x16, B, T, C);
     if (acc) { CUDA_OK(cudaMalloc(&a16, n * 2)); c->owned.push_back(a16); launch_to_planar(c, s, acc, a16, B, T, C); }
-    launch_respair_tc(c, s, d1, d2, x16, B, T, y16, a16, out_scale, post_slope);
+    run(x16, y16, a16);
     cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));
     CUDA_OK(cudaEventRecord(e0, s));
-    for (int r = 0; r < reps; ++r) launch_respair_tc(c, s, d1, d2, x16, B, T, y16, a16, out_scale, post_slope);
+    for (int r = 0; r < reps; ++r) run(x16, y16, a16);
     CUDA_OK(cudaEventRecord(e1, s));
     CUDA_OK(cudaStreamSynchronize(s));
     float ms = 0.f; CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));

@@ -57,6 +57,9 @@ struct ConvDesc {
     // second tiling of the same weights at 32 columns per tile, for launches that would otherwise run on a handful of CTAs (small
     // batches: the latency path): 4x the CTAs, each streaming a quarter of the weights
     const bf16* w16s = nullptr; int NTs = 0, KWs = 0;
+    // third tiling, for the fused ResBlock pair on a CTA pair (respair2_tc.cu): the columns split in two halves of N/2, each
+    // [tap][Cin/8][N/2][8] — one half per CTA of the cluster (tcgen05 cta_group::2 B operand)
+    const bf16* w16p = nullptr;
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc

@@ -1011,6 +1011,16 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
         c->launches++;
         d.w16s = ws; d.NTs = 32; d.KWs = KWs;
     }
+    d.w16p = nullptr;
+    if (!split && mode == 0 && !wide && d.Cin == d.N && ((d.N == 128 && d.taps == 3) || (d.N == 64 && d.taps == 11))) {
+        // square convs that respair2_tc.cu fuses on a CTA pair: [2 halves][1][taps][Cin/8][N/2][8]
+        bf16* wp = nullptr;
+        CUDA_OK(cudaMalloc(&wp, n * sizeof(bf16)));
+        c->owned.push_back(wp);
+        k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, wp, d.Cin, d.N, d.taps, d.N / 2, d.Cin, 0);
+        c->launches++;
+        d.w16p = wp;
+    }
 }
 
 static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);

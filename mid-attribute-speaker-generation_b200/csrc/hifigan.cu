@@ -144,6 +144,9 @@ static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT,
                 if (respair_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
                     // narrow stages: both convs in one kernel, h stays in shared memory (respair_tc.cu)
                     launch_respair_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
+                } else if (respair2_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
+                    // pairs whose weights need two SMs: the same fusion on a CTA pair (respair2_tc.cu)
+                    launch_respair2_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
                 } else {
                     convP(c, s, c->hg_c1[rb][m], y, true, B, So, h, So, ACT_LRELU, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)So);
                     convP(c, s, c->hg_c2[rb][m], h, true, B, So, yn, So, ACT_NONE, ACT_NONE, y, acc, scale, post, (int)So);

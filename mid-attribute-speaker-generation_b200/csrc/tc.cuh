@@ -20,3 +20,8 @@ bool respair_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc&
 void launch_respair_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const ConvDesc& d2, const bf16* X, int B, int T,
                        bf16* Y, const bf16* R2, float out_scale, float post_slope);
 int respair_debug_trace(long long* out, int max_elems);      // MASG_TC_DEBUG & 32: [5 roles][96 tiles][4 events] clock64 of CTA 0
+// the same fused pair on a CTA pair (cluster of 2, tcgen05 cta_group::2, the weights' columns split over the two CTAs) for the
+// pairs whose weights do not fit one SM: C = 128 k = 3 and C = 64 k = 11 (respair2_tc.cu)
+bool respair2_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc& d2);
+void launch_respair2_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const ConvDesc& d2, const bf16* X, int B, int T,
+                        bf16* Y, const bf16* R2, float out_scale, float post_slope);

@@ -500,6 +500,16 @@ RESPAIR_CASES = [
     (1, 2100, 64, 3, 1, True, 1.0, 1.0),
     (2, 1100, 64, 7, 5, True, 1.0 / 3.0, 0.1),       # weights fill shared memory: 2 activation slots, 1 h buffer
     (1, 250, 64, 7, 1, False, 1.0, 1.0),
+    # the CTA-pair kernel (respair2_tc.cu: cluster of 2, tcgen05 cta_group::2, weight columns split over the pair)
+    (2, 700, 128, 3, 1, False, 1.0, 1.0),
+    (1, 1300, 128, 3, 5, True, 1.0 / 3.0, 0.1),
+    (1, 126 * 3, 128, 3, 3, False, 1.0, 1.0),         # odd tile count: the last pair's second tile is empty
+    (3, 126 * 2, 128, 3, 3, True, 1.0, 1.0),          # T an exact multiple of the output rows per tile
+    (2, 1100, 64, 11, 5, True, 1.0 / 3.0, 0.1),
+    (1, 246 * 3, 64, 11, 1, False, 1.0, 1.0),
+    (1, 100, 64, 11, 3, False, 1.0, 1.0),             # one tile: the peer CTA has nothing to do
+    (5, 3000, 64, 11, 3, False, 1.0, 1.0),            # more tile pairs than one wave of clusters walks in one go? no: 65 tiles, 33 pairs
+    (40, 4000, 128, 3, 1, True, 1.0, 1.0),            # 1280 tiles = 640 pairs on 74 clusters: several pairs per cluster, slot reuse
 ]
 
 

@@ -12,6 +12,8 @@ CASES = [  # name, B, T, C, k, dil
     ("s4 k3 d1", 64, 153600, 32, 3, 1), ("s4 k3 d5", 64, 153600, 32, 3, 5), ("s4 k7 d3", 64, 153600, 32, 7, 3),
     ("s4 k11 d1", 64, 153600, 32, 11, 1), ("s4 k11 d5", 64, 153600, 32, 11, 5),
     ("s3 k3 d1", 64, 76800, 64, 3, 1), ("s3 k3 d5", 64, 76800, 64, 3, 5), ("s3 k7 d3", 64, 76800, 64, 7, 3),
+    # CTA-pair kernel (respair2_tc.cu)
+    ("s3 k11 d1", 64, 76800, 64, 11, 1), ("s3 k11 d5", 64, 76800, 64, 11, 5), ("s2 k3 d1", 64, 38400, 128, 3, 1), ("s2 k3 d5", 64, 38400, 128, 3, 5),
 ]
 
 def main():
