@@ -552,8 +552,8 @@ int masg_respair(masg_ctx* c, void* stream, const float* x, const float* acc, in
     const size_t keep = c->owned.size();
     ConvDesc d1 = make_conv(c, s, w1, b1, C, C, k, (k * dilation - dilation) / 2, dilation, nullptr, nullptr, false);
     ConvDesc d2 = make_conv(c, s, w2, b2, C, C, k, (k - 1) / 2, 1, nullptr, nullptr, false);
-    const bool one_sm = respair_tc_supported(c, d1, d2);
-    MASG_CHECK(one_sm || respair2_tc_supported(c, d1, d2), "masg_respair: unsupported pair C=%d k=%d dilation=%d", C, k, dilation);
+    const bool two_sm = respair2_tc_supported(c, d1, d2), one_sm = !two_sm && respair_tc_supported(c, d1, d2);   // the order hifigan.cu uses
+    MASG_CHECK(one_sm || two_sm, "masg_respair: unsupported pair C=%d k=%d dilation=%d", C, k, dilation);
     auto run = [&](const bf16* xi, bf16* yo, const bf16* ai) {
         if (one_sm) launch_respair_tc(c, s, d1, d2, xi, B, T, yo, ai, out_scale, post_slope);
         else launch_respair2_tc(c, s, d1, d2, xi, B, T, yo, ai, out_scale, post_slope);
@@ -574,14 +574,14 @@ int masg_respair(masg_ctx* c, void* stream, const float* x, const float* acc, in
     if (ms_out) *ms_out = ms / reps;
     if (getenv("MASG_TC_DEBUG") && (atoi(getenv("MASG_TC_DEBUG")) & 32)) {
         static long long tr[5 * 96 * 4];
-        const int nt = respair_debug_trace(tr, 5 * 96 * 4);
+        const int nt = one_sm ? respair_debug_trace(tr, 5 * 96 * 4) : respair2_debug_trace(tr, 5 * 96 * 4);
         auto at = [&](int role, int it, int e) { return tr[(role * nt + it) * 4 + e]; };
         const int i0 = 40, i1 = 52;
         const long long base = at(0, i0, 0);
         fprintf(stderr, "  [respair trace, CTA 0, cycles] tile | copy: wait-begin slot-free issued | worker: landed done | issuer: P1-ready P1-committed P2-ready P2-committed | E1: acc1-full h-written | E2: requested acc2-full stored\n");
         for (int it = i0; it < i1; ++it) {
             fprintf(stderr, "   %3d |", it);
-            const int ne[5] = {3, 2, 4, 2, 3};
+            const int ne[5] = {3, 2, 4, one_sm ? 2 : 4, 3};
             for (int role = 0; role < 5; ++role) {
                 for (int e = 0; e < ne[role]; ++e) fprintf(stderr, " %7lld", at(role, it, e) ? at(role, it, e) - base : -1LL);
                 fprintf(stderr, " |");

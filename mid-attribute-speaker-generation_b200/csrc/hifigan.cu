@@ -141,12 +141,13 @@ static void hifigan_forward_bf16(masg_ctx* c, cudaStream_t s, const float* melT,
                 const bf16* acc = (last && j > 0) ? xs : nullptr;
                 const float scale = (last && j == 2) ? (1.0f / 3.0f) : 1.f;
                 const float post = (last && j == 2) ? (i < 3 ? 0.1f : 0.01f) : 1.f;
-                if (respair_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
+                if (respair2_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
+                    // both convs in one kernel on a CTA pair, the weights' columns split over the two SMs (respair2_tc.cu): the pairs
+                    // whose weights do not fit one SM (C = 128 k = 3, C = 64 k = 11) or leave it too few buffers (C = 64 k = 7)
+                    launch_respair2_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
+                } else if (respair_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
                     // narrow stages: both convs in one kernel, h stays in shared memory (respair_tc.cu)
                     launch_respair_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
-                } else if (respair2_tc_supported(c, c->hg_c1[rb][m], c->hg_c2[rb][m])) {
-                    // pairs whose weights need two SMs: the same fusion on a CTA pair (respair2_tc.cu)
-                    launch_respair2_tc(c, s, c->hg_c1[rb][m], c->hg_c2[rb][m], y, B, (int)So, yn, acc, scale, post);
                 } else {
                     convP(c, s, c->hg_c1[rb][m], y, true, B, So, h, So, ACT_LRELU, ACT_LRELU, nullptr, nullptr, 1.f, 1.f, (int)So);
                     convP(c, s, c->hg_c2[rb][m], h, true, B, So, yn, So, ACT_NONE, ACT_NONE, y, acc, scale, post, (int)So);

@@ -20,7 +20,8 @@
 // r_out = 128 MS - (k - 1) output rows.  The cluster walks PAIRS of consecutive tiles: rank r of cluster c takes tile
 // 2 (c + it * n_clusters) + r; an odd tile count leaves the last peer tile empty (its MMAs run on whatever the slot holds, nothing
 // is loaded or stored).
-// Roles per CTA (768 threads): 8 E1 + 8 E2 epilogue warps, MS issuer warps (leader only), 2 copy warps, 4 leaky-relu workers.
+// Roles per CTA (768 threads): 8 E1 warps (which also issue the bulk copies of the x tiles), 8 E2 warps, 2 issuer warps (leader
+// only), 6 leaky-relu worker warps.
 #include "common.cuh"
 #include "tc.cuh"
 #include "tc_ptx.cuh"
@@ -30,9 +31,8 @@ using namespace tcptx;
 
 constexpr int R2_EPI_WARPS = 8;             // warps 0-7: E1, warps 8-15: E2 (warp % 4 = TMEM lane quadrant, (warp / 4) % 2 = channel half)
 constexpr int R2_MMA_WARP = 16;             // warps 16, 17: MMA issuers (leader CTA); warp 16 also allocates TMEM in both CTAs
-constexpr int R2_COPY_WARP = 18;            // warps 18, 19: copy warps (even / odd tiles of the CTA)
-constexpr int R2_WORK_WARP0 = 20;           // warps 20-23: leaky-relu workers
-constexpr int R2_WORK_WARPS = 4;
+constexpr int R2_WORK_WARP0 = 18;           // warps 18-23: leaky-relu workers
+constexpr int R2_WORK_WARPS = 6;
 constexpr int R2_WORK_THREADS = R2_WORK_WARPS * 32;
 constexpr int R2_THREADS = (R2_WORK_WARP0 + R2_WORK_WARPS) * 32;     // 768
 constexpr int R2_HDR = 2048;                // barriers [0, 256) | TMEM slot 256 | biases b1[C] | b2[C] from 512
@@ -44,8 +44,15 @@ struct Rp2Args {
     const bf16* W1; const bf16* W2; const float* b1; const float* b2;     // W1 / W2: [2 halves][K][C/8][C/2][8]
     int B, T, dil, tiles_per_b, total_tiles, n_pairs, Rx, r_out, p1, p2;
     float slope, out_scale, post_slope;
-    int res_pf;
+    int res_pf, dbg;
 };
+
+// MASG_TC_DEBUG & 32: timeline of the leader CTA of cluster 0 (clock64 at the hand-over points of its first R2_TRACE_TILES tiles).
+// roles: 0 unused | 1 worker 0 (loads converted, stored) | 2 issuer 0 (P1 ready, P1 issued, P2 ready,
+// P2 issued) | 3 E1 warp 0 (acc1 full, drained, h free, h written) | 4 E2 warp 0 (residuals requested, acc2 full, stored)
+constexpr int R2_TRACE_TILES = 96, R2_TRACE_EVTS = 4, R2_TRACE_ROLES = 5;
+__device__ long long g_rp2_trace[R2_TRACE_ROLES * R2_TRACE_TILES * R2_TRACE_EVTS];
+#define R2_TRACE(on, role, it, evt) do { if ((on) && (it) < R2_TRACE_TILES) g_rp2_trace[((role) * R2_TRACE_TILES + (it)) * R2_TRACE_EVTS + (evt)] = clock64(); } while (0)
 
 struct Rp2Bars {
     uint32_t base;
@@ -68,8 +75,12 @@ __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile
 __device__ __forceinline__ uint32_t map_to_rank(uint32_t addr, uint32_t rank) {
     uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
 }
+// Remote arrivals and the leader's waits use the default (CTA-scope release / acquire) forms, as CUTLASS's ClusterBarrier does:
+// what they order is this CTA's own shared-memory stores — already made visible to the async proxy by fence.proxy.async — against
+// MMAs that read THIS CTA's shared memory.  The .release.cluster / .acquire.cluster forms compile to MEMBAR.ALL.GPU + ERRBAR per
+// arrival and CCTL.IVALL (an L1 invalidate) per wait; in the hand-over chains they cost ~2,000 cycles per tile (measured).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t caddr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t caddr) {
     asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
@@ -77,14 +88,14 @@ __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t caddr) {
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {            // local barrier, arrivals from both CTAs
     uint32_t ok = 0;
     while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(bar), "r"(parity), "r"(20000u) : "memory");
     }
 }
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // arrive::one on the barrier at this offset in BOTH CTAs once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void tc_commit2(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
@@ -106,7 +117,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
     constexpr int WBYTES = K * C * NHALF * 2;               // one conv's half
     constexpr int HROWS = MS * 128 + 16;                    // rows of h + the (k - 1) rows the last sub-tile's taps reach past them
     constexpr int HBYTES = CG * HROWS * 16;
-    constexpr int NI = MS;                                  // issuers: issuer w owns sub-tile w of both convs
+    constexpr int NI = MS;                                  // commits per multicast barrier: MS = 2 both issuers (one sub-tile each), MS = 1 the one issuer of that conv
     static_assert(4 * MS * C == 512, "TMEM: acc1[2][MS][C] | acc2[2][MS][C] must be the 512 columns");
     static_assert(XS <= R2_MAX_XS && NH <= 2 && 512 + 2 * C * 4 <= R2_HDR, "header layout");
     const Rp2Bars bars{smem_u32(smem)};
@@ -122,10 +133,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
     const int cid = (int)blockIdx.x >> 1, n_clusters = (int)gridDim.x >> 1;
+    const bool trace = (a.dbg & 32) && (int)blockIdx.x == ((a.dbg >> 8) & 0xff);   // MASG_TC_DEBUG = 32 + 256 n: trace CTA n
     const int n_my = a.n_pairs > cid ? (a.n_pairs - cid + n_clusters - 1) / n_clusters : 0;    // tile pairs of this cluster: the same in both CTAs
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < XS; ++i) { mbar_init(bars.x_raw(i), 1); mbar_init(bars.x_full(i), 2 * R2_WORK_WARPS); mbar_init(bars.x_empty(i), NI); }
+        for (int i = 0; i < XS; ++i) { mbar_init(bars.x_raw(i), R2_EPI_WARPS); mbar_init(bars.x_full(i), 2 * R2_WORK_WARPS); mbar_init(bars.x_empty(i), NI); }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bars.acc1_full(i), NI); mbar_init(bars.acc1_empty(i), 2 * R2_EPI_WARPS);
             mbar_init(bars.h_full(i), 2 * R2_EPI_WARPS); mbar_init(bars.h_empty(i), NI);
@@ -144,77 +156,54 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
     cluster_sync_all();                                     // both CTAs' barriers are initialised before anyone arrives remotely
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if (warp == R2_COPY_WARP && lane == 0) {                // this CTA's half of both weight sets, resident for the life of the CTA
+    if (warp == R2_WORK_WARP0 && lane == 0) {               // this CTA's half of both weight sets, resident for the life of the CTA
         mbar_expect_tx(bars.w_ready(), 2u * WBYTES);
         bulk_g2s(smem_u32(W1s), reinterpret_cast<const uint8_t*>(a.W1) + (size_t)rank * WBYTES, WBYTES, bars.w_ready());
         bulk_g2s(smem_u32(W2s), reinterpret_cast<const uint8_t*>(a.W2) + (size_t)rank * WBYTES, WBYTES, bars.w_ready());
     }
 
     if (warp >= R2_WORK_WARP0) {
-        // ===== workers: leaky-relu in place on the landed x tile; one remote arrival per warp on the leader's barrier =====
+        // ===== workers: leaky-relu in place on the landed x tile (the raw x is also the residual, so the producer cannot apply it);
+        // one remote arrival per warp on the leader's barrier.
+        // (Loading the tile global -> registers -> leaky-relu -> shared memory instead — one shared-memory pass where copy + in-place
+        // pass + operand read cost three — was tried: the loads of a tile can only be issued once the previous tile's registers are
+        // free, their latency under load (~5,000 cycles from DRAM, still > 2,000 with the rows prefetched into L2) then sits in every
+        // tile period: C = 128 k = 3 0.41 -> 0.49 ms.  The bulk copies run XS tiles ahead for free.) =====
         const int tid = threadIdx.x - R2_WORK_WARP0 * 32;
         const int pieces = x_bytes >> 4;
         const Slope2 sl = make_slope2(a.slope);
         for (int it = 0; it < n_my; ++it) {
             const int slot = it % XS, u = it / XS;
             mbar_wait_relaxed(bars.x_raw(slot), u & 1);
+            R2_TRACE(trace && tid == 0, 1, it, 0);
             uint4* p = reinterpret_cast<uint4*>(Xs + (size_t)slot * x_bytes);
-            for (int i = tid; i < pieces; i += R2_WORK_THREADS) {
-                uint4 v = p[i];
-                v.x = lrelu_bf16x2(v.x, sl); v.y = lrelu_bf16x2(v.y, sl); v.z = lrelu_bf16x2(v.z, sl); v.w = lrelu_bf16x2(v.w, sl);
-                p[i] = v;
+            // six pieces per thread in flight: the slot cycle (copy -> leaky-relu -> conv 1) is part of what sets the tile period
+            for (int i = tid; i < pieces; i += 6 * R2_WORK_THREADS) {
+                uint4 v[6];
+#pragma unroll
+                for (int e = 0; e < 6; ++e) if (i + e * R2_WORK_THREADS < pieces) v[e] = p[i + e * R2_WORK_THREADS];
+#pragma unroll
+                for (int e = 0; e < 6; ++e) {
+                    v[e].x = lrelu_bf16x2(v[e].x, sl); v[e].y = lrelu_bf16x2(v[e].y, sl); v[e].z = lrelu_bf16x2(v[e].z, sl); v[e].w = lrelu_bf16x2(v[e].w, sl);
+                }
+#pragma unroll
+                for (int e = 0; e < 6; ++e) if (i + e * R2_WORK_THREADS < pieces) p[i + e * R2_WORK_THREADS] = v[e];
             }
             fence_proxy_async_all();                        // generic-proxy stores -> visible to the tensor cores (async proxy)
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(map_to_rank(bars.x_full(slot), 0));
-        }
-    } else if (warp == R2_COPY_WARP || warp == R2_COPY_WARP + 1) {
-        // ===== copy warps: one contiguous run per 8-channel group per tile (planar bf16 [B][C/8][T][8]) =====
-        const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
-        for (int it = warp - R2_COPY_WARP; it < n_my; it += 2) {
-            const int tile = 2 * (cid + it * n_clusters) + (int)rank;
-            const bool valid = tile < a.total_tiles;
-            const int slot = it % XS, u = it / XS;
-            const int b = tile / a.tiles_per_b, i = tile - b * a.tiles_per_b;
-            if (lane == 0) mbar_wait_relaxed(bars.x_empty(slot), (u & 1) ^ 1);
-            __syncwarp();
-            uint8_t* dst_g = Xs + (size_t)slot * x_bytes;
-            const uint32_t dst = smem_u32(dst_g), bar = bars.x_raw(slot);
-            const int t0 = i * a.r_out - a.p2 - a.p1;
-            const int lo = max(t0, 0), hi = valid ? max(min(t0 + a.Rx, a.T), lo) : lo;
-            const uint32_t run = (uint32_t)(hi - lo) * 16u;
-            if (valid && (lo > t0 || hi < t0 + a.Rx)) {      // conv zero padding at the utterance edges
-                for (int g = lane; g < CG; g += 32) {
-                    uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)g * a.Rx * 16);
-                    for (int r = 0; r < min(lo - t0, a.Rx); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
-                    for (int r = max(hi - t0, 0); r < a.Rx; ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
-                }
-                fence_proxy_async_all();
-                __syncwarp();
-            }
-            if (lane == 0) {
-                if (run) mbar_expect_tx(bar, run * (uint32_t)CG); else mbar_arrive(bar);
-            }
-            __syncwarp();
-            if (run) {
-                for (int g = lane; g < CG; g += 32) {
-                    const uint8_t* src = X8 + (((size_t)b * CG + g) * a.T + lo) * 16;
-                    bulk_g2s(dst + (uint32_t)((g * a.Rx + (lo - t0)) * 16), src, run, bar);
-                }
-            }
-            if (valid && a.R2 != nullptr && a.res_pf) {
-                // MRF accumulator rows of this tile -> L2 ahead of the E2 warps (DRAM loads queue behind the copies)
-                const int q0 = i * a.r_out, rows = min(a.r_out, a.T - q0);
-                if (rows > 0) for (int g = lane; g < CG; g += 32) bulk_prefetch_l2(a.R2 + (((size_t)b * CG + g) * a.T + q0) * 8, (uint32_t)rows * 16u);
-            }
+            R2_TRACE(trace && tid == 0, 1, it, 1);
         }
     } else if (warp >= R2_MMA_WARP && warp < R2_MMA_WARP + 2) {
         const uint32_t w = (uint32_t)(warp - R2_MMA_WARP);
         if (!leader) {
             // peer: tell the leader when this CTA's weight halves have landed; the leader's threads issue every MMA of the pair
             if (w == 0 && lane == 0) { mbar_wait(bars.w_ready(), 0); mbar_arrive_cluster(map_to_rank(bars.w_peer(), 0)); }
-        } else if ((int)w < NI) {
-            // ===== MMA issuers (leader CTA): issuer w owns sub-tile w (rows [128 w, 128 w + 128) of each CTA's tile) of both convs =====
+        } else {
+            // ===== MMA issuers (leader CTA).  MS = 2: issuer w owns sub-tile w (rows [128 w, 128 w + 128) of each CTA's tile) of both
+            // convs.  MS = 1: issuer 0 issues every conv 1, issuer 1 every conv 2 — one thread sustains ~54 cycles per MMA, so a single
+            // issuer would spend 2,600 of the ~3,100 cycles the pair's MMAs take just issuing, and, issuing in order, would hold conv 2
+            // (it) behind its wait for the x tile of conv 1 (it + 1) and vice versa =====
             // instruction descriptor: D fp32, A / B bf16, K-major, N = C, M = 256 (128 rows from each CTA of the pair)
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(C >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
             const uint32_t desc_hi = (128u >> 4) | (1u << 14);                  // SBO = 128 B, descriptor version 1
@@ -222,6 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             const uint32_t xs16 = smem_u32(Xs) >> 4, hs16 = smem_u32(Hs) >> 4, x16 = (uint32_t)x_bytes >> 4;
             // B: this CTA's C/2 columns, 8-channel groups C/2 rows apart; the peer's half is read at the same offsets of its memory
             const uint32_t w1_lo = ((uint32_t)NHALF << 16) | (smem_u32(W1s) >> 4), w2_lo = ((uint32_t)NHALF << 16) | (smem_u32(W2s) >> 4);
+            const uint32_t sub = MS == 2 ? w : 0u;
             mbar_wait(bars.w_ready(), 0);
             mbar_wait_cluster(bars.w_peer(), 0);
             auto P1 = [&](int it) {
@@ -229,9 +219,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                 mbar_wait_cluster(bars.x_full(slot), u & 1);
                 mbar_wait_cluster(bars.acc1_empty(b), (ub & 1) ^ 1);
                 tc_fence_after();
+                R2_TRACE(trace && sub == 0 && lane == 0, 2, it, 0);
                 if (elect_one()) {
-                    const uint32_t a0 = (lbo_x << 16) | (xs16 + (uint32_t)slot * x16 + w * 128u);
-                    const uint32_t d = tmem_base + (uint32_t)((b * MS) * C) + w * (uint32_t)C;
+                    const uint32_t a0 = (lbo_x << 16) | (xs16 + (uint32_t)slot * x16 + sub * 128u);
+                    const uint32_t d = tmem_base + (uint32_t)((b * MS) * C) + sub * (uint32_t)C;
 #pragma unroll
                     for (int j = 0; j < K; ++j) {
 #pragma unroll
@@ -242,6 +233,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                     tc_commit2(bars.acc1_full(b));
                 }
                 __syncwarp();
+                R2_TRACE(trace && sub == 0 && lane == 0, 2, it, 1);
             };
             auto P2 = [&](int it) {
                 const int b = it & 1, ub = it >> 1;
@@ -249,9 +241,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                 mbar_wait_cluster(bars.h_full(hbuf), hu & 1);
                 mbar_wait_cluster(bars.acc2_empty(b), (ub & 1) ^ 1);
                 tc_fence_after();
+                R2_TRACE(trace && sub == 0 && lane == 0, 2, it, 2);
                 if (elect_one()) {
-                    const uint32_t a0 = ((uint32_t)HROWS << 16) | (hs16 + (uint32_t)hbuf * (uint32_t)(HBYTES >> 4) + w * 128u);
-                    const uint32_t d = tmem_base + (uint32_t)(2 * MS * C + (b * MS) * C) + w * (uint32_t)C;
+                    const uint32_t a0 = ((uint32_t)HROWS << 16) | (hs16 + (uint32_t)hbuf * (uint32_t)(HBYTES >> 4) + sub * 128u);
+                    const uint32_t d = tmem_base + (uint32_t)(2 * MS * C + (b * MS) * C) + sub * (uint32_t)C;
 #pragma unroll
                     for (int j = 0; j < K; ++j) {
 #pragma unroll
@@ -262,11 +255,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                     tc_commit2(bars.acc2_full(b));
                 }
                 __syncwarp();
+                R2_TRACE(trace && sub == 0 && lane == 0, 2, it, 3);
             };
-            if (n_my > 0) P1(0);
-            for (int it = 0; it < n_my; ++it) {
-                if (it + 1 < n_my) P1(it + 1);
-                P2(it);
+            if (MS == 2) {
+                if (n_my > 0) P1(0);
+                for (int it = 0; it < n_my; ++it) {
+                    if (it + 1 < n_my) P1(it + 1);
+                    P2(it);
+                }
+            } else if (w == 0) {
+                for (int it = 0; it < n_my; ++it) P1(it);
+            } else {
+                for (int it = 0; it < n_my; ++it) P2(it);
             }
         }
     } else if (warp < R2_EPI_WARPS) {
@@ -275,6 +275,51 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
         constexpr int CH = C / 2;                            // channels per warp (this half)
         const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         const Slope2 sl = make_slope2(a.slope);
+        // ---- x tile copies: E1 warp w moves the GW 8-channel groups [w GW, (w + 1) GW) of every tile, one contiguous run per group
+        // (planar bf16 [B][C/8][T][8]).  A cp.async.bulk costs its issuing warp ~350 cycles, whichever lane it comes from (2,600-3,400
+        // cycles for a tile's 8 / 16 runs from one or two dedicated copy warps, all of it in the slot cycle), so the runs are spread
+        // over these 8 warps; the copy of tile it + XS goes out when acc1 (it) is full: conv 1 (it) has then read the slot.
+        constexpr int GW = CG / R2_EPI_WARPS;
+        const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
+        auto issue_copy = [&](int itc) {
+            const int tile = 2 * (cid + itc * n_clusters) + (int)rank;
+            const bool valid = tile < a.total_tiles;
+            const int slot = itc % XS;
+            const int bb = tile / a.tiles_per_b, i = tile - bb * a.tiles_per_b;
+            uint8_t* dst_g = Xs + (size_t)slot * x_bytes;
+            const uint32_t dst = smem_u32(dst_g), bar = bars.x_raw(slot);
+            const int t0 = i * a.r_out - a.p2 - a.p1;
+            const int lo = max(t0, 0), hi = valid ? max(min(t0 + a.Rx, a.T), lo) : lo;
+            const uint32_t run = (uint32_t)(hi - lo) * 16u;
+            const int g0 = warp * GW;
+            if (valid && (lo > t0 || hi < t0 + a.Rx)) {      // conv zero padding at the utterance edges
+                const int nlo = min(lo - t0, a.Rx), nhi0 = max(hi - t0, 0);
+                for (int j = 0; j < GW; ++j) {
+                    uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)(g0 + j) * a.Rx * 16);
+                    for (int r = lane; r < nlo; r += 32) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                    for (int r = nhi0 + lane; r < a.Rx; r += 32) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                }
+                fence_proxy_async_all();
+                __syncwarp();
+            }
+            if (lane == 0) {
+                if (run) {
+                    mbar_expect_tx(bar, run * (uint32_t)GW);
+                    const uint8_t* src = X8 + (((size_t)bb * CG + g0) * a.T + lo) * 16;
+                    const uint32_t d0 = dst + (uint32_t)((g0 * a.Rx + (lo - t0)) * 16);
+#pragma unroll
+                    for (int j = 0; j < GW; ++j) bulk_g2s(d0 + (uint32_t)(j * a.Rx * 16), src + (size_t)j * a.T * 16, run, bar);
+                } else mbar_arrive(bar);
+                if (valid && a.R2 != nullptr && a.res_pf) {
+                    // MRF accumulator rows of this tile -> L2 ahead of the E2 warps (DRAM loads queue behind the copies)
+                    const int q0 = i * a.r_out, rows = min(a.r_out, a.T - q0);
+                    if (rows > 0)
+                        for (int j = 0; j < GW; ++j) bulk_prefetch_l2(a.R2 + (((size_t)bb * CG + g0 + j) * a.T + q0) * 8, (uint32_t)rows * 16u);
+                }
+            }
+            __syncwarp();
+        };
+        for (int itc = 0; itc < XS && itc < n_my; ++itc) issue_copy(itc);
         for (int it = 0; it < n_my; ++it) {
             const int tile = 2 * (cid + it * n_clusters) + (int)rank;
             const int b = it & 1, ub = it >> 1;
@@ -287,6 +332,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             // leaky-relu out of it (acc1 (it) has been full since before conv 2 (it - 1) was issued)
             mbar_wait_relaxed(bars.acc1_full(b), ub & 1);
             tc_fence_after();
+            R2_TRACE(trace && threadIdx.x == 0, 3, it, 0);
+            if (it + XS < n_my) {                            // the slot conv 1 (it) read is free: start the copy of tile it + XS
+                mbar_wait_relaxed(bars.x_empty(it % XS), (it / XS) & 1);
+                issue_copy(it + XS);
+                R2_TRACE(trace && threadIdx.x == 0, 0, it + XS, 2);
+            }
             uint4 pk[MS][CH / 8];
             constexpr int NLD = MS == 2 ? CH / 16 : CH / 32;   // two 16-column loads in flight per wait: (ms 0, ms 1) or (cg, cg + 1)
 #pragma unroll
@@ -317,7 +368,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster_relaxed(map_to_rank(bars.acc1_empty(b), 0));   // orders only the TMEM reads above
+            R2_TRACE(trace && threadIdx.x == 0, 3, it, 1);
             mbar_wait_relaxed(bars.h_empty(hbuf), (hu & 1) ^ 1);
+            R2_TRACE(trace && threadIdx.x == 0, 3, it, 2);
             uint8_t* hb = Hs + (size_t)hbuf * HBYTES;
 #pragma unroll
             for (int ms = 0; ms < MS; ++ms) {
@@ -329,6 +382,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             fence_proxy_async_all();                        // h stores -> visible to the tensor cores
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(map_to_rank(bars.h_full(hbuf), 0));
+            R2_TRACE(trace && threadIdx.x == 0, 3, it, 3);
         }
     } else if (warp < 2 * R2_EPI_WARPS) {
         // ===== E2 warps: acc2 (TMEM) -> + b2 + x [+ acc] -> scale -> trailing leaky-relu -> planar bf16 y =====
@@ -338,6 +392,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
         const long gstride = (long)a.T * 8;                  // elements between 8-channel groups
         const bool has_r2 = a.R2 != nullptr;
         const Slope2 sl_post = make_slope2(a.post_slope);
+        // (Two groups of four warps on alternate tiles, each warp covering all channels of its quadrant in two passes, was tried when
+        // this pass looked like the limiter — 4,400 cycles per tile, never waiting: no change; the kernel is bound by shared-memory
+        // bandwidth, see the header.)
         for (int it = 0; it < n_my; ++it) {
             const int tile = 2 * (cid + it * n_clusters) + (int)rank;
             const bool valid = tile < a.total_tiles;
@@ -345,7 +402,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             const int bb = tile / a.tiles_per_b, i = tile - bb * a.tiles_per_b;
             const int q0 = i * a.r_out;
             const long boff = ((long)bb * CG + hf * (CH / 8)) * gstride;
-            // the residual rows (x again: L2 hits, the copy warp read them a few tiles ago) are requested before the accumulator is waited for
+            // the residual rows (x again: L2 hits, the copy read them a few tiles ago) are requested before the accumulator is waited for
             uint4 rx[MS][CH / 8];
             bool ok[MS];
 #pragma unroll
@@ -356,8 +413,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                 for (int g = 0; g < CH / 8; ++g)
                     rx[ms][g] = ok[ms] ? *reinterpret_cast<const uint4*>(a.X + boff + (long)g * gstride + (long)t * 8) : make_uint4(0u, 0u, 0u, 0u);
             }
+            R2_TRACE(trace && threadIdx.x == R2_EPI_WARPS * 32, 4, it, 0);
             mbar_wait_relaxed(bars.acc2_full(b), ub & 1);
             tc_fence_after();
+            R2_TRACE(trace && threadIdx.x == R2_EPI_WARPS * 32, 4, it, 1);
 #pragma unroll
             for (int ms = 0; ms < MS; ++ms) {
                 const int t = q0 + ms * 128 + quad * 32 + lane;
@@ -403,6 +462,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster_relaxed(map_to_rank(bars.acc2_empty(b), 0));   // orders only the TMEM reads above, not the global stores
+            R2_TRACE(trace && threadIdx.x == R2_EPI_WARPS * 32, 4, it, 2);
         }
     }
     tc_fence_before();
@@ -418,6 +478,11 @@ struct Rp2Config { int ms, xs, nh; };
 bool rp2_config(int C, int K, Rp2Config& cf) {
     if (C == 128 && K == 3) { cf = {1, 2, 1}; return true; }
     if (C == 64 && K == 11) { cf = {2, 2, 1}; return true; }
+    if (C == 64 && K == 7) {                                // fits one SM too (respair_tc.cu, 2 slots + 1 h buffer); here 2 + 2.  MASG_RP2_K7=0: off
+        static int on = -1;
+        if (on < 0) { const char* e = getenv("MASG_RP2_K7"); on = e ? atoi(e) : 1; }
+        if (on) { cf = {2, 2, 2}; return true; }
+    }
     return false;
 }
 int rp2_rx(int ms, const ConvDesc& d1) { return (ms * 128 + (d1.taps - 1) * d1.tstep + 7) & ~7; }
@@ -433,6 +498,13 @@ void launch_rp2(const Rp2Args& a, dim3 grid, size_t smem, cudaStream_t s) {
 }
 
 }  // namespace
+
+int respair2_debug_trace(long long* out, int max_elems) {
+    const int n = R2_TRACE_ROLES * R2_TRACE_TILES * R2_TRACE_EVTS;
+    if (max_elems < n) return -1;
+    CUDA_OK(cudaMemcpyFromSymbol(out, g_rp2_trace, sizeof(long long) * n));
+    return R2_TRACE_TILES;
+}
 
 bool respair2_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc& d2) {
     static int off = -1;
@@ -465,6 +537,7 @@ void launch_respair2_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const C
     a.tiles_per_b = (T + a.r_out - 1) / a.r_out; a.total_tiles = B * a.tiles_per_b; a.n_pairs = (a.total_tiles + 1) / 2;
     a.slope = 0.1f; a.out_scale = out_scale; a.post_slope = post_slope;
     { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
+    { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
     const dim3 grid(2 * std::min(a.n_pairs, c->n_sm / 2), 1, 1);           // one CTA pair per TPC, persistent
     const size_t smem = rp2_smem(C, K, a.Rx, cf);
     masg_ctx::ProfRec rec;
@@ -475,6 +548,7 @@ void launch_respair2_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const C
     }
     if (C == 128 && K == 3) launch_rp2<128, 3, 1, 2, 1>(a, grid, smem, s);
     else if (C == 64 && K == 11) launch_rp2<64, 11, 2, 2, 1>(a, grid, smem, s);
+    else if (C == 64 && K == 7) launch_rp2<64, 7, 2, 2, 2>(a, grid, smem, s);
     CUDA_OK(cudaGetLastError());
     c->launches++;
     if (c->profiling) { CUDA_OK(cudaEventRecord(rec.e1, s)); c->prof.push_back(rec); }

@@ -25,3 +25,4 @@ int respair_debug_trace(long long* out, int max_elems);      // MASG_TC_DEBUG & 
 bool respair2_tc_supported(const masg_ctx* c, const ConvDesc& d1, const ConvDesc& d2);
 void launch_respair2_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const ConvDesc& d2, const bf16* X, int B, int T,
                         bf16* Y, const bf16* R2, float out_scale, float post_slope);
+int respair2_debug_trace(long long* out, int max_elems);     // MASG_TC_DEBUG & 32: the same timeline for the leader CTA of cluster 0
