@@ -577,7 +577,7 @@ def run_ours(args):
         "gather": ({"collective": "NCCL all_gather of every rank's int16 audio (padded-to-max exchange + counts), side stream, overlapped with the next step",
                     "bytes_per_rank_per_step": B * 3 * L * syn.HOP * 2} if gather_was_on else None),
         "clocks": clk,
-        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc (tcgen05 implicit-GEMM conv1d / linear / convT and the fused ResBlock pairs)", "achieved": ach, "peak": pk["tflops"],
+        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc + k_respair2_tc (tcgen05 implicit-GEMM conv1d / linear / convT and the fused ResBlock pairs, one-SM and CTA-pair)", "achieved": ach, "peak": pk["tflops"],
                      "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
                      "traffic_source": traffic_src, "peak_source": pk["src"],
                      "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": step_ms_plain,
@@ -724,7 +724,7 @@ def run_sharded(args):
         "e2e": {"value": job_audio * args.steps / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": ms_e2e / args.steps, "note": "rank 0's bytes; one masg_synthesize_host call per batch"},
         "gpu_launches": int(launches), "clocks": clk,
-        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
+        "roofline": {"bound": "tensor", "kernel": "k_conv_tc + k_respair_tc + k_respair2_tc", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
                      "traffic": None, "peak_source": pk["src"], "launches_per_step": k_n, "kernel_ms_per_step": k_ms, "step_ms": pass_ms,
                      "share_of_step": k_ms / pass_ms if pass_ms else None,
                      "how": "per-launch CUDA events over one extra pass of rank 0's share; FLOPs counted over the padded rows each launch processes"},

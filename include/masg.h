@@ -199,7 +199,8 @@ int masg_synthesize_host_wait(masg_ctx* ctx, int ticket);
  * activations in bf16 in HBM as the HiFi-GAN path does (x is converted before, y after the timed launches);
  * 4 = add x as residual (Cin == Cout), as ResBlock.forward does (hifigan/models.py:102); 8 = single-pass fp16 operands (the
  * FastSpeech2 decoder side); 16 = with 2 | 4: the residual is read from its own copy of x (DRAM reads, as in the generator,
- * where the residual is not the conv's input).  The launch is repeated `reps`
+ * where the residual is not the conv's input); 32 / 64 = with 2: run the CTA-pair form of the kernel (clusters of two CTAs, tcgen05
+ * cta_group::2; N = 128 column tiles only) whatever the size / never (default: for launches of at least two tiles per SM).  The launch is repeated `reps`
  * times between CUDA events on `stream`; *h_ms (nullable) receives the mean milliseconds per launch. */
 int masg_conv1d(masg_ctx* ctx, void* stream, const float* x, int B, int T, int Cin, const float* w, const float* bias,
                 int Cout, int k, int dilation, int stride_transposed, float in_lrelu_slope, int out_act, int flags,

@@ -504,6 +504,7 @@ int masg_conv1d(masg_ctx* c, void* stream, const float* x, int B, int T, int Cin
         io.R1 = r16;
     }
     if (in_lrelu_slope != 0.f) { io.in_act = ACT_LRELU; io.in_slope = in_lrelu_slope; }
+    io.pair_mode = (flags & 32) ? 1 : ((flags & 64) ? -1 : 0);
     launch_conv(c, s, d, io);                                  // warm-up / result
     cudaEvent_t e0, e1; CUDA_OK(cudaEventCreate(&e0)); CUDA_OK(cudaEventCreate(&e1));
     CUDA_OK(cudaEventRecord(e0, s));

@@ -60,6 +60,8 @@ struct ConvDesc {
     // third tiling, for the fused ResBlock pair on a CTA pair (respair2_tc.cu): the columns split in two halves of N/2, each
     // [tap][Cin/8][N/2][8] — one half per CTA of the cluster (tcgen05 cta_group::2 B operand)
     const bf16* w16p = nullptr;
+    // the commit-time tiling at NT / 2 columns per blob set, for the pair mode of k_conv_tc (NT = 128 layers)
+    const bf16* w16h = nullptr;
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc
@@ -150,6 +152,7 @@ struct ConvIO {
     // fused LayerNorm epilogue (tcgen05 path, N == 256 == one tile row): Y = mask(LN(act(acc + bias) + R1) * ln_g + ln_b), rows with
     // t >= ln_lens[b] written as zeros (Layers.py:25,28); Y16p (nullable) = the same as planar fp16 [B][32][ln_T][8]
     const float* ln_g = nullptr; const float* ln_b = nullptr; const int64_t* ln_lens = nullptr; int ln_T = 0; bf16* Y16p = nullptr;
+    int pair_mode = 0;                                                       // tcgen05 path: 1 = CTA-pair kernel whatever the size (tests), -1 = never, 0 = by size
 };
 void launch_conv_f32(masg_ctx* c, cudaStream_t s, const ConvDesc& d, const ConvIO& io);
 // precision dispatch: MASG_PREC_FP32 → conv_simt.cu, MASG_PREC_BF16 → conv_tc.cu (tcgen05)

@@ -77,6 +77,7 @@ struct TcArgs {
     int f16;                                           // operands are fp16 (single pass, 11-bit mantissa) instead of bf16
     int a_lbo16, a_ms16, a_tx, a_blk_bytes;            // operand strides in 16-byte units; TMA bytes per chunk; bytes per ms block
     int B, row_tiles, n_ntiles, total_tiles;
+    int total_pairs;                                   // pair mode: tile pairs (two consecutive row blocks x one column tile)
     // output
     float* Y; bf16* Y16; long y_bs; long y_limit; long orow; long ooff; int Q;
     int y_planar, y_T, up, up_pad, cout_shift;         // planar bf16 output [B][Cout/8][y_T][8]; t = q*up + n/Cout - up_pad
@@ -135,7 +136,9 @@ struct Bars {                                            // mbarrier addresses (
     __device__ uint32_t w_empty(int i) const { return base + 8u * (3 * A_SLOTS + W_STAGES + i); }
     __device__ uint32_t acc_full(int i) const { return base + 8u * (3 * A_SLOTS + 2 * W_STAGES + i); }
     __device__ uint32_t acc_empty(int i) const { return base + 8u * (3 * A_SLOTS + 2 * W_STAGES + 2 + i); }
+    __device__ uint32_t w_peer(int i) const { return base + 8u * (3 * A_SLOTS + 2 * W_STAGES + 4 + i); }   // pair mode, leader: the peer's weight stage has landed
 };
+static_assert(8 * (3 * A_SLOTS + 3 * W_STAGES + 4) <= 512, "barrier block overlaps the TMEM slot");
 
 // ---------------------------------------------------------------------------------------------
 // MMA issue loop (one thread).  Everything that changes per MMA is a running 32-bit add on the low descriptor word.
@@ -144,16 +147,18 @@ struct Bars {                                            // mbarrier addresses (
 // the same barrier sequence as the others; every release barrier therefore expects NI commits.  (Measured: one
 // thread sustains ~56 cycles per MMA, the tensor core needs 40 at N=32 and 48 at N=64 — shared-memory operand reads,
 // (4096 + 32 N) bytes at 128 B/clk — so two to four issuers are needed to keep it busy.)
-template <int NT, int MS, int NI, bool SPLIT, int W>
+template <int NT, int MS, int NI, bool SPLIT, int W, bool PAIR>
 __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const uint32_t a_smem, const uint32_t w_smem, const uint32_t tmem_base) {
     constexpr int w = W;                                   // issuer index: compile-time, so every value below is warp-uniform
     constexpr int MSL = MS / NI;
     // instruction descriptor: D fp32, A/B bf16, both K-major, N = NT, M = 128
     const uint32_t ab_fmt = a.f16 ? 0u : ((1u << 7) | (1u << 10));                         // A / B format: 0 = fp16, 1 = bf16
-    const uint32_t idesc = (1u << 4) | ab_fmt | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    // pair mode (cta_group::2): M = 256 = 128 rows from each CTA of the pair; each CTA holds NT / 2 of the tile's weight columns
+    constexpr int NTB = PAIR ? NT / 2 : NT;
+    const uint32_t idesc = (1u << 4) | ab_fmt | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)((PAIR ? 256 : 128) >> 4) << 24);
     const uint32_t desc_hi = (128u >> 4) | (1u << 14);                     // SBO = 128 B, descriptor version 1
-    const uint32_t a_fixed = (uint32_t)a.a_lbo16 << 16, w_fixed = (uint32_t)NT << 16;     // LBO fields (16-byte units)
-    const uint32_t a_ks = 2u * (uint32_t)a.a_lbo16, w_ks = 2u * (uint32_t)NT;              // one K=16 step = two 8-channel groups
+    const uint32_t a_fixed = (uint32_t)a.a_lbo16 << 16, w_fixed = (uint32_t)NTB << 16;    // LBO fields (16-byte units)
+    const uint32_t a_ks = 2u * (uint32_t)a.a_lbo16, w_ks = 2u * (uint32_t)NTB;             // one K=16 step = two 8-channel groups
     const uint32_t a_sub = (uint32_t)(a.KW >> 3) * (uint32_t)a.a_lbo16;
     const uint32_t a_ms = (uint32_t)a.a_ms16;
     const uint32_t blob16 = (uint32_t)a.blob_bytes >> 4, a_half16 = (uint32_t)a.a_half >> 4, w_half16 = blob16 >> 1;
@@ -164,7 +169,10 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
     const bool tr = (a.dbg & 32) && w == 0 && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
     int wslot = 0, aslot = 0, it = 0;
     uint32_t wphase = 0, aphase = 0;
-    for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+    const int w_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, w_stride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int w_total = PAIR ? a.total_pairs : a.total_tiles;
+    auto commit = [](uint32_t bar) { if (PAIR) tc_commit2(bar); else tc_commit(bar); };
+    for (int tile = w_first; tile < w_total; tile += w_stride, ++it) {
         const int accb = it & 1;
         STAT_WAIT(st, 0, mbar_wait(bars.acc_empty(accb), ((it >> 1) & 1) ^ 1));   // epilogue has drained this accumulator set
         tc_fence_after();
@@ -187,10 +195,10 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
                 for (int j = 0; j < a.taps; ++j, a_tap += (uint32_t)a.tstep) {
                     if (g == a.G) {                                        // next weight stage
                         if (have_stage) {
-                            if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));
+                            if (!no_w && elect_one()) commit(bars.w_empty(wslot));
                             if (++wslot == a.w_stages) { wslot = 0; wphase ^= 1; }
                         }
-                        if (!no_w) { STAT_WAIT(st, 2, mbar_wait(bars.w_full(wslot), wphase)); tc_fence_after(); }
+                        if (!no_w) { STAT_WAIT(st, 2, mbar_wait(bars.w_full(wslot), wphase)); if (PAIR) mbar_wait(bars.w_peer(wslot), wphase); tc_fence_after(); }
                         wbase16 = (w_smem + (uint32_t)wslot * (uint32_t)a.stage_bytes) >> 4;
                         g = 0; have_stage = true;
                     }
@@ -202,7 +210,8 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
 #pragma unroll
                             for (int i = 0; i < MSL; ++i) {
                                 const uint32_t d = tacc_w + (uint32_t)(i * NI * NT), al = a_lo + (uint32_t)(i * NI) * a_ms;
-                                tc_mma(d, al, w_lo, desc_hi, idesc, (ks == 0) ? accum : 1u);
+                                if (PAIR) tc_mma2(d, al, w_lo, desc_hi, idesc, (ks == 0) ? accum : 1u);
+                                else tc_mma(d, al, w_lo, desc_hi, idesc, (ks == 0) ? accum : 1u);
                                 if (SPLIT) {
                                     tc_mma(d, al + a_half16, w_lo, desc_hi, idesc, 1u);
                                     tc_mma(d, al, w_lo + w_half16, desc_hi, idesc, 1u);
@@ -214,12 +223,12 @@ __device__ __forceinline__ void mma_role(const TcArgs& a, const Bars bars, const
                     accum = 1u;
                 }
             }
-            if (!no_a && elect_one()) tc_commit(bars.a_empty(aslot));                     // chunk consumed -> slot may be overwritten
+            if (!no_a && elect_one()) commit(bars.a_empty(aslot));                        // chunk consumed -> slot may be overwritten
             if (++aslot == A_SLOTS) { aslot = 0; aphase ^= 1; }
         }
-        if (!no_w && elect_one()) tc_commit(bars.w_empty(wslot));          // the weight stream restarts on a stage boundary per tile
+        if (!no_w && elect_one()) commit(bars.w_empty(wslot));             // the weight stream restarts on a stage boundary per tile
         if (++wslot == a.w_stages) { wslot = 0; wphase ^= 1; }
-        if (elect_one()) tc_commit(bars.acc_full(accb));
+        if (elect_one()) commit(bars.acc_full(accb));
         TRACE(tr, 2, it, 2);
     }
     if (st) atomicAdd(&g_tc_stats[3], (unsigned long long)(clock64() - t_begin));
@@ -533,8 +542,15 @@ __device__ __forceinline__ void epi_layernorm(const TcArgs& a, const uint32_t tr
     }
 }
 
-template <int NT, bool TMA_IN>
+// PAIR: the kernel runs as clusters of two CTAs (launch attribute) whose MMAs are tcgen05 cta_group::2 instructions issued by the
+// leader CTA (M = 256: 128 rows of A from each CTA's own tile; the NT weight columns split over the pair, NT / 2 per CTA) — the
+// scheme of respair2_tc.cu.  A single-CTA N = 128 MMA reads 8 KB of operands per 64 cycles, all of the shared-memory bandwidth, so
+// the weight ring's and the activation copies' writes slow the MMAs down; in pair mode each SM reads 6 KB per MMA and streams half
+// of the weight bytes.  The two CTAs of a cluster take consecutive row blocks of the same column tile.  Barriers the issuers wait
+// on live in the leader and count both CTAs' arrivals; the ones they signal are multicast commits.  Planar input only (TMA_IN).
+template <int NT, bool TMA_IN, bool PAIR = false>
 __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
+    static_assert(!PAIR || TMA_IN, "pair mode takes planar input");
     extern __shared__ __align__(1024) uint8_t smem[];
     // header: mbarriers + TMEM base; then the bias row, the activation slots and the weight ring
     const Bars bars{smem_u32(smem)};
@@ -547,26 +563,41 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     const int n_chunks = a.Cin / a.KC;
     const int n_stages = (a.n_blobs + a.G - 1) / a.G;
     const int acc_cols = a.msub * NT;                      // TMEM columns of one accumulator set (two sets)
-    const bool a_workers = !TMA_IN || a.in_act != ACT_NONE;
+    const bool a_workers = PAIR || !TMA_IN || a.in_act != ACT_NONE;   // pair mode: the workers also forward "tile landed" to the leader
     const bool ln_helpers = NT == 256 && a.ln_g != nullptr && !a_workers && !(a.dbg & 1024);   // idle worker warps join the LayerNorm epilogue
     const int n_issuers = min(a.msub, MMA_WARPS);
+    // work items: tiles, or (pair mode) tile pairs: pair p = (row-block pair p / n_ntiles, column tile p % n_ntiles), rank r takes
+    // row block 2 (p / n_ntiles) + r; an odd row-block count leaves the last peer tile empty (nothing loaded or stored)
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const int w_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, w_stride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int w_total = PAIR ? a.total_pairs : a.total_tiles;
+    auto tile_of = [&](int wi) { return PAIR ? (2 * (wi / a.n_ntiles) + (int)rank) * a.n_ntiles + wi % a.n_ntiles : wi; };
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_SLOTS; ++i) {
-            mbar_init(bars.a_full(i), a_workers ? A_THREADS : 1); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), 1);
+            mbar_init(bars.a_full(i), PAIR ? 2 * A_WARPS : (a_workers ? A_THREADS : 1)); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), 1);
         }
-        for (int i = 0; i < 2; ++i) { mbar_init(bars.acc_full(i), n_issuers); mbar_init(bars.acc_empty(i), ln_helpers ? EPI_WARPS + A_WARPS : EPI_WARPS); }
-        for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), n_issuers); }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bars.acc_full(i), n_issuers);
+            mbar_init(bars.acc_empty(i), PAIR ? 2 * EPI_WARPS : (ln_helpers ? EPI_WARPS + A_WARPS : EPI_WARPS));
+        }
+        for (int i = 0; i < W_STAGES; ++i) { mbar_init(bars.w_full(i), 1); mbar_init(bars.w_empty(i), n_issuers); mbar_init(bars.w_peer(i), 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int i = threadIdx.x; i < a.N; i += NTHREADS) bias_s[i] = a.bias ? a.bias[i % a.bias_mod] : 0.f;
     if (NT == 256 && a.ln_g) for (int i = threadIdx.x; i < 256; i += NTHREADS) { bias_s[256 + i] = a.ln_g[i]; bias_s[512 + i] = a.ln_b[i]; }
     if (warp == MMA_WARP) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(a.tmem_cols) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {                                           // the same warp of both CTAs: the pair's TMEM is allocated together
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(a.tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(a.tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();                           // both CTAs' barriers are initialised before anyone arrives remotely
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     // programmatic dependent launch: everything above touched constants only; the weight warp (constants) and the issuers (shared
@@ -600,13 +631,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     if (lane == 0) mbar_arrive(bars.acc_empty(accb));
                 }
             }
-            // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled =====
-            if (a.in_act != ACT_NONE) {
-                const int pieces = a.a_tx >> 4;
+            // ===== workers, planar input: leaky-relu in place on the slot the TMA unit has filled (pair mode: also without an
+            // activation, to tell the leader CTA that this CTA's tile has landed — one remote arrival per warp) =====
+            if (PAIR || a.in_act != ACT_NONE) {
+                const int pieces = a.in_act != ACT_NONE ? a.a_tx >> 4 : 0;
                 const Slope2 sl = make_slope2(a.in_slope);
                 int slot = 0, it = 0; uint32_t phase = 0;
                 const bool tr = (a.dbg & 32) && blockIdx.x == 0 && tid == 0;
-                for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+                for (int tile = w_first; tile < w_total; tile += w_stride, ++it) {
                     for (int kc = 0; kc < n_chunks; ++kc) {
                         STAT_WAIT((a.dbg & 16) && tid == 0, 8, mbar_wait_relaxed(bars.a_raw(slot), phase));
                         if (kc == 0) TRACE(tr, 1, it, 0);
@@ -618,7 +650,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                             p[i] = v;
                         }
                         fence_proxy_async();                  // generic-proxy stores -> visible to the tensor core (async proxy)
-                        mbar_arrive(bars.a_full(slot));
+                        if (PAIR) { __syncwarp(); if (lane == 0) mbar_arrive_cluster(map_to_rank(bars.a_full(slot), 0)); }
+                        else mbar_arrive(bars.a_full(slot));
                         if (kc == 0) TRACE(tr, 1, it, 1);
                         if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
                     }
@@ -683,7 +716,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             const int cgpc = a.KC >> 3;
             const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
             const bool res_pf = a.res_pf && a.y_planar && a.R1 != nullptr && a.r_bf16 && a.up == 1 && a.up_pad == 0;
-            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+            for (int wi = w_first; wi < w_total; wi += w_stride, ++it) {
+                const int tile = tile_of(wi);
+                const bool valid = !PAIR || tile < a.total_tiles;
                 const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
                 const int q_lo = rt * a.msub * 128 + a.off_lo;
                 for (int kc = 0; kc < n_chunks; ++kc) {
@@ -691,13 +726,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     if (lane == 0) STAT_WAIT(a.dbg & 16, 6, mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1));
                     __syncwarp();
                     if (kc == 0) TRACE(tr, 0, it, 1);
-                    const uint32_t bar = a.in_act != ACT_NONE ? bars.a_raw(slot) : bars.a_full(slot);
+                    const uint32_t bar = (PAIR || a.in_act != ACT_NONE) ? bars.a_raw(slot) : bars.a_full(slot);
                     uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
                     const uint32_t dst = smem_u32(dst_g);
                     // the tile is ONE [KC/8][Rp][8] block (its msub*128 rows + the halo): one contiguous run per 8-channel group
-                    const int t0 = q_lo, lo = max(t0, 0), hi = max(min(t0 + a.Rp, a.Tin), lo);
+                    const int t0 = q_lo, lo = max(t0, 0), hi = valid ? max(min(t0 + a.Rp, a.Tin), lo) : lo;
                     const uint32_t run = (uint32_t)(hi - lo) * 16u;
-                    if (lo > t0 || hi < t0 + a.Rp) {
+                    if (valid && (lo > t0 || hi < t0 + a.Rp)) {
                         for (int g = lane; g < cgpc; g += 32) {
                             uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)g * a.Rp * 16);
                             for (int r = 0; r < min(lo - t0, a.Rp); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
@@ -719,7 +754,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     if (kc == 0) TRACE(tr, 0, it, 2);
                     if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
                 }
-                if (res_pf) {
+                if (res_pf && valid) {
                     // residual rows of this tile -> L2, one run per 8-channel group, a few tiles before the epilogue warps read them.
                     // The activation copies above keep ~100 KB per SM (15 MB chip-wide) queued at the memory controllers, so a
                     // residual load that has to go to DRAM waits 2.5-5 us behind them and the epilogue's two load rounds per tile
@@ -741,10 +776,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         // ===== weight producer: 1-D bulk copies of pre-tiled blobs =====
         if (lane == 0 && !(a.dbg & 1)) {
             int slot = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
-                const int nt = tile % a.n_ntiles;
-                const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)nt * a.n_blobs * a.blob_bytes;
-                if (a.w_resident && tile != (int)blockIdx.x) {       // resident weights: only the hand-shake, no copy
+            for (int wi = w_first; wi < w_total; wi += w_stride) {
+                const int nt = wi % a.n_ntiles;                      // (tile % n_ntiles; in pair mode both CTAs of a pair share the column tile)
+                // pair mode: the blobs are tiled NT / 2 columns wide, column tile nt = blob sets 2 nt (leader) and 2 nt + 1 (peer)
+                const uint8_t* src = reinterpret_cast<const uint8_t*>(a.Wt) + (size_t)(PAIR ? 2 * nt + (int)rank : nt) * a.n_blobs * a.blob_bytes;
+                if (a.w_resident && wi != w_first) {                 // resident weights: only the hand-shake, no copy
                     mbar_wait_relaxed(bars.w_empty(0), phase ^ 1);
                     mbar_arrive(bars.w_full(0));
                     phase ^= 1;
@@ -763,9 +799,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     } else if (warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS) {
         // ===== MMA issuers: one thread per warp; specialised on the number of accumulator sub-tiles =====
         const int w = warp - MMA_WARP;
-        if (w < n_issuers) {
+        if (PAIR && rank != 0) {
+            // peer CTA: the leader issues every MMA of the pair; one thread here tells it when each weight stage of THIS CTA has landed
+            if (w == 0 && lane == 0 && !(a.dbg & 1)) {
+                int slot = 0; uint32_t phase = 0;
+                for (int wi = w_first; wi < w_total; wi += w_stride) {
+                    const int ns = (a.w_resident && wi != w_first) ? 1 : n_stages;     // the weight warp's sequence of w_full phases
+                    for (int st = 0; st < ns; ++st) {
+                        mbar_wait(bars.w_full(slot), phase);
+                        mbar_arrive_cluster(map_to_rank(bars.w_peer(slot), 0));
+                        if (++slot == a.w_stages) { slot = 0; phase ^= 1; }
+                    }
+                }
+            }
+        } else if (w < n_issuers) {
             const uint32_t as = smem_u32(A_smem), ws = smem_u32(W_smem);
-#define MASG_ROLE(MSV, NIV, SPL, WV) mma_role<NT, MSV, NIV, SPL, WV>(a, bars, as, ws, tmem_base)
+#define MASG_ROLE(MSV, NIV, SPL, WV) mma_role<NT, MSV, NIV, SPL, WV, PAIR>(a, bars, as, ws, tmem_base)
             if (a.split) {
                 if (a.msub == 1) MASG_ROLE(1, 1, true, 0);
                 else if (a.msub == 2 && NT <= 128) { if (w == 0) MASG_ROLE(2, 2, true, 0); else MASG_ROLE(2, 2, true, 1); }
@@ -794,12 +843,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         const bool res_fast = RES_FAST && a.y_planar && a.R1 != nullptr && a.up == 1 && a.up_pad == 0 && a.msub * NT == 256 && !(a.dbg & 64);
         int it = 0;
         const long long t_epi0 = clock64();
-        for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+        auto release_acc = [&](int accb) {                  // this warp has read its part of the accumulator set
+            tc_fence_before();                              // order this warp's tcgen05.ld before the release below
+            __syncwarp();
+            if (lane == 0) { if (PAIR) mbar_arrive_cluster(map_to_rank(bars.acc_empty(accb), 0)); else mbar_arrive(bars.acc_empty(accb)); }
+        };
+        for (int wi = w_first; wi < w_total; wi += w_stride, ++it) {
+            const int tile = tile_of(wi);
             const int nt = tile % a.n_ntiles, rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
             const int n0 = nt * NT, q0 = rt * a.msub * 128;
             const int accb = it & 1;
             const bool tr = (a.dbg & 32) && blockIdx.x == 0 && threadIdx.x == 0;
             TRACE(tr, 3, it, 0);
+            if (PAIR && tile >= a.total_tiles) {            // the empty peer tile of an odd row-block count
+                mbar_wait_relaxed(bars.acc_full(accb), (it >> 1) & 1);
+                tc_fence_after();
+                release_acc(accb);
+                continue;
+            }
             const long boff = (long)b * a.y_bs;
             if constexpr (RES_FAST) {
                 if (res_fast) {
@@ -808,9 +869,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     if (a.R2 == nullptr) epi_res_run<NT, 256 / NT, false>(a, rtile, bars.acc_full(accb), (it >> 1) & 1, tacc, bias_s, n0);
                     else epi_res_run<NT, 256 / NT, true>(a, rtile, bars.acc_full(accb), (it >> 1) & 1, tacc, bias_s, n0);
                     TRACE(tr, 3, it, 1);
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bars.acc_empty(accb));
+                    release_acc(accb);
                     TRACE(tr, 3, it, 2);
                     continue;
                 }
@@ -890,18 +949,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
                     }
                 }
             }
-            tc_fence_before();                              // order this warp's tcgen05.ld before the release below
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bars.acc_empty(accb));
+            release_acc(accb);
             TRACE(tr, 3, it, 2);
         }
         if ((a.dbg & 16) && threadIdx.x == 0) atomicAdd(&g_tc_stats[5], (unsigned long long)(clock64() - t_epi0));
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();                           // neither CTA's shared memory / TMEM goes away while the pair's MMAs can still touch it
     if (warp == MMA_WARP) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols) : "memory");
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols) : "memory");
     }
 }
 
@@ -951,6 +1010,19 @@ void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s, int n_
     static bool attr = false;
     if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
     CUDA_OK(launch_pdl(k_conv_tc<NT, TMA_IN>, grid, NTHREADS, smem, s, a, a.total_tiles < n_sm));
+}
+// pair mode: clusters of two CTAs (one per SM of a TPC)
+template <int NT>
+void launch_inst_pair(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(NTHREADS, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CUDA_OK(cudaLaunchKernelEx(&cfg, k_conv_tc<NT, true, true>, a));
 }
 
 }  // namespace
@@ -1011,6 +1083,16 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
         c->launches++;
         d.w16s = ws; d.NTs = 32; d.KWs = KWs;
     }
+    d.w16h = nullptr;
+    if (!split && !wide && NT == 128) {
+        // pair mode of k_conv_tc: the same blobs 64 columns wide — column tile nt = blob sets 2 nt (leader CTA) and 2 nt + 1 (peer)
+        bf16* wh = nullptr;
+        CUDA_OK(cudaMalloc(&wh, n * sizeof(bf16)));
+        c->owned.push_back(wh);
+        k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, wh, d.Cin, d.N, d.taps, NT / 2, KW, mode);
+        c->launches++;
+        d.w16h = wh;
+    }
     d.w16p = nullptr;
     if (!split && mode == 0 && !wide && d.Cin == d.N && ((d.N == 128 && d.taps == 3) || (d.N == 64 && (d.taps == 11 || d.taps == 7)))) {
         // square convs that respair2_tc.cu fuses on a CTA pair: [2 halves][1][taps][Cin/8][N/2][8]
@@ -1055,7 +1137,7 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     TcArgs a;
     memset(&a, 0, sizeof(a));
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
-    a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;
+    a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;      // (pair mode: a.Wt is replaced below)
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
     a.KW = d.KW; a.split = d.split; a.f16 = d.f16;
     MASG_CHECK(!io.x_planar || !io.in_act || !d.f16, "conv_tc: planar fp16 input has no input activation");
@@ -1064,6 +1146,17 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
                "conv_tc: fp16 planar output supports bias + relu / tanh only");
     const int NT = d.NT;
     const size_t a_mul = d.split ? 2 : 1;
+    // pair mode (clusters of two CTAs, cta_group::2 MMAs): N = 128 tiles of planar, single-pass layers without a fused LayerNorm,
+    // when the launch has at least two tiles per SM (MASG_TC_PAIR = 0: off)
+    bool pair = false;
+    {
+        static int on = -1;
+        if (on < 0) { const char* e = getenv("MASG_TC_PAIR"); on = e ? atoi(e) : 1; }
+        // (not the transposed-conv upsamplers: two taps, many column tiles — measured 6-20 % slower in pair mode)
+        pair = on && NT == 128 && tma_in && !d.split && d.w16h != nullptr && !io.ln_g && io.y_planar && (d.up == 0 || io.pair_mode > 0) &&
+               io.pair_mode >= 0 && (io.pair_mode > 0 || (long)io.B * ((io.Q + 255) / 256) * (d.N / NT) >= 2L * c->n_sm);
+    }
+    const int NTB = pair ? NT / 2 : NT;                    // weight columns per CTA
     int off_lo = d.off0, off_hi = d.off0;
     for (int j = 0; j < d.taps; ++j) { int o = d.off0 + j * d.tstep; off_lo = std::min(off_lo, o); off_hi = std::max(off_hi, o); }
     const int halo = off_hi - off_lo;
@@ -1133,7 +1226,8 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         a.a_lbo16 = Rp; a.a_ms16 = 128;
     }
     a.msub = msub; a.KC = KC;
-    a.blob_bytes = d.KW * NT * 2 * (int)a_mul;
+    a.blob_bytes = d.KW * NTB * 2 * (int)a_mul;
+    if (pair) a.Wt = d.w16h;
     a.n_blobs = (d.Cin / d.KW) * d.taps;
     // weight ring: every stage costs the issuers one barrier round trip, so stages hold two 16 KB blobs (three stages)
     // when that fits beside the activation slots and the stream is long, else 16 KB (four stages)
@@ -1146,7 +1240,7 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + 3 * (size_t)g2 * a.blob_bytes;
         // measured at the C3 shapes (with the lean planar epilogue): +6 % at k = 7, +8 % / +13 % at k = 11 (stage 2 / stage 1),
         // neutral for k = 3 and the upsamplers
-        if (big && !d.split && a.blob_bytes == W_STAGE_BYTES && a.n_blobs >= big && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
+        if (big && !d.split && a.blob_bytes * (pair ? 2 : 1) == W_STAGE_BYTES && a.n_blobs >= big * (pair ? 2 : 1) && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
     }
     {
         // small weight sets (C = 64 k = 11: 90 KB; C = 128 k = 3: 96 KB) stay resident: one stage holding every blob, loaded by
@@ -1173,6 +1267,7 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     a.tmem_cols = cols;
     a.B = io.B; a.row_tiles = (io.Q + msub * 128 - 1) / (msub * 128); a.n_ntiles = ntiles_n;
     a.total_tiles = io.B * a.row_tiles * ntiles_n;
+    a.total_pairs = ((io.B * a.row_tiles + 1) / 2) * ntiles_n;
     a.Y = io.Y; a.Y16 = io.Y16; a.y_bs = io.y_bs; a.y_limit = io.y_limit; a.orow = d.orow ? d.orow : d.N; a.ooff = d.ooff; a.Q = io.Q;
     a.in_act = io.in_act; a.in_slope = io.in_slope; a.out_act = io.out_act; a.out_slope = io.out_slope;
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale; a.post_slope = io.post_slope;
@@ -1203,6 +1298,17 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     const size_t smem = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + (size_t)a.w_stages * a.stage_bytes;
     MASG_CHECK(smem <= (size_t)MAX_SMEM, "conv_tc: %zu bytes of shared memory needed", smem);
     MASG_CHECK(!tma_in || ((uintptr_t)io.X & 15) == 0, "conv_tc: planar input must be 16-byte aligned");
+    if (pair) {
+        // resident weights with several column tiles: the cluster count is a multiple of the column-tile count (see grid_r above)
+        int clusters = c->n_sm / 2;
+        if (a.w_resident && ntiles_n > 1) clusters = (clusters / ntiles_n) * ntiles_n;
+        MASG_CHECK(clusters > 0, "conv_tc: pair mode needs at least %d SMs", 2 * ntiles_n);
+        const dim3 grid2(2 * std::min(a.total_pairs, clusters), 1, 1);
+        launch_inst_pair<128>(a, grid2, smem, s);
+        CUDA_OK(cudaGetLastError());
+        c->launches++;
+        return;
+    }
     dim3 grid(std::min(a.total_tiles, grid_cap), 1, 1);            // persistent: one CTA per SM walks the tile list
 #define MASG_TC_CASE(NTV)                                                                       \
     case NTV: if (tma_in) launch_inst<NTV, true>(a, grid, smem, s, c->n_sm); else launch_inst<NTV, false>(a, grid, smem, s, c->n_sm); break;

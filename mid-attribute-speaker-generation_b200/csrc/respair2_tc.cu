@@ -70,43 +70,6 @@ struct Rp2Bars {
 };
 static_assert(8 * (3 * R2_MAX_XS + 14) <= 256, "barrier block overlaps the TMEM slot");
 
-// ---- cluster-scope PTX (the CTA-scope wrappers are in tc_ptx.cuh) ----
-__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ uint32_t map_to_rank(uint32_t addr, uint32_t rank) {
-    uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
-}
-// Remote arrivals and the leader's waits use the default (CTA-scope release / acquire) forms, as CUTLASS's ClusterBarrier does:
-// what they order is this CTA's own shared-memory stores — already made visible to the async proxy by fence.proxy.async — against
-// MMAs that read THIS CTA's shared memory.  The .release.cluster / .acquire.cluster forms compile to MEMBAR.ALL.GPU + ERRBAR per
-// arrival and CCTL.IVALL (an L1 invalidate) per wait; in the hand-over chains they cost ~2,000 cycles per tile (measured).
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t caddr) {
-    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t caddr) {
-    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {            // local barrier, arrivals from both CTAs
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(20000u) : "memory");
-    }
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-// arrive::one on the barrier at this offset in BOTH CTAs once every MMA issued so far by this thread has completed
-__device__ __forceinline__ void tc_commit2(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"((uint16_t)3) : "memory");
-}
-__device__ __forceinline__ void tc_mma2(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
-                 "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}"
-                 ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
-}
-
 // XS activation slots, NH buffers of h, MS sub-tiles of 128 rows per CTA tile
 template <int C, int K, int MS, int XS, int NH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_respair2_tc(const Rp2Args a) {

@@ -448,20 +448,30 @@ CONV_CASES = [
     (1, 2100, 64, 64, 7, 3, 0, 0.1, 0),
     (2, 37, 512, 256, 16, 1, 8, 0.1, 0),      # ConvTranspose1d ups[0]
     (2, 300, 64, 32, 4, 1, 2, 0.1, 0),        # ConvTranspose1d ups[3]
+    (3, 700, 128, 128, 7, 3, 0, 0.1, 0),      # HiFi-GAN stage 2: 9 row blocks (odd: an empty peer tile in the CTA-pair form)
+    (2, 520, 256, 256, 11, 5, 0, 0.1, 0),     # stage 1: two column tiles, multi-chunk K
+    (1, 77, 256, 128, 16, 1, 8, 0.1, 0),      # ConvTranspose1d ups[1]: N = 1024
 ]
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16-split", "bf16-act"])
+# "bf16-act-pair": the same planar layers through the CTA-pair form of the kernel (clusters of two CTAs, tcgen05 cta_group::2),
+# which the library otherwise only picks for launches of at least two tiles per SM
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16-split", "bf16-act", "bf16-act-pair"])
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_conv_kernel_matches_torch(precision, case):
     import torch.nn.functional as F
     from masg_b200 import _lib
     B, T, Cin, Cout, k, dil, ups, slope, act = case
     split = precision == "bf16-split"
+    pair = precision == "bf16-act-pair"
+    if pair:
+        precision = "bf16-act"
+        if ((ups or 1) * Cout) % 128:
+            pytest.skip("the CTA-pair form exists for 128-column tiles")
     if precision == "bf16-act" and (Cout & (Cout - 1)):
         pytest.skip("planar bf16 activations (HiFi-GAN layout) need a power-of-two channel count")
     residual = precision == "bf16-act" and Cin == Cout and not ups       # bf16 activations in HBM + residual add (HiFi-GAN style)
-    flags = (1 if split else 0) | (2 if precision == "bf16-act" else 0) | (4 if residual else 0)
+    flags = (1 if split else 0) | (2 if precision == "bf16-act" else 0) | (4 if residual else 0) | (32 if pair else 0)
     cx = _lib.default_context(DEV, "bf16" if precision.startswith("bf16") else precision)
     g = torch.Generator().manual_seed(hash(case) % 1000)
     x = torch.randn(B, T, Cin, generator=g)

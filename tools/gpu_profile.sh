@@ -14,7 +14,7 @@ $CMD > $out/plain_$tag.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 4000 --csv --log-file $out/launches_$tag.csv $CMD > $out/ncu1_$tag.log 2>&1
 echo "ncu launches exit $?"
 $CMD > $out/plain_$tag.log 2>&1 &&
-ncu --set full --clock-control none --profile-from-start off -k 'regex:k_conv_tc|k_respair_tc' -c 130 -o $out/prof_all_$tag -f $CMD > $out/ncu2_$tag.log 2>&1
+ncu --set full --clock-control none --profile-from-start off -k 'regex:k_conv_tc|k_respair' -c 130 -o $out/prof_all_$tag -f $CMD > $out/ncu2_$tag.log 2>&1
 echo "ncu full exit $?"
 ncu -i $out/prof_all_$tag.ncu-rep --page raw --csv > $out/prof_all_$tag.csv 2>/dev/null
 ls -la $out/prof_all_$tag.ncu-rep; rm -f $out/prof_all_$tag.ncu-rep
