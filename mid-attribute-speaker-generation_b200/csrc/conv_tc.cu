@@ -1178,6 +1178,15 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     }
     const int ntiles_n = d.N / NT;
     while (msub > 1 && (long)((io.Q + msub * 128 - 1) / (msub * 128)) * ntiles_n * io.B < c->n_sm) msub /= 2;
+    if (pair && msub == 2) {
+        // pair mode streams half of a tile's weights per CTA, so a 128-row tile per CTA costs the L2 what a 256-row tile costs the
+        // single-CTA form — and pads less: T = 600 is 5 tiles of 128 rows (640) against 3 of 256 (768), 17 % fewer MMAs in the
+        // decoder's w_1 and the PostNet.  Taken when it saves at least 8 % of the rows.
+        const long r2 = (long)((io.Q + 255) / 256) * 256, r1 = (long)((io.Q + 127) / 128) * 128;
+        static int m1 = -1;
+        if (m1 < 0) { const char* e = getenv("MASG_TC_PAIR_M1"); m1 = e ? atoi(e) : 1; }
+        if (m1 && r1 * 100 <= r2 * 92) msub = 1;
+    }
     int KC = 0, grid_cap = c->n_sm;
     if (tma_in) {
         // one [KC/8][Rb][8] block per tile (its msub*128 rows + the halo); sub-tile ms starts 128 rows further down; every
