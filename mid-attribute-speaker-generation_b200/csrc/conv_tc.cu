@@ -1094,7 +1094,7 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
         d.w16h = wh;
     }
     d.w16p = nullptr;
-    if (!split && mode == 0 && !wide && d.Cin == d.N && ((d.N == 128 && d.taps == 3) || (d.N == 64 && (d.taps == 11 || d.taps == 7)))) {
+    if (!split && mode == 0 && !wide && d.Cin == d.N && ((d.N == 128 && d.taps == 3) || (d.N == 64 && (d.taps == 11 || d.taps == 7)) || (d.N == 32 && (d.taps == 3 || d.taps == 7 || d.taps == 11)))) {
         // square convs that respair2_tc.cu fuses on a CTA pair: [2 halves][1][taps][Cin/8][N/2][8]
         bf16* wp = nullptr;
         CUDA_OK(cudaMalloc(&wp, n * sizeof(bf16)));

@@ -80,7 +80,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
     constexpr int WBYTES = K * C * NHALF * 2;               // one conv's half
     constexpr int HROWS = MS * 128 + 16;                    // rows of h + the (k - 1) rows the last sub-tile's taps reach past them
     constexpr int HBYTES = CG * HROWS * 16;
-    constexpr int NI = MS;                                  // commits per multicast barrier: MS = 2 both issuers (one sub-tile each), MS = 1 the one issuer of that conv
+    constexpr int NI = MS >= 2 ? 2 : 1;                     // commits per multicast barrier: MS >= 2 both issuers (sub-tiles w, w + 2, ... each), MS = 1 the one issuer of that conv
+    constexpr int MSL = MS >= 2 ? MS / 2 : 1;               // sub-tiles per issuer
     static_assert(4 * MS * C == 512, "TMEM: acc1[2][MS][C] | acc2[2][MS][C] must be the 512 columns");
     static_assert(XS <= R2_MAX_XS && NH <= 2 && 512 + 2 * C * 4 <= R2_HDR, "header layout");
     const Rp2Bars bars{smem_u32(smem)};
@@ -100,7 +101,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
     const int n_my = a.n_pairs > cid ? (a.n_pairs - cid + n_clusters - 1) / n_clusters : 0;    // tile pairs of this cluster: the same in both CTAs
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < XS; ++i) { mbar_init(bars.x_raw(i), R2_EPI_WARPS); mbar_init(bars.x_full(i), 2 * R2_WORK_WARPS); mbar_init(bars.x_empty(i), NI); }
+        for (int i = 0; i < XS; ++i) { mbar_init(bars.x_raw(i), CG >= R2_EPI_WARPS ? R2_EPI_WARPS : CG); mbar_init(bars.x_full(i), 2 * R2_WORK_WARPS); mbar_init(bars.x_empty(i), NI); }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bars.acc1_full(i), NI); mbar_init(bars.acc1_empty(i), 2 * R2_EPI_WARPS);
             mbar_init(bars.h_full(i), 2 * R2_EPI_WARPS); mbar_init(bars.h_empty(i), NI);
@@ -174,7 +175,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
             const uint32_t xs16 = smem_u32(Xs) >> 4, hs16 = smem_u32(Hs) >> 4, x16 = (uint32_t)x_bytes >> 4;
             // B: this CTA's C/2 columns, 8-channel groups C/2 rows apart; the peer's half is read at the same offsets of its memory
             const uint32_t w1_lo = ((uint32_t)NHALF << 16) | (smem_u32(W1s) >> 4), w2_lo = ((uint32_t)NHALF << 16) | (smem_u32(W2s) >> 4);
-            const uint32_t sub = MS == 2 ? w : 0u;
+            const uint32_t sub = MS >= 2 ? w : 0u;
             mbar_wait(bars.w_ready(), 0);
             mbar_wait_cluster(bars.w_peer(), 0);
             auto P1 = [&](int it) {
@@ -189,8 +190,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
 #pragma unroll
                     for (int j = 0; j < K; ++j) {
 #pragma unroll
-                        for (int ks = 0; ks < KS; ++ks)
-                            tc_mma2(d, a0 + (uint32_t)j * dil + (uint32_t)ks * 2u * lbo_x, w1_lo + (uint32_t)((j * KS + ks) * 2 * NHALF), desc_hi, idesc, (j | ks) ? 1u : 0u);
+                        for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+                            for (int i = 0; i < MSL; ++i)       // this issuer's sub-tiles sub, sub + 2, ...: the same weight block back to back
+                                tc_mma2(d + (uint32_t)(2 * i * C), a0 + (uint32_t)(2 * i) * 128u + (uint32_t)j * dil + (uint32_t)ks * 2u * lbo_x,
+                                        w1_lo + (uint32_t)((j * KS + ks) * 2 * NHALF), desc_hi, idesc, (j | ks) ? 1u : 0u);
+                        }
                     }
                     tc_commit2(bars.x_empty(slot));
                     tc_commit2(bars.acc1_full(b));
@@ -211,8 +216,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
 #pragma unroll
                     for (int j = 0; j < K; ++j) {
 #pragma unroll
-                        for (int ks = 0; ks < KS; ++ks)
-                            tc_mma2(d, a0 + (uint32_t)j + (uint32_t)(ks * 2 * HROWS), w2_lo + (uint32_t)((j * KS + ks) * 2 * NHALF), desc_hi, idesc, (j | ks) ? 1u : 0u);
+                        for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+                            for (int i = 0; i < MSL; ++i)
+                                tc_mma2(d + (uint32_t)(2 * i * C), a0 + (uint32_t)(2 * i) * 128u + (uint32_t)j + (uint32_t)(ks * 2 * HROWS),
+                                        w2_lo + (uint32_t)((j * KS + ks) * 2 * NHALF), desc_hi, idesc, (j | ks) ? 1u : 0u);
+                        }
                     }
                     tc_commit2(bars.h_empty(hbuf));
                     tc_commit2(bars.acc2_full(b));
@@ -220,7 +229,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                 __syncwarp();
                 R2_TRACE(trace && sub == 0 && lane == 0, 2, it, 3);
             };
-            if (MS == 2) {
+            if (MS >= 2) {
                 if (n_my > 0) P1(0);
                 for (int it = 0; it < n_my; ++it) {
                     if (it + 1 < n_my) P1(it + 1);
@@ -242,9 +251,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
         // (planar bf16 [B][C/8][T][8]).  A cp.async.bulk costs its issuing warp ~350 cycles, whichever lane it comes from (2,600-3,400
         // cycles for a tile's 8 / 16 runs from one or two dedicated copy warps, all of it in the slot cycle), so the runs are spread
         // over these 8 warps; the copy of tile it + XS goes out when acc1 (it) is full: conv 1 (it) has then read the slot.
-        constexpr int GW = CG / R2_EPI_WARPS;
+        constexpr int GW = CG >= R2_EPI_WARPS ? CG / R2_EPI_WARPS : 1;     // C = 32: four groups, E1 warps 0-3 issue one each
+        constexpr int CW = CG >= R2_EPI_WARPS ? R2_EPI_WARPS : CG;          // warps that issue copies
         const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
         auto issue_copy = [&](int itc) {
+            if (warp >= CW) return;
             const int tile = 2 * (cid + itc * n_clusters) + (int)rank;
             const bool valid = tile < a.total_tiles;
             const int slot = itc % XS;
@@ -302,12 +313,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R2_THREADS, 1) k_res
                 R2_TRACE(trace && threadIdx.x == 0, 0, it + XS, 2);
             }
             uint4 pk[MS][CH / 8];
-            constexpr int NLD = MS == 2 ? CH / 16 : CH / 32;   // two 16-column loads in flight per wait: (ms 0, ms 1) or (cg, cg + 1)
+            constexpr int NLD = MS * (CH / 16) / 2;             // two 16-column loads in flight per wait: items (cg, ms) = (t / MS, t % MS), t = 2 q, 2 q + 1
 #pragma unroll
             for (int q = 0; q < NLD; ++q) {
                 float v[2][16];
-                const int cga = MS == 2 ? q : 2 * q, cgb = MS == 2 ? q : 2 * q + 1;
-                const int msa = 0, msb = MS == 2 ? 1 : 0;
+                const int cga = (2 * q) / MS, cgb = (2 * q + 1) / MS;
+                const int msa = (2 * q) % MS, msb = (2 * q + 1) % MS;
                 tmem_ld16x2(tlane + (uint32_t)((b * MS + msa) * C + hf * CH + cga * 16), tlane + (uint32_t)((b * MS + msb) * C + hf * CH + cgb * 16), v[0], v[1]);
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
@@ -441,6 +452,11 @@ struct Rp2Config { int ms, xs, nh; };
 bool rp2_config(int C, int K, Rp2Config& cf) {
     if (C == 128 && K == 3) { cf = {1, 2, 1}; return true; }
     if (C == 64 && K == 11) { cf = {2, 2, 1}; return true; }
+    if (C == 32 && (K == 3 || K == 7 || K == 11)) {          // fits one SM (respair_tc.cu, 6 slots + 2 h buffers, 256-row tiles); here 512-row tiles, 3 + 2.  MASG_RP2_C32=0: off
+        static int on = -1;
+        if (on < 0) { const char* e = getenv("MASG_RP2_C32"); on = e ? atoi(e) : 0; }   // measured: k = 3 / 11 2 % faster, k = 7 6 % slower than respair_tc: off
+        if (on) { cf = {4, 3, 2}; return true; }
+    }
     if (C == 64 && K == 7) {                                // fits one SM too (respair_tc.cu, 2 slots + 1 h buffer); here 2 + 2.  MASG_RP2_K7=0: off
         static int on = -1;
         if (on < 0) { const char* e = getenv("MASG_RP2_K7"); on = e ? atoi(e) : 1; }
@@ -512,6 +528,9 @@ void launch_respair2_tc(masg_ctx* c, cudaStream_t s, const ConvDesc& d1, const C
     if (C == 128 && K == 3) launch_rp2<128, 3, 1, 2, 1>(a, grid, smem, s);
     else if (C == 64 && K == 11) launch_rp2<64, 11, 2, 2, 1>(a, grid, smem, s);
     else if (C == 64 && K == 7) launch_rp2<64, 7, 2, 2, 2>(a, grid, smem, s);
+    else if (C == 32 && K == 3) launch_rp2<32, 3, 4, 3, 2>(a, grid, smem, s);
+    else if (C == 32 && K == 7) launch_rp2<32, 7, 4, 3, 2>(a, grid, smem, s);
+    else if (C == 32 && K == 11) launch_rp2<32, 11, 4, 3, 2>(a, grid, smem, s);
     CUDA_OK(cudaGetLastError());
     c->launches++;
     if (c->profiling) { CUDA_OK(cudaEventRecord(rec.e1, s)); c->prof.push_back(rec); }
