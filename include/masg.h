@@ -208,8 +208,10 @@ int masg_conv1d(masg_ctx* ctx, void* stream, const float* x, int B, int T, int C
 
 /* One (convs1[m], convs2[m]) step of ResBlock1.forward (hifigan/models.py:96-103) through the fused bf16 kernel:
  *     y = (c2(leaky_relu(c1(leaky_relu(x, 0.1)), 0.1)) + x [+ acc]) * out_scale,  then leaky_relu(post_slope) unless 1.
- * Diagnostic / micro-benchmark hook for the vocoder's narrow stages (MASG_PREC_BF16 only; C = 32 with k = 3, 7, 11 or
- * C = 64 with k = 3, 7; anything else is an error).  x, acc (nullable), y fp32 [B, T, C] channels-last (converted to the
+ * Diagnostic / micro-benchmark hook for the vocoder's fused stages (MASG_PREC_BF16 only; C = 32 with k = 3, 7, 11, C = 64 with
+ * k = 3, 7, 11 or C = 128 with k = 3; anything else is an error).  The call takes the kernel the generator takes: the one-SM kernel
+ * (respair_tc.cu) or, for C = 64 k = 7 / 11 and C = 128 k = 3, the CTA-pair kernel (respair2_tc.cu: clusters of two CTAs, tcgen05
+ * cta_group::2, the weight columns split over the pair).  x, acc (nullable), y fp32 [B, T, C] channels-last (converted to the
  * planar bf16 layout before and after the timed launches); w1, w2 fp32 [C, C, k] (torch layout, weight-norm already
  * folded); c1 has `dilation`, c2 dilation 1, both "same" padding.  *h_ms as in masg_conv1d. */
 int masg_respair(masg_ctx* ctx, void* stream, const float* x, const float* acc, int B, int T, int C, const float* w1,
