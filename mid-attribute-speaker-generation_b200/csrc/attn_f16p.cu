@@ -244,11 +244,8 @@ k_attention_f16p(const __half* __restrict__ qkv, const int64_t* __restrict__ len
 
 // qkv: planar fp16 [B][96][S][8] (q | k | v, heads of 128 columns); out: planar fp16 [B][32][S][8]
 void launch_attention_f16p(masg_ctx* c, cudaStream_t s, const void* qkv, const int64_t* lens, int B, int S, void* out) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        CUDA_OK(cudaFuncSetAttribute(k_attention_f16p, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_attention_f16p, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     dim3 grid((S + AQ - 1) / AQ, 2, B);
     k_attention_f16p<<<grid, NTHR, SMEM_BYTES, s>>>((const __half*)qkv, lens, S, (__half*)out);
     CUDA_OK(cudaGetLastError());

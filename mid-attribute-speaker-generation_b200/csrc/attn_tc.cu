@@ -267,11 +267,10 @@ k_attention_tc(const float* __restrict__ qkv, const int64_t* __restrict__ lens, 
 
 void launch_attention_tc(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out, int f16) {
     dim3 grid((S + AQ - 1) / AQ, 2, B);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    if (once.need()) {
         CUDA_OK(cudaFuncSetAttribute(k_attention_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         CUDA_OK(cudaFuncSetAttribute(k_attention_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM_F16));
-        attr_set = true;
     }
     if (f16) k_attention_tc<true><<<grid, AT_THREADS, AT_SMEM_F16, s>>>(qkv, lens, S, out);
     else k_attention_tc<false><<<grid, AT_THREADS, AT_SMEM, s>>>(qkv, lens, S, out);

@@ -25,6 +25,19 @@ struct MasgError { std::string msg; };
     do { cudaError_t _e = (call); if (_e != cudaSuccess) {                                  \
          throw MasgError{std::string("CUDA error: ") + cudaGetErrorString(_e) + " in " #call " at " __FILE__ ":" + std::to_string(__LINE__)}; } } while (0)
 
+// The dynamic shared-memory opt-in (cudaFuncSetAttribute) is a per-DEVICE attribute of a kernel: one process driving several GPUs
+// has to set it on each.  `static PerDeviceOnce once; if (once.need()) cudaFuncSetAttribute(...)` in every launcher.
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool need() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+        if (done[d]) return false;
+        done[d] = true;                                   // (a race between host threads only repeats an idempotent call)
+        return true;
+    }
+};
+
 // ---- device arena: grown on demand, never freed mid-stream (stream-ordered reuse by one ctx) ----
 struct Arena {
     char* base = nullptr; size_t cap = 0, off = 0;

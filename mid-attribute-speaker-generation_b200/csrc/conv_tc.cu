@@ -1007,15 +1007,15 @@ __global__ void k_from_planar(const bf16* __restrict__ x, float* __restrict__ ou
 
 template <int NT, bool TMA_IN>
 void launch_inst(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s, int n_sm) {
-    static bool attr = false;
-    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, TMA_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     CUDA_OK(launch_pdl(k_conv_tc<NT, TMA_IN>, grid, NTHREADS, smem, s, a, a.total_tiles < n_sm));
 }
 // pair mode: clusters of two CTAs (one per SM of a TPC)
 template <int NT>
 void launch_inst_pair(const TcArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM)); attr = true; }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_conv_tc<NT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = dim3(NTHREADS, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = s;
     cudaLaunchAttribute at[1];

@@ -418,8 +418,8 @@ k_attention_f32(const float* __restrict__ qkv, const int64_t* __restrict__ lens,
 void launch_attention_f32(masg_ctx* c, cudaStream_t s, const float* qkv, const int64_t* lens, int B, int S, float* out) {
     dim3 grid(cdiv(S, AT_Q), 2, B);
     const int smem = (AT_Q * 128 + 32 * 128 + 32 * 129) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) { CUDA_OK(cudaFuncSetAttribute(k_attention_f32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_attention_f32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     k_attention_f32<<<grid, 128, smem, s>>>(qkv, lens, S, out);
     c->launches++;
 }

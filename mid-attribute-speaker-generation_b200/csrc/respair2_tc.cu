@@ -471,8 +471,8 @@ size_t rp2_smem(int C, int K, int Rx, const Rp2Config& cf) {
 
 template <int C, int K, int MS, int XS, int NH>
 void launch_rp2(const Rp2Args& a, dim3 grid, size_t smem, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_respair2_tc<C, K, MS, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, R2_MAX_SMEM)); attr = true; }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_respair2_tc<C, K, MS, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, R2_MAX_SMEM));
     k_respair2_tc<C, K, MS, XS, NH><<<grid, R2_THREADS, smem, s>>>(a);
 }
 

@@ -382,8 +382,8 @@ __global__ void __launch_bounds__(RP_THREADS, 1) k_respair_tc(const RpArgs a) {
 
 template <int C, int K, int XS, int NH>
 void launch_rp(const RpArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
-    static bool attr = false;
-    if (!attr) { CUDA_OK(cudaFuncSetAttribute(k_respair_tc<C, K, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, RP_MAX_SMEM)); attr = true; }
+    static PerDeviceOnce once;
+    if (once.need()) CUDA_OK(cudaFuncSetAttribute(k_respair_tc<C, K, XS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, RP_MAX_SMEM));
     CUDA_OK(launch_pdl(k_respair_tc<C, K, XS, NH>, grid, RP_THREADS, smem, s, a, a.total_tiles <= (int)grid.x));
 }
 
