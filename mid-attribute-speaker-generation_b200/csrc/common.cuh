@@ -75,6 +75,7 @@ struct ConvDesc {
     const bf16* w16p = nullptr;
     // the commit-time tiling at NT / 2 columns per blob set, for the pair mode of k_conv_tc (NT = 128 layers)
     const bf16* w16h = nullptr;
+    const bf16* w16h2 = nullptr;      // the same at 128 input channels per blob (launches with 128-row tiles: one issuing thread)
 };
 
 struct ConvWeights {                  // owned storage for a ConvDesc

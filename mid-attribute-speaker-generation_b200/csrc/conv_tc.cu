@@ -1083,15 +1083,27 @@ void tc_prepare_weights(masg_ctx* c, cudaStream_t s, ConvDesc& d, int mode) {
         c->launches++;
         d.w16s = ws; d.NTs = 32; d.KWs = KWs;
     }
-    d.w16h = nullptr;
+    d.w16h = nullptr; d.w16h2 = nullptr;
     if (!split && !wide && NT == 128) {
         // pair mode of k_conv_tc: the same blobs 64 columns wide — column tile nt = blob sets 2 nt (leader CTA) and 2 nt + 1 (peer)
         bf16* wh = nullptr;
         CUDA_OK(cudaMalloc(&wh, n * sizeof(bf16)));
         c->owned.push_back(wh);
+        // 128 input channels per blob where Cin allows it (16 KB blobs again): 8 K-steps per (tap, slab) block of the issue loop — at
+        // 4, one thread issuing a whole 128-row tile (pair mode's msub = 1) spends ~79 cycles per 64-cycle MMA on the block overhead
+        static int kw128 = -1;
+        if (kw128 < 0) { const char* e = getenv("MASG_TC_PAIR_KW128"); kw128 = e ? atoi(e) : 1; }
         k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, wh, d.Cin, d.N, d.taps, NT / 2, KW, mode);
         c->launches++;
         d.w16h = wh;
+        if (kw128 && d.Cin % 128 == 0 && KW < 128) {          // second copy, used by launches that take 128-row tiles (msub = 1)
+            bf16* wh2 = nullptr;
+            CUDA_OK(cudaMalloc(&wh2, n * sizeof(bf16)));
+            c->owned.push_back(wh2);
+            k_tile_w<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d.w32, wh2, d.Cin, d.N, d.taps, NT / 2, 128, mode);
+            c->launches++;
+            d.w16h2 = wh2;
+        }
     }
     d.w16p = nullptr;
     if (!split && mode == 0 && !wide && d.Cin == d.N && ((d.N == 128 && d.taps == 3) || (d.N == 64 && (d.taps == 11 || d.taps == 7)) || (d.N == 32 && (d.taps == 3 || d.taps == 7 || d.taps == 11)))) {
@@ -1139,7 +1151,7 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     a.X = io.X; a.x_bs = io.x_bs; a.x_ld = io.x_ld; a.Tin = io.Tin;
     a.Wt = d.w16; a.bias = d.bias; a.bias_mod = d.bias_mod ? d.bias_mod : d.N;      // (pair mode: a.Wt is replaced below)
     a.Cin = d.Cin; a.N = d.N; a.taps = d.taps; a.off0 = d.off0; a.tstep = d.tstep;
-    a.KW = d.KW; a.split = d.split; a.f16 = d.f16;
+    a.split = d.split; a.f16 = d.f16;                  // (a.KW: below, once pair mode is decided)
     MASG_CHECK(!io.x_planar || !io.in_act || !d.f16, "conv_tc: planar fp16 input has no input activation");
     a.y_f16 = io.y_f16;
     MASG_CHECK(!io.y_f16 || (io.y_planar && io.out_act != ACT_LRELU && io.post_slope == 1.f && !io.R1 && !io.R2),
@@ -1187,6 +1199,10 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         if (m1 < 0) { const char* e = getenv("MASG_TC_PAIR_M1"); m1 = e ? atoi(e) : 1; }
         if (m1 && r1 * 100 <= r2 * 92) msub = 1;
     }
+    // input channels per weight blob: the commit-time 64 (or less), or 128 for pair-mode launches with 128-row tiles
+    const bool kw128 = pair && msub == 1 && d.w16h2 != nullptr;
+    const int KW = kw128 ? 128 : d.KW;
+    a.KW = KW;
     int KC = 0, grid_cap = c->n_sm;
     if (tma_in) {
         // one [KC/8][Rb][8] block per tile (its msub*128 rows + the halo); sub-tile ms starts 128 rows further down; every
@@ -1195,9 +1211,9 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         int Rb = 0;
         for (;;) {
             Rb = (msub * 128 + halo + 7) & ~7;
-            for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
-                if ((d.Cin / d.KW) % m) continue;
-                const int kc = m * d.KW;
+            for (int m = d.Cin / KW; m >= 1 && !KC; --m) {
+                if ((d.Cin / KW) % m) continue;
+                const int kc = m * KW;
                 if ((size_t)Rb * kc * 2 <= (size_t)A_SLOT_BYTES) KC = kc;
             }
             if (KC || msub == 1) break;
@@ -1220,9 +1236,9 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
                 while ((rp % 8) != want && !(cpr >= 8 && (rp & 1))) ++rp;
                 return rp;
             };
-            for (int m = d.Cin / d.KW; m >= 1 && !KC; --m) {
-                if ((d.Cin / d.KW) % m) continue;
-                const int kc = m * d.KW;
+            for (int m = d.Cin / KW; m >= 1 && !KC; --m) {
+                if ((d.Cin / KW) % m) continue;
+                const int kc = m * KW;
                 if ((size_t)pad_rows(kc) * kc * 2 * a_mul + 256 <= (size_t)A_SLOT_BYTES) { KC = kc; Rp = pad_rows(kc); }
             }
             if (KC || msub == 1) break;
@@ -1235,9 +1251,9 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         a.a_lbo16 = Rp; a.a_ms16 = 128;
     }
     a.msub = msub; a.KC = KC;
-    a.blob_bytes = d.KW * NTB * 2 * (int)a_mul;
-    if (pair) a.Wt = d.w16h;
-    a.n_blobs = (d.Cin / d.KW) * d.taps;
+    a.blob_bytes = KW * NTB * 2 * (int)a_mul;
+    if (pair) a.Wt = kw128 ? d.w16h2 : d.w16h;
+    a.n_blobs = (d.Cin / KW) * d.taps;
     // weight ring: every stage costs the issuers one barrier round trip, so stages hold two 16 KB blobs (three stages)
     // when that fits beside the activation slots and the stream is long, else 16 KB (four stages)
     a.w_stages = W_STAGES;
@@ -1249,7 +1265,8 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         const size_t need = SMEM_HDR + BIAS_MAX * 4 + A_SLOTS * (size_t)a.a_bytes + 3 * (size_t)g2 * a.blob_bytes;
         // measured at the C3 shapes (with the lean planar epilogue): +6 % at k = 7, +8 % / +13 % at k = 11 (stage 2 / stage 1),
         // neutral for k = 3 and the upsamplers
-        if (big && !d.split && a.blob_bytes * (pair ? 2 : 1) == W_STAGE_BYTES && a.n_blobs >= big * (pair ? 2 : 1) && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
+        const int per16 = W_STAGE_BYTES / a.blob_bytes;                       // blobs per 16 KB (1, or 2 for pair mode's 64-channel blobs)
+        if (big && !d.split && per16 >= 1 && per16 * a.blob_bytes == W_STAGE_BYTES && a.n_blobs >= big * per16 && need <= (size_t)MAX_SMEM) { a.G = g2; a.w_stages = 3; }
     }
     {
         // small weight sets (C = 64 k = 11: 90 KB; C = 128 k = 3: 96 KB) stay resident: one stage holding every blob, loaded by
@@ -1270,7 +1287,7 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
         }
     }
     a.stage_bytes = a.G * a.blob_bytes;
-    a.n_blobs = (d.Cin / d.KW) * d.taps;
+    a.n_blobs = (d.Cin / KW) * d.taps;
     int cols = 32; while (cols < 2 * msub * NT) cols *= 2;
     MASG_CHECK(cols <= 512, "conv_tc: %d TMEM columns needed", cols);
     a.tmem_cols = cols;
