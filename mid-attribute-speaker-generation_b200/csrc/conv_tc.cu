@@ -88,6 +88,7 @@ struct TcArgs {
     int w_stages;                                      // weight ring depth (3 with 32 KB stages, else 4 with 16 KB stages)
     // fused LayerNorm epilogue (NT == N == 256, row-major fp32 output): see epi_layernorm
     const float* ln_g; const float* ln_b; const int64_t* ln_lens; int ln_T; bf16* Y16p;
+    int copiers;   // warps issuing the activation bulk copies (the copy warp + up to three idle MMA warps; MASG_TC_COPIERS forces a count)
     int dbg;   // MASG_TC_DEBUG what-if switches (timing experiments only): 1 no weight stream, 2 no activation staging, 4 no epilogue I/O, 8 no MMA
 };
 
@@ -566,6 +567,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     const bool a_workers = PAIR || !TMA_IN || a.in_act != ACT_NONE;   // pair mode: the workers also forward "tile landed" to the leader
     const bool ln_helpers = NT == 256 && a.ln_g != nullptr && !a_workers && !(a.dbg & 1024);   // idle worker warps join the LayerNorm epilogue
     const int n_issuers = min(a.msub, MMA_WARPS);
+    const int n_copiers = TMA_IN ? max(1, min(a.copiers, 1 + MMA_WARPS - max(n_issuers, 1))) : 1;   // copy warp + idle MMA warps
     // work items: tiles, or (pair mode) tile pairs: pair p = (row-block pair p / n_ntiles, column tile p % n_ntiles), rank r takes
     // row block 2 (p / n_ntiles) + r; an odd row-block count leaves the last peer tile empty (nothing loaded or stored)
     const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
@@ -575,7 +577,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < A_SLOTS; ++i) {
-            mbar_init(bars.a_full(i), PAIR ? 2 * A_WARPS : (a_workers ? A_THREADS : 1)); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), 1);
+            mbar_init(bars.a_full(i), PAIR ? 2 * A_WARPS : (a_workers ? A_THREADS : n_copiers)); mbar_init(bars.a_empty(i), n_issuers); mbar_init(bars.a_raw(i), n_copiers);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bars.acc_full(i), n_issuers);
@@ -604,6 +606,75 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
     // memory / TMEM only) run ahead, every role that reads or writes activations waits for the previous grid of the stream
     pdl_trigger();
     if (warp != W_WARP && !(warp >= MMA_WARP && warp < MMA_WARP + MMA_WARPS)) pdl_wait();
+
+    // ---- activation copies (planar input): copier ci of n_copiers moves the 8-channel groups ci, ci + n_copiers, ... of every chunk.
+    // Copier 0 is the copy warp; the others are the MMA warps that issue nothing in this launch (msub = 1: three, msub = 2: two).
+    // Why: a cp.async.bulk costs its issuing warp ~200-350 cycles whichever lane it comes from, so the 64 runs of a tile of the first
+    // upsampler (Cin = 512) from one warp outlast its 128 MMAs.  Used only there (see the launch code).
+    auto copy_role = [&](const int ci) {
+        if (ci > 0) pdl_wait();
+        int slot = 0, it = 0; uint32_t phase = 0;
+        const bool tr = (a.dbg & 32) && blockIdx.x == 0 && lane == 0 && ci == 0;
+        const int cgpc = a.KC >> 3;
+        const int ng = ci < cgpc ? (cgpc - ci + n_copiers - 1) / n_copiers : 0;       // this copier's groups per chunk
+        const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
+        const bool res_pf = ci == 0 && a.res_pf && a.y_planar && a.R1 != nullptr && a.r_bf16 && a.up == 1 && a.up_pad == 0;
+        for (int wi = w_first; wi < w_total; wi += w_stride, ++it) {
+            const int tile = tile_of(wi);
+            const bool valid = !PAIR || tile < a.total_tiles;
+            const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
+            const int q_lo = rt * a.msub * 128 + a.off_lo;
+            for (int kc = 0; kc < n_chunks; ++kc) {
+                if (kc == 0) TRACE(tr, 0, it, 0);
+                if (lane == 0) STAT_WAIT((a.dbg & 16) && ci == 0, 6, mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1));
+                __syncwarp();
+                if (kc == 0) TRACE(tr, 0, it, 1);
+                const uint32_t bar = (PAIR || a.in_act != ACT_NONE) ? bars.a_raw(slot) : bars.a_full(slot);
+                uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
+                const uint32_t dst = smem_u32(dst_g);
+                // the tile is ONE [KC/8][Rp][8] block (its msub*128 rows + the halo): one contiguous run per 8-channel group
+                const int t0 = q_lo, lo = max(t0, 0), hi = valid ? max(min(t0 + a.Rp, a.Tin), lo) : lo;
+                const uint32_t run = (uint32_t)(hi - lo) * 16u;
+                if (valid && (lo > t0 || hi < t0 + a.Rp)) {
+                    for (int g = ci + n_copiers * lane; g < cgpc; g += 32 * n_copiers) {
+                        uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)g * a.Rp * 16);
+                        for (int r = 0; r < min(lo - t0, a.Rp); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                        for (int r = max(hi - t0, 0); r < a.Rp; ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                }
+                if (lane == 0) {
+                    if (run && ng) mbar_expect_tx(bar, run * (uint32_t)ng); else mbar_arrive(bar);
+                }
+                __syncwarp();
+                if (run) {
+                    for (int g = ci + n_copiers * lane; g < cgpc; g += 32 * n_copiers) {
+                        const uint8_t* src = X8 + (((size_t)b * (a.Cin >> 3) + (size_t)(kc * cgpc + g)) * a.Tin + lo) * 16;
+                        bulk_g2s(dst + (uint32_t)((g * a.Rp + (lo - t0)) * 16), src, run, bar);
+                    }
+                }
+                if (kc == 0) TRACE(tr, 0, it, 2);
+                if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
+            }
+            if (res_pf && valid) {
+                // residual rows of this tile -> L2, one run per 8-channel group, a few tiles before the epilogue warps read them.
+                // The activation copies above keep ~100 KB per SM (15 MB chip-wide) queued at the memory controllers, so a
+                // residual load that has to go to DRAM waits 2.5-5 us behind them and the epilogue's two load rounds per tile
+                // (16.8 kcycles at C = 64 k = 11) outlast the tile's MMAs (12.5 kcycles); from L2 they do not.
+                const int nt = tile % a.n_ntiles, q0 = rt * a.msub * 128;
+                const int rows = min(a.msub * 128, min(a.Q, a.y_T) - q0);
+                if (rows > 0) {
+                    const long gs = (long)a.y_T * 8;
+                    const long off = (long)b * a.y_bs + (long)((nt * NT) >> 3) * gs + (long)q0 * 8;
+                    for (int g = lane; g < NT / 8; g += 32) {
+                        bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R1) + off + (long)g * gs, (uint32_t)rows * 16u);
+                        if (a.R2) bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R2) + off + (long)g * gs, (uint32_t)rows * 16u);
+                    }
+                }
+            }
+        }
+    };
 
     // tile id -> (batch b, row tile rt, column tile nt); a CTA walks ids blockIdx.x, blockIdx.x + gridDim.x, ...
     if (warp >= A_WARP0) {
@@ -710,68 +781,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
         // (cp.async.bulk -> UBLKCP), one per lane.  (A 4-D tensor-map copy of the same box has a 16-byte innermost
         // dimension and was measured at ~16 B/clk/SM, 3.9 TB/s chip-wide.)  Rows outside [0, Tin) — the conv zero padding,
         // only in the first / last tile of an utterance — are zero-filled by the lane before the copies are issued. =====
-        if (TMA_IN && !(a.dbg & 2)) {
-            int slot = 0, it = 0; uint32_t phase = 0;
-            const bool tr = (a.dbg & 32) && blockIdx.x == 0 && lane == 0;
-            const int cgpc = a.KC >> 3;
-            const uint8_t* X8 = reinterpret_cast<const uint8_t*>(a.X);
-            const bool res_pf = a.res_pf && a.y_planar && a.R1 != nullptr && a.r_bf16 && a.up == 1 && a.up_pad == 0;
-            for (int wi = w_first; wi < w_total; wi += w_stride, ++it) {
-                const int tile = tile_of(wi);
-                const bool valid = !PAIR || tile < a.total_tiles;
-                const int rb = tile / a.n_ntiles, b = rb / a.row_tiles, rt = rb % a.row_tiles;
-                const int q_lo = rt * a.msub * 128 + a.off_lo;
-                for (int kc = 0; kc < n_chunks; ++kc) {
-                    if (kc == 0) TRACE(tr, 0, it, 0);
-                    if (lane == 0) STAT_WAIT(a.dbg & 16, 6, mbar_wait_relaxed(bars.a_empty(slot), phase ^ 1));
-                    __syncwarp();
-                    if (kc == 0) TRACE(tr, 0, it, 1);
-                    const uint32_t bar = (PAIR || a.in_act != ACT_NONE) ? bars.a_raw(slot) : bars.a_full(slot);
-                    uint8_t* dst_g = A_smem + (size_t)slot * a.a_bytes;
-                    const uint32_t dst = smem_u32(dst_g);
-                    // the tile is ONE [KC/8][Rp][8] block (its msub*128 rows + the halo): one contiguous run per 8-channel group
-                    const int t0 = q_lo, lo = max(t0, 0), hi = valid ? max(min(t0 + a.Rp, a.Tin), lo) : lo;
-                    const uint32_t run = (uint32_t)(hi - lo) * 16u;
-                    if (valid && (lo > t0 || hi < t0 + a.Rp)) {
-                        for (int g = lane; g < cgpc; g += 32) {
-                            uint4* blk = reinterpret_cast<uint4*>(dst_g + (size_t)g * a.Rp * 16);
-                            for (int r = 0; r < min(lo - t0, a.Rp); ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
-                            for (int r = max(hi - t0, 0); r < a.Rp; ++r) blk[r] = make_uint4(0u, 0u, 0u, 0u);
-                        }
-                        fence_proxy_async();
-                        __syncwarp();
-                    }
-                    if (lane == 0) {
-                        if (run) mbar_expect_tx(bar, run * (uint32_t)cgpc); else mbar_arrive(bar);
-                    }
-                    __syncwarp();
-                    if (run) {
-                        for (int g = lane; g < cgpc; g += 32) {
-                            const uint8_t* src = X8 + (((size_t)b * (a.Cin >> 3) + (size_t)(kc * cgpc + g)) * a.Tin + lo) * 16;
-                            bulk_g2s(dst + (uint32_t)((g * a.Rp + (lo - t0)) * 16), src, run, bar);
-                        }
-                    }
-                    if (kc == 0) TRACE(tr, 0, it, 2);
-                    if (++slot == A_SLOTS) { slot = 0; phase ^= 1; }
-                }
-                if (res_pf && valid) {
-                    // residual rows of this tile -> L2, one run per 8-channel group, a few tiles before the epilogue warps read them.
-                    // The activation copies above keep ~100 KB per SM (15 MB chip-wide) queued at the memory controllers, so a
-                    // residual load that has to go to DRAM waits 2.5-5 us behind them and the epilogue's two load rounds per tile
-                    // (16.8 kcycles at C = 64 k = 11) outlast the tile's MMAs (12.5 kcycles); from L2 they do not.
-                    const int nt = tile % a.n_ntiles, q0 = rt * a.msub * 128;
-                    const int rows = min(a.msub * 128, min(a.Q, a.y_T) - q0);
-                    if (rows > 0) {
-                        const long gs = (long)a.y_T * 8;
-                        const long off = (long)b * a.y_bs + (long)((nt * NT) >> 3) * gs + (long)q0 * 8;
-                        for (int g = lane; g < NT / 8; g += 32) {
-                            bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R1) + off + (long)g * gs, (uint32_t)rows * 16u);
-                            if (a.R2) bulk_prefetch_l2(reinterpret_cast<const bf16*>(a.R2) + off + (long)g * gs, (uint32_t)rows * 16u);
-                        }
-                    }
-                }
-            }
-        }
+        if (TMA_IN && !(a.dbg & 2)) copy_role(0);
     } else if (warp == W_WARP) {
         // ===== weight producer: 1-D bulk copies of pre-tiled blobs =====
         if (lane == 0 && !(a.dbg & 1)) {
@@ -831,6 +841,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_conv_tc(const TcArgs a) {
             }
 #undef MASG_ROLE
         }
+        // MMA warps with nothing to issue help the copy warp (see copy_role)
+        if (TMA_IN && !(a.dbg & 2) && w >= max(n_issuers, 1) && w - max(n_issuers, 1) + 1 < n_copiers) copy_role(w - max(n_issuers, 1) + 1);
         __syncwarp();
     } else {
         // ===== epilogue (8 warps): TMEM -> registers -> bias / activation / residual / scale -> global =====
@@ -1299,6 +1311,13 @@ static void launch_conv_tc_tiled(masg_ctx* c, cudaStream_t s, const ConvDesc& d,
     a.R1 = io.R1; a.R2 = io.R2; a.r_bf16 = io.r_bf16; a.out_scale = io.out_scale; a.post_slope = io.post_slope;
     { static int dbg = -1; if (dbg < 0) { const char* e = getenv("MASG_TC_DEBUG"); dbg = e ? atoi(e) : 0; } a.dbg = dbg; }
     { static int pf = -1; if (pf < 0) { const char* e = getenv("MASG_TC_RESPF"); pf = e ? atoi(e) : 1; } a.res_pf = pf; }
+    {   // helper copiers only where a tile has many runs and few MMAs: the first upsampler (64 groups, 2 taps: 0.290 -> 0.238 ms).
+        // Everywhere else four copiers measured 1-3 % SLOWER than the copy warp alone (more warps polling the slot barriers), and the
+        // k = 1 layers (w_2: 128 runs per 128-row tile), the suspects, did not move: they are not bound by the copy issue.
+        static int nc = -1;
+        if (nc < 0) { const char* e = getenv("MASG_TC_COPIERS"); nc = e ? atoi(e) : 0; }
+        a.copiers = nc > 0 ? nc : ((d.Cin >= 512 && d.taps <= 2) ? 4 : 1);
+    }
     a.ln_g = io.ln_g; a.ln_b = io.ln_b; a.ln_lens = io.ln_lens; a.ln_T = io.ln_T; a.Y16p = io.Y16p;
     if (io.ln_g) {
         MASG_CHECK(NT == 256 && d.N == 256 && io.ln_b, "conv_tc: the fused LayerNorm needs a 256-column tile (weights prepared wide)");
